@@ -1,0 +1,446 @@
+// Memory-bound kernels: softmax cross-entropy (fwd+bwd fused), column sums, AdamW fused with
+// the gradient scale and the bf16 working-copy cast, casts, RNG key evolution, stand-alone
+// activation/dropout. All are sized to stream at HBM rate: 16-byte accesses, grid-stride loops
+// with a grid that is a multiple of the SM count.
+#include "../include/b200dist.h"
+#include "common.cuh"
+
+namespace b200 {
+
+// ------------------------------------------------------------------------------------------
+// softmax cross-entropy: one warp per row when classes <= 1024 (the reference's 10-class head),
+// one block per row otherwise (vocabulary-sized heads). Emits loss sum, correct count, dlogits.
+// Reference: optax.softmax_cross_entropy_with_integer_labels + argmax accuracy
+// (data_paral.py:181-187).
+// ------------------------------------------------------------------------------------------
+__global__ void xent_warp_kernel(const float* __restrict__ logits, int ld, const int64_t* __restrict__ labels,
+                                 int rows, int classes, float grad_scale, __nv_bfloat16* __restrict__ dlogits,
+                                 int ldd, float* __restrict__ metrics, float* __restrict__ row_loss) {
+  const int warps_per_block = blockDim.x >> 5;
+  const int lane = threadIdx.x & 31;
+  float loss_acc = 0.f, correct_acc = 0.f;
+  for (int row = blockIdx.x * warps_per_block + (threadIdx.x >> 5); row < rows;
+       row += gridDim.x * warps_per_block) {
+    const float* x = logits + static_cast<size_t>(row) * ld;
+    const int label = static_cast<int>(labels[row]);
+    float mx = -INFINITY;
+    int amax = 0x7fffffff;
+    for (int c = lane; c < classes; c += 32) {
+      float v = x[c];
+      if (v > mx) { mx = v; amax = c; }
+    }
+    // warp argmax (first index wins ties, like jnp.argmax)
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      float om = __shfl_xor_sync(0xffffffffu, mx, o);
+      int oa = __shfl_xor_sync(0xffffffffu, amax, o);
+      if (om > mx || (om == mx && oa < amax)) { mx = om; amax = oa; }
+    }
+    float sum = 0.f;
+    for (int c = lane; c < classes; c += 32) sum += __expf(x[c] - mx);
+    sum = warp_sum(sum);
+    const float lse = mx + __logf(sum);
+    const float inv = 1.0f / sum;
+    if (dlogits != nullptr) {
+      __nv_bfloat16* d = dlogits + static_cast<size_t>(row) * ldd;
+      for (int c = lane; c < classes; c += 32) {
+        float pch = __expf(x[c] - mx) * inv;
+        d[c] = __float2bfloat16_rn((pch - (c == label ? 1.0f : 0.0f)) * grad_scale);
+      }
+    }
+    if (lane == 0) {
+      float l = lse - x[label];
+      loss_acc += l;
+      correct_acc += (amax == label) ? 1.0f : 0.0f;
+      if (row_loss != nullptr) row_loss[row] = l;
+    }
+  }
+  // one atomic pair per block
+  __shared__ float s_loss[32], s_corr[32];
+  if (lane == 0) { s_loss[threadIdx.x >> 5] = loss_acc; s_corr[threadIdx.x >> 5] = correct_acc; }
+  __syncthreads();
+  if (threadIdx.x == 0 && metrics != nullptr) {
+    float a = 0.f, b = 0.f;
+    for (int w = 0; w < warps_per_block; ++w) { a += s_loss[w]; b += s_corr[w]; }
+    if (a != 0.f || b != 0.f) { atomicAdd(&metrics[0], a); atomicAdd(&metrics[1], b); }
+  }
+}
+
+// Large-vocabulary variant on bf16 logits, in place: logits are replaced by dlogits.
+// One block per row; the row is read twice (max+sum online in pass 1, gradient in pass 2);
+// the second read hits L2 (a 50k-class bf16 row is 100 KB).
+__global__ void __launch_bounds__(512)
+xent_block_bf16_kernel(__nv_bfloat16* __restrict__ logits, int ld, const int64_t* __restrict__ labels,
+                       int rows, int classes, float grad_scale, float* __restrict__ metrics,
+                       float* __restrict__ row_loss) {
+  __shared__ float s_m[16], s_s[16];
+  __shared__ int s_a[16];
+  __shared__ float s_bcast[2];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  for (int row = blockIdx.x; row < rows; row += gridDim.x) {
+    __nv_bfloat16* x = logits + static_cast<size_t>(row) * ld;
+    const int label = static_cast<int>(labels[row]);
+    float mx = -INFINITY, sum = 0.f;
+    int amax = 0x7fffffff;
+    const bool vec = (ld % 8 == 0) && ((reinterpret_cast<uintptr_t>(logits) & 15) == 0);
+    const int nvec = vec ? classes / 8 : 0;
+    for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
+      uint4 w = *reinterpret_cast<const uint4*>(x + i * 8);
+      const uint32_t ws[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float v = __uint_as_float(((ws[j >> 1] >> ((j & 1) * 16)) & 0xFFFFu) << 16);
+        if (v > mx) { sum = sum * __expf(mx - v) + 1.0f; mx = v; amax = i * 8 + j; }
+        else sum += __expf(v - mx);
+      }
+    }
+    for (int c = nvec * 8 + threadIdx.x; c < classes; c += blockDim.x) {
+      float v = __bfloat162float(x[c]);
+      if (v > mx) { sum = sum * __expf(mx - v) + 1.0f; mx = v; amax = c; }
+      else sum += __expf(v - mx);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      float om = __shfl_xor_sync(0xffffffffu, mx, o);
+      float os = __shfl_xor_sync(0xffffffffu, sum, o);
+      int oa = __shfl_xor_sync(0xffffffffu, amax, o);
+      float nm = fmaxf(mx, om);
+      float ns = (mx == -INFINITY ? 0.f : sum * __expf(mx - nm)) + (om == -INFINITY ? 0.f : os * __expf(om - nm));
+      if (om > mx || (om == mx && oa < amax)) amax = oa;
+      mx = nm; sum = ns;
+    }
+    if (lane == 0) { s_m[warp] = mx; s_s[warp] = sum; s_a[warp] = amax; }
+    __syncthreads();
+    if (warp == 0) {
+      float m2 = lane < nwarp ? s_m[lane] : -INFINITY;
+      float s2 = lane < nwarp ? s_s[lane] : 0.f;
+      int a2 = lane < nwarp ? s_a[lane] : 0x7fffffff;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        float om = __shfl_xor_sync(0xffffffffu, m2, o);
+        float os = __shfl_xor_sync(0xffffffffu, s2, o);
+        int oa = __shfl_xor_sync(0xffffffffu, a2, o);
+        float nm = fmaxf(m2, om);
+        float ns = (m2 == -INFINITY ? 0.f : s2 * __expf(m2 - nm)) + (om == -INFINITY ? 0.f : os * __expf(om - nm));
+        if (om > m2 || (om == m2 && oa < a2)) a2 = oa;
+        m2 = nm; s2 = ns;
+      }
+      if (lane == 0) {
+        s_bcast[0] = m2; s_bcast[1] = s2;
+        float l = m2 + __logf(s2) - __bfloat162float(x[label]);
+        if (row_loss != nullptr) row_loss[row] = l;
+        if (metrics != nullptr) {
+          atomicAdd(&metrics[0], l);
+          if (a2 == label) atomicAdd(&metrics[1], 1.0f);
+        }
+      }
+    }
+    __syncthreads();
+    const float m = s_bcast[0];
+    const float inv = 1.0f / s_bcast[1];
+    for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
+      uint4 w = *reinterpret_cast<const uint4*>(x + i * 8);
+      uint32_t ws[4] = {w.x, w.y, w.z, w.w};
+      uint32_t out[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float v0 = __uint_as_float((ws[j] & 0xFFFFu) << 16);
+        float v1 = __uint_as_float(ws[j] & 0xFFFF0000u);
+        int c0 = i * 8 + j * 2;
+        float g0 = (__expf(v0 - m) * inv - (c0 == label ? 1.f : 0.f)) * grad_scale;
+        float g1 = (__expf(v1 - m) * inv - (c0 + 1 == label ? 1.f : 0.f)) * grad_scale;
+        __nv_bfloat162 t = __floats2bfloat162_rn(g0, g1);
+        out[j] = *reinterpret_cast<uint32_t*>(&t);
+      }
+      *reinterpret_cast<uint4*>(x + i * 8) = make_uint4(out[0], out[1], out[2], out[3]);
+    }
+    for (int c = nvec * 8 + threadIdx.x; c < classes; c += blockDim.x) {
+      float v = __bfloat162float(x[c]);
+      x[c] = __float2bfloat16_rn((__expf(v - m) * inv - (c == label ? 1.f : 0.f)) * grad_scale);
+    }
+    __syncthreads();
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// column sums (bias gradients): block (32 x 8) walks a 32-column stripe, coalesced along cols.
+// ------------------------------------------------------------------------------------------
+__global__ void colsum_bf16_kernel(const __nv_bfloat16* __restrict__ x, int ld, int rows, int cols,
+                                   float* __restrict__ out, int accumulate, int row_chunks) {
+  __shared__ float s[8][33];
+  const int col = blockIdx.x * 32 + threadIdx.x;
+  const int chunk = blockIdx.y;
+  const int rows_per = (rows + row_chunks - 1) / row_chunks;
+  const int r0 = chunk * rows_per;
+  const int r1 = min(rows, r0 + rows_per);
+  float acc = 0.f;
+  if (col < cols)
+    for (int r = r0 + threadIdx.y; r < r1; r += 8)
+      acc += __bfloat162float(x[static_cast<size_t>(r) * ld + col]);
+  s[threadIdx.y][threadIdx.x] = acc;
+  __syncthreads();
+  if (threadIdx.y == 0 && col < cols) {
+    float t = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t += s[i][threadIdx.x];
+    if (row_chunks == 1 && !accumulate) out[col] = t;
+    else atomicAdd(&out[col], t);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// AdamW, optax.adamw semantics: m,v update; bias correction with t = count+1; eps outside the
+// sqrt; decoupled weight decay on every leaf. Fused: gradient scale (mean over
+// minibatches / devices), bf16 working copy, optional gradient zeroing for the next step.
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ void adamw_elem(float& p, float& m, float& v, float g, float lr, float b1,
+                                           float b2, float eps, float wd, float c1, float c2) {
+  m = b1 * m + (1.0f - b1) * g;
+  v = b2 * v + (1.0f - b2) * g * g;
+  float mh = m * c1;
+  float vh = v * c2;
+  p = p - lr * (mh / (sqrtf(vh) + eps) + wd * p);
+}
+
+__global__ void adamw_kernel(float* __restrict__ p, float* __restrict__ m, float* __restrict__ v,
+                             float* __restrict__ g, __nv_bfloat16* __restrict__ pb, int64_t n,
+                             b200_adamw_hparams hp, const int32_t* __restrict__ step_count, int zero_grad) {
+  const float t = static_cast<float>(*step_count + 1);
+  const float c1 = 1.0f / (1.0f - __powf(hp.beta1, t));
+  const float c2 = 1.0f / (1.0f - __powf(hp.beta2, t));
+  const int64_t n4 = n >> 2;
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n4; i += stride) {
+    float4 pp = reinterpret_cast<float4*>(p)[i];
+    float4 mm = reinterpret_cast<float4*>(m)[i];
+    float4 vv = reinterpret_cast<float4*>(v)[i];
+    float4 gg = reinterpret_cast<const float4*>(g)[i];
+    adamw_elem(pp.x, mm.x, vv.x, gg.x * hp.grad_scale, hp.lr, hp.beta1, hp.beta2, hp.eps, hp.weight_decay, c1, c2);
+    adamw_elem(pp.y, mm.y, vv.y, gg.y * hp.grad_scale, hp.lr, hp.beta1, hp.beta2, hp.eps, hp.weight_decay, c1, c2);
+    adamw_elem(pp.z, mm.z, vv.z, gg.z * hp.grad_scale, hp.lr, hp.beta1, hp.beta2, hp.eps, hp.weight_decay, c1, c2);
+    adamw_elem(pp.w, mm.w, vv.w, gg.w * hp.grad_scale, hp.lr, hp.beta1, hp.beta2, hp.eps, hp.weight_decay, c1, c2);
+    reinterpret_cast<float4*>(p)[i] = pp;
+    reinterpret_cast<float4*>(m)[i] = mm;
+    reinterpret_cast<float4*>(v)[i] = vv;
+    if (zero_grad) reinterpret_cast<float4*>(g)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (pb != nullptr) {
+      __nv_bfloat162 lo = __floats2bfloat162_rn(pp.x, pp.y);
+      __nv_bfloat162 hi = __floats2bfloat162_rn(pp.z, pp.w);
+      uint2 w;
+      w.x = *reinterpret_cast<uint32_t*>(&lo);
+      w.y = *reinterpret_cast<uint32_t*>(&hi);
+      reinterpret_cast<uint2*>(pb)[i] = w;
+    }
+  }
+  // tail
+  for (int64_t i = (n4 << 2) + static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
+    float pp = p[i], mm = m[i], vv = v[i];
+    adamw_elem(pp, mm, vv, g[i] * hp.grad_scale, hp.lr, hp.beta1, hp.beta2, hp.eps, hp.weight_decay, c1, c2);
+    p[i] = pp; m[i] = mm; v[i] = vv;
+    if (zero_grad) g[i] = 0.f;
+    if (pb != nullptr) pb[i] = __float2bfloat16_rn(pp);
+  }
+}
+
+__global__ void bump_step_kernel(int32_t* step) { *step += 1; }
+
+__global__ void cast_f32_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int64_t n) {
+  const int64_t n4 = n >> 2;
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n4; i += stride) {
+    float4 a = reinterpret_cast<const float4*>(src)[i];
+    __nv_bfloat162 lo = __floats2bfloat162_rn(a.x, a.y), hi = __floats2bfloat162_rn(a.z, a.w);
+    uint2 w;
+    w.x = *reinterpret_cast<uint32_t*>(&lo);
+    w.y = *reinterpret_cast<uint32_t*>(&hi);
+    reinterpret_cast<uint2*>(dst)[i] = w;
+  }
+  for (int64_t i = (n4 << 2) + static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride)
+    dst[i] = __float2bfloat16_rn(src[i]);
+}
+
+__global__ void cast_bf16_f32_kernel(const __nv_bfloat16* __restrict__ src, float* __restrict__ dst, int64_t n) {
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride)
+    dst[i] = __bfloat162float(src[i]);
+}
+
+__global__ void scale_f32_kernel(float* __restrict__ x, int64_t n, float s) {
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride)
+    x[i] = s == 0.f ? 0.f : x[i] * s;
+}
+
+__global__ void rng_split_kernel(uint64_t* key, uint64_t* out_step, uint64_t salt_next, uint64_t salt_step) {
+  uint64_t k = *key;
+  if (out_step != nullptr) *out_step = mix64(k ^ salt_step);
+  *key = mix64(k ^ salt_next);
+}
+
+// stand-alone activation + dropout (rows x cols, pitch ld)
+__global__ void act_dropout_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
+                                   __nv_bfloat16* __restrict__ out, int64_t rows, int cols, int ld, int act,
+                                   const uint64_t* __restrict__ key, uint64_t salt, uint32_t thresh16, float scale,
+                                   int bwd) {
+  uint64_t seed = 0;
+  if (key != nullptr) seed = mix64(*key ^ mix64(salt));
+  const int64_t total = rows * cols;
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
+    int64_t r = i / cols;
+    int c = static_cast<int>(i - r * cols);
+    size_t off = static_cast<size_t>(r) * ld + c;
+    float xv = __bfloat162float(x[off]);
+    float v;
+    if (!bwd) {
+      v = act == B200_ACT_SILU ? silu_f(xv) : act == B200_ACT_GELU ? gelu_f(xv) : xv;
+    } else {
+      float gy = __bfloat162float(dy[off]);
+      float d = act == B200_ACT_SILU ? silu_grad_f(xv) : act == B200_ACT_GELU ? gelu_grad_f(xv) : 1.0f;
+      v = gy * d;
+    }
+    if (key != nullptr) v = dropout_keep(seed, static_cast<uint64_t>(i), thresh16) ? v * scale : 0.f;
+    out[off] = __float2bfloat16_rn(v);
+  }
+}
+
+static inline int stream_grid(int64_t work_items, int threads) {
+  int64_t blocks = (work_items + threads - 1) / threads;
+  int64_t cap = static_cast<int64_t>(num_sms()) * 8;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  return static_cast<int>(blocks);
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_softmax_xent(const float* logits, int ld_logits, const int64_t* labels, int rows,
+                                 int classes, float grad_scale, void* dlogits, int ld_dlogits,
+                                 float* metrics, float* row_loss, void* stream) {
+  B200_REQUIRE(rows > 0 && classes > 0, "xent: empty input");
+  const int threads = 128;
+  int blocks = (rows + 3) / 4;
+  int cap = num_sms() * 16;
+  if (blocks > cap) blocks = cap;
+  xent_warp_kernel<<<blocks, threads, 0, static_cast<cudaStream_t>(stream)>>>(
+      logits, ld_logits, labels, rows, classes, grad_scale, static_cast<__nv_bfloat16*>(dlogits),
+      ld_dlogits, metrics, row_loss);
+  count_launch();
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200_softmax_xent_bf16_inplace(void* logits_bf16, int ld, const int64_t* labels, int rows,
+                                              int classes, float grad_scale, float* metrics, float* row_loss,
+                                              void* stream) {
+  B200_REQUIRE(rows > 0 && classes > 0, "xent: empty input");
+  int blocks = rows < num_sms() * 4 ? rows : num_sms() * 4;
+  xent_block_bf16_kernel<<<blocks, 512, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<__nv_bfloat16*>(logits_bf16), ld, labels, rows, classes, grad_scale, metrics, row_loss);
+  count_launch();
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200_colsum_bf16(const void* x, int ld, int rows, int cols, float* out, int accumulate,
+                                void* stream) {
+  B200_REQUIRE(rows > 0 && cols > 0, "colsum: empty input");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  int col_blocks = (cols + 31) / 32;
+  int row_chunks = 1;
+  // enough blocks to fill the chip when the matrix is tall
+  while (col_blocks * row_chunks < num_sms() * 2 && rows / (row_chunks * 2) >= 64) row_chunks *= 2;
+  if (row_chunks > 1 && !accumulate) {
+    B200_CUDA(cudaMemsetAsync(out, 0, sizeof(float) * cols, s));
+  }
+  colsum_bf16_kernel<<<dim3(col_blocks, row_chunks), dim3(32, 8), 0, s>>>(
+      static_cast<const __nv_bfloat16*>(x), ld, rows, cols, out, accumulate, row_chunks);
+  count_launch();
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200_adamw(float* p, float* m, float* v, const float* g, void* p_bf16, int64_t n,
+                          const b200_adamw_hparams* hp, int32_t* step_count, int bump_step, int zero_grad,
+                          void* stream) {
+  B200_REQUIRE(n > 0, "adamw: empty buffer");
+  B200_REQUIRE(((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(m) |
+                 reinterpret_cast<uintptr_t>(v) | reinterpret_cast<uintptr_t>(g)) & 15) == 0,
+               "adamw: buffers must be 16-byte aligned");
+  B200_REQUIRE(p_bf16 == nullptr || (reinterpret_cast<uintptr_t>(p_bf16) & 7) == 0,
+               "adamw: bf16 copy must be 8-byte aligned");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  adamw_kernel<<<stream_grid(n / 4 + 1, 256), 256, 0, s>>>(p, m, v, const_cast<float*>(g),
+                                                          static_cast<__nv_bfloat16*>(p_bf16), n, *hp,
+                                                          step_count, zero_grad);
+  count_launch();
+  if (bump_step) {
+    bump_step_kernel<<<1, 1, 0, s>>>(step_count);
+    count_launch();
+  }
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200_cast_f32_bf16(const float* src, void* dst, int64_t n, void* stream) {
+  B200_REQUIRE(n > 0, "cast: empty buffer");
+  B200_REQUIRE((reinterpret_cast<uintptr_t>(src) & 15) == 0 && (reinterpret_cast<uintptr_t>(dst) & 7) == 0,
+               "cast: misaligned buffers");
+  cast_f32_bf16_kernel<<<stream_grid(n / 4 + 1, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      src, static_cast<__nv_bfloat16*>(dst), n);
+  count_launch();
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200_cast_bf16_f32(const void* src, float* dst, int64_t n, void* stream) {
+  B200_REQUIRE(n > 0, "cast: empty buffer");
+  cast_bf16_f32_kernel<<<stream_grid(n, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(src), dst, n);
+  count_launch();
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200_scale_f32(float* x, int64_t n, float scale, void* stream) {
+  B200_REQUIRE(n > 0, "scale: empty buffer");
+  scale_f32_kernel<<<stream_grid(n, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, n, scale);
+  count_launch();
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200_rng_split(uint64_t* key, uint64_t* out_step, uint64_t salt_next, uint64_t salt_step,
+                              void* stream) {
+  rng_split_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(key, out_step, salt_next, salt_step);
+  count_launch();
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
+
+static int act_dropout_launch(const void* x, const void* dy, void* out, int64_t rows, int cols, int ld,
+                              int act, const uint64_t* key, uint64_t salt, float rate, int bwd, void* stream) {
+  B200_REQUIRE(rows > 0 && cols > 0, "act_dropout: empty input");
+  float keep = 1.0f - rate;
+  const uint64_t* k = rate > 0.f ? key : nullptr;
+  act_dropout_kernel<<<stream_grid(rows * cols, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(dy),
+      static_cast<__nv_bfloat16*>(out), rows, cols, ld, act, k, salt,
+      static_cast<uint32_t>(keep * 65536.0f + 0.5f), keep > 0.f ? 1.0f / keep : 0.f, bwd);
+  count_launch();
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200_act_dropout_fwd(const void* x, void* y, int64_t rows, int cols, int ld, int act,
+                                    const uint64_t* drop_key, uint64_t drop_salt, float drop_rate,
+                                    void* stream) {
+  return act_dropout_launch(x, nullptr, y, rows, cols, ld, act, drop_key, drop_salt, drop_rate, 0, stream);
+}
+extern "C" int b200_act_dropout_bwd(const void* x, const void* dy, void* dx, int64_t rows, int cols, int ld,
+                                    int act, const uint64_t* drop_key, uint64_t drop_salt, float drop_rate,
+                                    void* stream) {
+  return act_dropout_launch(x, dy, dx, rows, cols, ld, act, drop_key, drop_salt, drop_rate, 1, stream);
+}

@@ -1,0 +1,530 @@
+// Persistent, warp-specialised bf16 GEMM for sm_100a.
+//
+//   warp 0      TMA producer   cp.async.bulk.tensor tiles -> 128B-swizzled shared memory ring
+//   warp 1      MMA issuer     one lane issues tcgen05.mma (M=128, N=BN, K=16), accumulators in TMEM
+//   warps 2..5  epilogue       tcgen05.ld -> registers -> bias/activation/dropout/residual/cast -> global
+//
+// TMEM holds two accumulator stages so the epilogue of tile i overlaps the main loop of tile
+// i+1. The B operand can come from several equally sized shards (peer GPUs' memory) selected
+// per K block or per N tile: that is the FSDP all-gather fused into the consuming GEMM.
+//
+// What the reference does here: flax nn.Dense lowered by XLA to a library GEMM followed by
+// separate elementwise fusions (data_paral.py:86-100); FSDP gathers the weight with a
+// stand-alone all_gather before the matmul (param_sharding.py:140,153-158).
+#include "../include/b200dist.h"
+#include "common.cuh"
+
+namespace b200 {
+
+constexpr int BM = 128;
+constexpr int BK = 64;       // 64 bf16 = one 128-byte swizzle row
+constexpr int UMMA_K = 16;
+constexpr int GEMM_THREADS = 192;
+
+struct TmapSet {
+  CUtensorMap m[8];
+};
+
+struct GemmDev {
+  int M, N, K;
+  int shard_mode, nsrc, shard_len, rot;
+  // epilogue
+  void* d;
+  int ldd, d_fp32, accumulate;
+  float alpha;
+  const __nv_bfloat16* bias;
+  __nv_bfloat16* pre;
+  int ldpre;
+  int act;
+  const __nv_bfloat16* resid;
+  int ldres;
+  int bwd;
+  const __nv_bfloat16* aux;
+  int ldaux;
+  const uint64_t* drop_key;
+  uint64_t drop_salt;
+  uint32_t drop_thresh16;
+  float drop_scale;
+  int vec_d, vec_pre, vec_aux, vec_res;  // 16-byte vector access allowed
+};
+
+template <int BN>
+struct GemmCfg {
+  static constexpr int A_BYTES = BM * BK * 2;
+  static constexpr int B_BYTES = BN * BK * 2;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int STAGES = (BN == 256) ? 4 : (BN == 128) ? 6 : 8;
+  static constexpr uint32_t TMEM_COLS = (2 * BN <= 32) ? 32 : (2 * BN <= 64) ? 64 : (2 * BN <= 128) ? 128 : (2 * BN <= 256) ? 256 : 512;
+  static constexpr int BAR_BYTES = (2 * STAGES + 4) * 8 + 16;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + BAR_BYTES + 1024;  // + alignment slack
+};
+
+struct TileCoord {
+  int m0, n0, n_limit, b_n, b_src;
+};
+
+__device__ __forceinline__ TileCoord tile_coord(const GemmDev& p, int tile, int m_tiles, int BN) {
+  TileCoord t;
+  int mt = tile % m_tiles;
+  int nt = tile / m_tiles;
+  t.m0 = mt * BM;
+  if (p.shard_mode == 2) {
+    int tps = (p.shard_len + BN - 1) / BN;
+    int n_tiles = tps * p.nsrc;
+    nt = (nt + p.rot * tps) % n_tiles;
+    int src = nt / tps, loc = nt % tps;
+    t.b_src = src;
+    t.b_n = loc * BN;
+    t.n0 = src * p.shard_len + loc * BN;
+    int lim = (src + 1) * p.shard_len;
+    t.n_limit = lim < p.N ? lim : p.N;
+  } else {
+    t.b_src = 0;
+    t.b_n = nt * BN;
+    t.n0 = nt * BN;
+    t.n_limit = p.N;
+  }
+  return t;
+}
+
+__device__ __forceinline__ float bf16_bits_to_f(uint32_t v) { return __uint_as_float(v << 16); }
+
+template <int BN, int A_MN, int B_MN>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ TmapSet tma_b,
+                    const GemmDev p) {
+  using Cfg = GemmCfg<BN>;
+  constexpr int STAGES = Cfg::STAGES;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE_BYTES);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tmem_full = empty_bar + STAGES;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  const int m_tiles = (p.M + BM - 1) / BM;
+  int n_tiles;
+  if (p.shard_mode == 2)
+    n_tiles = ((p.shard_len + BN - 1) / BN) * p.nsrc;
+  else
+    n_tiles = (p.N + BN - 1) / BN;
+  const int num_tiles = m_tiles * n_tiles;
+  int kps = 0, nk;
+  if (p.shard_mode == 1) {
+    // TMA needs the innermost coordinate 16-byte aligned. A shard that starts at an A column that
+    // is not a multiple of 8 is read from the aligned column below it, and B's row coordinate
+    // (outer dimension, may go negative: zero-filled) moves down by the same shift, so up to 7
+    // extra K rows per shard may be touched.
+    kps = (p.shard_len + ((p.shard_len & 7) ? 7 : 0) + BK - 1) / BK;
+    nk = kps * p.nsrc;
+  } else {
+    nk = (p.K + BK - 1) / BK;
+  }
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tma_a);
+    for (int s = 0; s < p.nsrc; ++s) tma_prefetch_desc(&tma_b.m[s]);
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&tmem_full[s], 1);
+      mbar_init(&tmem_empty[s], 4);
+    }
+    mbar_fence_init();
+  }
+  if (warp == 1) tmem_alloc<Cfg::TMEM_COLS>(tmem_ptr);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        TileCoord tc = tile_coord(p, tile, m_tiles, BN);
+        for (int it = 0; it < nk; ++it) {
+          int a_k, b_k, b_src;
+          if (p.shard_mode == 1) {
+            int s = it / kps, kb = it - s * kps;
+            b_src = p.rot + s;
+            if (b_src >= p.nsrc) b_src -= p.nsrc;
+            const int base = b_src * p.shard_len;
+            const int shift = base & 7;
+            a_k = base - shift + kb * BK;
+            b_k = kb * BK - shift;
+          } else {
+            a_k = b_k = it * BK;
+            b_src = tc.b_src;
+          }
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * Cfg::STAGE_BYTES;
+          uint8_t* sb = sa + Cfg::A_BYTES;
+          mbar_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
+          if (A_MN == 0) {
+            tma_load_2d(sa, &tma_a, &full_bar[stage], a_k, tc.m0);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BM / 64; ++j)
+              tma_load_2d(sa + j * (64 * BK * 2), &tma_a, &full_bar[stage], tc.m0 + j * 64, a_k);
+          }
+          const CUtensorMap* bm = &tma_b.m[b_src];
+          if (B_MN == 0) {
+            tma_load_2d(sb, bm, &full_bar[stage], b_k, tc.b_n);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j)
+              tma_load_2d(sb + j * (64 * BK * 2), bm, &full_bar[stage], tc.b_n + j * 64, b_k);
+          }
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    constexpr uint32_t idesc = umma_idesc_bf16(BM, BN, A_MN, B_MN);
+    // K-major SW128: rows of 128 B, 8-row groups 1024 B apart; next K=16 slice is +32 B.
+    // MN-major SW128: k rows of 128 B (64 MN elements), 8-k groups 1024 B apart (SBO),
+    //                 64-element MN blocks BK*128 B apart (LBO); next K=16 slice is +2048 B.
+    constexpr uint32_t A_LBO = A_MN ? BK * 128 : 16, A_SBO = 1024, A_KSTEP = A_MN ? 2048 : 32;
+    constexpr uint32_t B_LBO = B_MN ? BK * 128 : 16, B_SBO = 1024, B_KSTEP = B_MN ? 2048 : 32;
+    int stage = 0;
+    uint32_t phase = 0;
+    int local = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
+      const int as = local & 1;
+      const uint32_t aphase = (local >> 1) & 1;
+      mbar_wait(&tmem_empty[as], aphase ^ 1);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + as * BN;
+      for (int it = 0; it < nk; ++it) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        if (lane == 0) {
+          const uint32_t sa = smem_u32(smem + stage * Cfg::STAGE_BYTES);
+          const uint32_t sb = sa + Cfg::A_BYTES;
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            uint64_t da = umma_smem_desc(sa + k * A_KSTEP, A_LBO, A_SBO);
+            uint64_t db = umma_smem_desc(sb + k * B_KSTEP, B_LBO, B_SBO);
+            umma_bf16(d_tmem, da, db, idesc, (it | k) ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[stage]);
+          if (it == nk - 1) umma_commit(&tmem_full[as]);
+        }
+        __syncwarp();
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+    }
+  } else {
+    // ===================== epilogue (warps 2..5) =====================
+    const int quad = warp & 3;  // TMEM lane quadrant this warp may read
+    uint64_t seed = 0;
+    if (p.drop_key != nullptr) seed = mix64(*p.drop_key ^ mix64(p.drop_salt));
+    int local = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
+      const int as = local & 1;
+      const uint32_t aphase = (local >> 1) & 1;
+      TileCoord tc = tile_coord(p, tile, m_tiles, BN);
+      mbar_wait(&tmem_full[as], aphase);
+      tc_fence_after();
+      const int row = tc.m0 + quad * 32 + lane;
+      const bool row_ok = row < p.M;
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + as * BN;
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        const int col0 = tc.n0 + c * 32;
+        if (col0 >= tc.n_limit) break;  // warp-uniform
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(taddr + c * 32, r);
+        tmem_ld_wait();
+        // keep the warp converged around the .sync.aligned TMEM loads: predicate, don't branch out
+        if (row_ok) {
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          const int col = col0 + g * 8;
+          if (col >= tc.n_limit) break;
+          const bool full8 = col + 8 <= tc.n_limit;
+          float v[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[g * 8 + j]) * p.alpha;
+          if (!p.bwd) {
+            if (p.bias != nullptr) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j)
+                if (col + j < tc.n_limit) v[j] += __bfloat162float(p.bias[col + j]);
+            }
+            if (p.pre != nullptr) {
+              __nv_bfloat16* pp = p.pre + static_cast<size_t>(row) * p.ldpre + col;
+              if (full8 && p.vec_pre) {
+                uint4 w;
+                __nv_bfloat162 t0 = __floats2bfloat162_rn(v[0], v[1]);
+                __nv_bfloat162 t1 = __floats2bfloat162_rn(v[2], v[3]);
+                __nv_bfloat162 t2 = __floats2bfloat162_rn(v[4], v[5]);
+                __nv_bfloat162 t3 = __floats2bfloat162_rn(v[6], v[7]);
+                w.x = *reinterpret_cast<uint32_t*>(&t0);
+                w.y = *reinterpret_cast<uint32_t*>(&t1);
+                w.z = *reinterpret_cast<uint32_t*>(&t2);
+                w.w = *reinterpret_cast<uint32_t*>(&t3);
+                *reinterpret_cast<uint4*>(pp) = w;
+              } else {
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                  if (col + j < tc.n_limit) pp[j] = __float2bfloat16_rn(v[j]);
+              }
+              // the activation sees the value as it was stored (bf16), like the backward will
+#pragma unroll
+              for (int j = 0; j < 8; ++j) v[j] = __bfloat162float(__float2bfloat16_rn(v[j]));
+            }
+            if (p.act == B200_ACT_SILU) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) v[j] = silu_f(v[j]);
+            } else if (p.act == B200_ACT_GELU) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) v[j] = gelu_f(v[j]);
+            }
+          } else if (p.aux != nullptr) {
+            const __nv_bfloat16* ap = p.aux + static_cast<size_t>(row) * p.ldaux + col;
+            float x[8];
+            if (full8 && p.vec_aux) {
+              uint4 w = *reinterpret_cast<const uint4*>(ap);
+              x[0] = bf16_bits_to_f(w.x & 0xFFFF); x[1] = bf16_bits_to_f(w.x >> 16);
+              x[2] = bf16_bits_to_f(w.y & 0xFFFF); x[3] = bf16_bits_to_f(w.y >> 16);
+              x[4] = bf16_bits_to_f(w.z & 0xFFFF); x[5] = bf16_bits_to_f(w.z >> 16);
+              x[6] = bf16_bits_to_f(w.w & 0xFFFF); x[7] = bf16_bits_to_f(w.w >> 16);
+            } else {
+#pragma unroll
+              for (int j = 0; j < 8; ++j)
+                x[j] = (col + j < tc.n_limit) ? __bfloat162float(ap[j]) : 0.0f;
+            }
+            if (p.act == B200_ACT_SILU) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) v[j] *= silu_grad_f(x[j]);
+            } else if (p.act == B200_ACT_GELU) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) v[j] *= gelu_grad_f(x[j]);
+            }
+          }
+          if (p.drop_key != nullptr) {
+            const uint64_t base = static_cast<uint64_t>(row) * static_cast<uint64_t>(p.N) + col;
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              v[j] = dropout_keep(seed, base + j, p.drop_thresh16) ? v[j] * p.drop_scale : 0.0f;
+          }
+          if (!p.bwd && p.resid != nullptr) {
+            const __nv_bfloat16* rp = p.resid + static_cast<size_t>(row) * p.ldres + col;
+            if (full8 && p.vec_res) {
+              uint4 w = *reinterpret_cast<const uint4*>(rp);
+              v[0] += bf16_bits_to_f(w.x & 0xFFFF); v[1] += bf16_bits_to_f(w.x >> 16);
+              v[2] += bf16_bits_to_f(w.y & 0xFFFF); v[3] += bf16_bits_to_f(w.y >> 16);
+              v[4] += bf16_bits_to_f(w.z & 0xFFFF); v[5] += bf16_bits_to_f(w.z >> 16);
+              v[6] += bf16_bits_to_f(w.w & 0xFFFF); v[7] += bf16_bits_to_f(w.w >> 16);
+            } else {
+#pragma unroll
+              for (int j = 0; j < 8; ++j)
+                if (col + j < tc.n_limit) v[j] += __bfloat162float(rp[j]);
+            }
+          }
+          // ---- store ----
+          if (p.d_fp32) {
+            float* dp = reinterpret_cast<float*>(p.d) + static_cast<size_t>(row) * p.ldd + col;
+            if (full8 && p.vec_d) {
+              float4 o0 = make_float4(v[0], v[1], v[2], v[3]);
+              float4 o1 = make_float4(v[4], v[5], v[6], v[7]);
+              if (p.accumulate) {
+                float4 c0 = *reinterpret_cast<float4*>(dp);
+                float4 c1 = *reinterpret_cast<float4*>(dp + 4);
+                o0.x += c0.x; o0.y += c0.y; o0.z += c0.z; o0.w += c0.w;
+                o1.x += c1.x; o1.y += c1.y; o1.z += c1.z; o1.w += c1.w;
+              }
+              *reinterpret_cast<float4*>(dp) = o0;
+              *reinterpret_cast<float4*>(dp + 4) = o1;
+            } else {
+#pragma unroll
+              for (int j = 0; j < 8; ++j)
+                if (col + j < tc.n_limit) dp[j] = p.accumulate ? dp[j] + v[j] : v[j];
+            }
+          } else {
+            __nv_bfloat16* dp =
+                reinterpret_cast<__nv_bfloat16*>(p.d) + static_cast<size_t>(row) * p.ldd + col;
+            if (full8 && p.vec_d) {
+              uint4 w;
+              __nv_bfloat162 t0 = __floats2bfloat162_rn(v[0], v[1]);
+              __nv_bfloat162 t1 = __floats2bfloat162_rn(v[2], v[3]);
+              __nv_bfloat162 t2 = __floats2bfloat162_rn(v[4], v[5]);
+              __nv_bfloat162 t3 = __floats2bfloat162_rn(v[6], v[7]);
+              w.x = *reinterpret_cast<uint32_t*>(&t0);
+              w.y = *reinterpret_cast<uint32_t*>(&t1);
+              w.z = *reinterpret_cast<uint32_t*>(&t2);
+              w.w = *reinterpret_cast<uint32_t*>(&t3);
+              *reinterpret_cast<uint4*>(dp) = w;
+            } else {
+#pragma unroll
+              for (int j = 0; j < 8; ++j)
+                if (col + j < tc.n_limit) dp[j] = __float2bfloat16_rn(v[j]);
+            }
+          }
+        }
+        }  // row_ok
+        __syncwarp();
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tmem_empty[as]);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// host
+// ---------------------------------------------------------------------------------------------
+template <int BN, int A_MN, int B_MN>
+static int launch_gemm(const b200_gemm_args& a, const GemmDev& dev, cudaStream_t stream) {
+  using Cfg = GemmCfg<BN>;
+  CUtensorMap ta;
+  TmapSet tb;
+  memset(&tb, 0, sizeof(tb));
+  int rc;
+  if (A_MN == 0)
+    rc = make_tmap_2d(&ta, a.a, 2, (uint64_t)a.k, (uint64_t)a.m, (uint64_t)a.lda * 2, BK, BM, 128);
+  else
+    rc = make_tmap_2d(&ta, a.a, 2, (uint64_t)a.m, (uint64_t)a.k, (uint64_t)a.lda * 2, 64, BK, 128);
+  if (rc) return rc;
+  // logical extent of one B source
+  uint64_t bn = a.n, bk = a.k;
+  if (a.b_shard_mode == 1) bk = a.b_shard_len;
+  if (a.b_shard_mode == 2) bn = a.b_shard_len;
+  for (int s = 0; s < dev.nsrc; ++s) {
+    if (B_MN == 0)
+      rc = make_tmap_2d(&tb.m[s], a.b_src[s], 2, bk, bn, (uint64_t)a.ldb * 2, BK, BN, 128);
+    else
+      rc = make_tmap_2d(&tb.m[s], a.b_src[s], 2, bn, bk, (uint64_t)a.ldb * 2, 64, BK, 128);
+    if (rc) return rc;
+  }
+  auto kern = gemm_tcgen05_kernel<BN, A_MN, B_MN>;
+  static bool attr_done = false;
+  if (!attr_done) {
+    B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   Cfg::SMEM_BYTES));
+    attr_done = true;
+  }
+  int m_tiles = (a.m + BM - 1) / BM;
+  int n_tiles = (a.b_shard_mode == 2) ? ((a.b_shard_len + BN - 1) / BN) * dev.nsrc
+                                      : (a.n + BN - 1) / BN;
+  long long tiles = (long long)m_tiles * n_tiles;
+  int grid = (int)(tiles < num_sms() ? tiles : num_sms());
+  kern<<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(ta, tb, dev);
+  count_launch();
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
+
+template <int BN>
+static int dispatch_major(const b200_gemm_args& a, const GemmDev& dev, cudaStream_t s) {
+  if (a.a_mn == 0 && a.b_mn == 0) return launch_gemm<BN, 0, 0>(a, dev, s);
+  if (a.a_mn == 0 && a.b_mn == 1) return launch_gemm<BN, 0, 1>(a, dev, s);
+  if (a.a_mn == 1 && a.b_mn == 0) return launch_gemm<BN, 1, 0>(a, dev, s);
+  return launch_gemm<BN, 1, 1>(a, dev, s);
+}
+
+static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+}  // namespace b200
+
+extern "C" int b200_gemm_bf16(const b200_gemm_args* args, void* stream) {
+  using namespace b200;
+  const b200_gemm_args& a = *args;
+  B200_REQUIRE(a.m > 0 && a.n > 0 && a.k > 0, "gemm: empty problem %dx%dx%d", a.m, a.n, a.k);
+  B200_REQUIRE(a.a != nullptr && a.d != nullptr, "gemm: null operand");
+  B200_REQUIRE(a.lda % 8 == 0 && a.ldb % 8 == 0, "gemm: lda/ldb must be multiples of 8 (got %d, %d)",
+               a.lda, a.ldb);
+  B200_REQUIRE(!(a.accumulate && !a.d_fp32), "gemm: accumulate needs an fp32 output");
+  int nsrc = a.b_shard_mode == 0 ? 1 : a.b_nsrc;
+  B200_REQUIRE(nsrc >= 1 && nsrc <= 8, "gemm: b_nsrc %d out of range", nsrc);
+  for (int s = 0; s < nsrc; ++s) B200_REQUIRE(a.b_src[s] != nullptr, "gemm: null B source %d", s);
+  if (a.b_shard_mode == 1)
+    B200_REQUIRE((long long)a.b_shard_len * nsrc == a.k, "gemm: K shards (%d x %d) != K (%d)",
+                 a.b_shard_len, nsrc, a.k);
+  if (a.b_shard_mode == 1 && !a.b_mn)
+    B200_REQUIRE(a.b_shard_len % 8 == 0,
+                 "gemm: K-sharded K-major B needs shard_len %% 8 == 0 (got %d): gather it first",
+                 a.b_shard_len);
+  if (a.b_shard_mode == 2)
+    B200_REQUIRE((long long)a.b_shard_len * nsrc == a.n, "gemm: N shards (%d x %d) != N (%d)",
+                 a.b_shard_len, nsrc, a.n);
+  GemmDev dev;
+  memset(&dev, 0, sizeof(dev));
+  dev.M = a.m; dev.N = a.n; dev.K = a.k;
+  dev.shard_mode = a.b_shard_mode; dev.nsrc = nsrc; dev.shard_len = a.b_shard_len;
+  dev.rot = nsrc > 1 ? ((a.b_rot % nsrc) + nsrc) % nsrc : 0;
+  dev.d = a.d; dev.ldd = a.ldd; dev.d_fp32 = a.d_fp32; dev.accumulate = a.accumulate;
+  dev.alpha = a.alpha == 0.0f ? 1.0f : a.alpha;
+  dev.bias = static_cast<const __nv_bfloat16*>(a.bias);
+  dev.pre = static_cast<__nv_bfloat16*>(a.pre); dev.ldpre = a.ldpre;
+  dev.act = a.act;
+  dev.resid = static_cast<const __nv_bfloat16*>(a.resid); dev.ldres = a.ldres;
+  dev.bwd = a.bwd;
+  dev.aux = static_cast<const __nv_bfloat16*>(a.aux); dev.ldaux = a.ldaux;
+  dev.drop_key = (a.drop_rate > 0.0f) ? a.drop_key : nullptr;
+  dev.drop_salt = a.drop_salt;
+  float keep = 1.0f - a.drop_rate;
+  dev.drop_thresh16 = (uint32_t)(keep * 65536.0f + 0.5f);
+  dev.drop_scale = keep > 0.f ? 1.0f / keep : 0.f;
+  int dvec = a.d_fp32 ? 4 : 8;
+  dev.vec_d = aligned16(a.d) && (a.ldd % dvec == 0) &&
+              (a.b_shard_mode != 2 || a.b_shard_len % 8 == 0);
+  dev.vec_pre = a.pre && aligned16(a.pre) && (a.ldpre % 8 == 0) && dev.vec_d;
+  dev.vec_aux = a.aux && aligned16(a.aux) && (a.ldaux % 8 == 0) && dev.vec_d;
+  dev.vec_res = a.resid && aligned16(a.resid) && (a.ldres % 8 == 0) && dev.vec_d;
+  if (a.b_shard_mode == 2 && a.b_shard_len % 8 != 0) {
+    dev.vec_pre = dev.vec_aux = dev.vec_res = 0;
+  }
+
+  int bn = a.block_n;
+  if (bn == 0) {
+    int n_eff = a.b_shard_mode == 2 ? a.b_shard_len : a.n;
+    if (n_eff <= 64) bn = 64;
+    else if (n_eff <= 128) bn = 128;
+    else {
+      // cost ~ waves * tile width; 128-wide tiles pay ~15% more shared-memory traffic per flop
+      long long m_tiles = (a.m + BM - 1) / BM;
+      long long reps = a.b_shard_mode == 2 ? nsrc : 1;
+      long long t256 = m_tiles * ((n_eff + 255) / 256) * reps;
+      long long t128 = m_tiles * ((n_eff + 127) / 128) * reps;
+      long long sms = num_sms();
+      double c256 = (double)((t256 + sms - 1) / sms) * 256.0;
+      double c128 = (double)((t128 + sms - 1) / sms) * 128.0 * 1.15;
+      bn = c256 <= c128 ? 256 : 128;
+    }
+  }
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  switch (bn) {
+    case 64: return dispatch_major<64>(a, dev, s);
+    case 128: return dispatch_major<128>(a, dev, s);
+    case 256: return dispatch_major<256>(a, dev, s);
+    default: B200_REQUIRE(false, "gemm: unsupported block_n %d", bn);
+  }
+  return 0;
+}

@@ -1,0 +1,205 @@
+/* b200dist — C ABI of the sm_100a kernel library (libb200dist.so).
+ *
+ * Every function returns 0 on success; on failure it returns non-zero and the text is
+ * available from b200_last_error() (per calling thread). All pointers are device pointers
+ * unless stated otherwise; `stream` is a cudaStream_t passed as void*.
+ *
+ * The Python package loads this library with ctypes (jax_distributed_tuts_b200/ops/_lib.py);
+ * nothing here depends on PyTorch.
+ */
+#ifndef B200DIST_H_
+#define B200DIST_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_ABI_VERSION 3
+
+const char* b200_last_error(void);
+int b200_abi_version(void);
+/* Number of kernels launched by this library since the last reset (host-side counter). */
+long long b200_launch_count(void);
+void b200_reset_launch_count(void);
+
+/* ------------------------------------------------------------------------------------------
+ * GEMM on tcgen05 tensor cores with TMEM accumulators and TMA-fed operand tiles.
+ *
+ *   D[M,N] (+)= epilogue( A[M,K] * B[K,N] ),  bf16 inputs, fp32 accumulation.
+ *
+ * Operand storage (all row-major bf16, `ld*` = row pitch in elements, multiple of 8):
+ *   a_mn = 0: A stored [M][K] (K contiguous)      a_mn = 1: A stored [K][M] (M contiguous)
+ *   b_mn = 0: B stored [N][K] (K contiguous)      b_mn = 1: B stored [K][N] (N contiguous)
+ * This covers the three products of a Dense layer whose kernel is kept in the reference's
+ * (in, out) layout (reference: data_paral.py:86-98):
+ *   forward  y  = x  * W      a_mn=0, b_mn=1
+ *   dgrad    dx = dy * W^T    a_mn=0, b_mn=0
+ *   wgrad    dW = x^T * dy    a_mn=1, b_mn=1   (accumulate=1 sums minibatches in place,
+ *                                               reference: util.py:69-77)
+ *
+ * Sharded B (FSDP all-gather fused into the consuming GEMM; reference: param_sharding.py:129-175
+ * gathers the weight first and multiplies afterwards): B may be given as `b_nsrc` equally sized
+ * shards that live on different GPUs (peer-mapped pointers). The TMA producer reads each shard in
+ * place, so no gathered copy of the weight is ever materialised.
+ *   b_shard_mode = 0  single B (b_src[0])
+ *   b_shard_mode = 1  shards split K: shard s holds K rows/cols [s*b_shard_len, (s+1)*b_shard_len)
+ *   b_shard_mode = 2  shards split N: shard s holds N rows/cols [s*b_shard_len, (s+1)*b_shard_len)
+ *   b_rot             shard visited first (callers pass their own rank so that peers are pulled
+ *                     evenly).
+ * ------------------------------------------------------------------------------------------ */
+enum { B200_ACT_NONE = 0, B200_ACT_SILU = 1, B200_ACT_GELU = 2 };
+
+typedef struct b200_gemm_args {
+  const void* a;
+  const void* b_src[8];
+  void* d;
+  int32_t m, n, k;
+  int32_t lda, ldb, ldd;
+  int32_t a_mn, b_mn;
+  int32_t b_nsrc, b_shard_mode, b_shard_len, b_rot;
+  int32_t d_fp32;     /* 1: D is fp32, 0: D is bf16 */
+  int32_t accumulate; /* 1: D += result (fp32 D only) */
+  float alpha;        /* result scale applied to the accumulator first */
+  /* forward epilogue: v = alpha*acc + bias; pre = v; v = act(v); v = dropout(v); v += resid */
+  const void* bias; /* bf16 [N] or NULL */
+  void* pre;        /* bf16 [M][ldpre] or NULL: saved pre-activation */
+  int32_t ldpre;
+  int32_t act; /* B200_ACT_* */
+  const void* resid; /* bf16 [M][ldres] or NULL */
+  int32_t ldres;
+  /* backward epilogue (bwd = 1): v = alpha*acc * dropout_mask_scale * act'(aux) */
+  int32_t bwd;
+  const void* aux; /* bf16 [M][ldaux]: the forward's saved pre-activation */
+  int32_t ldaux;
+  /* dropout (either direction); disabled when drop_key == NULL */
+  const uint64_t* drop_key; /* device pointer to the 64-bit step key */
+  uint64_t drop_salt;       /* host constant folded into the key (minibatch, rank, layer) */
+  float drop_rate;
+  int32_t block_n; /* 0 = choose, else 64/128/256 */
+} b200_gemm_args;
+
+int b200_gemm_bf16(const b200_gemm_args* args, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Softmax cross-entropy with integer labels, forward + backward in one pass
+ * (reference: data_paral.py:181-187).
+ *   logits fp32 [rows][ld_logits]; labels int64 [rows]
+ *   dlogits (bf16, pitch ld_dlogits, may be NULL) = (softmax - onehot) * grad_scale
+ *   metrics (fp32[2], accumulated atomically): [0] += sum of per-row losses, [1] += #correct
+ *   row_loss (fp32 [rows], may be NULL)
+ * ------------------------------------------------------------------------------------------ */
+int b200_softmax_xent(const float* logits, int ld_logits, const int64_t* labels, int rows,
+                      int classes, float grad_scale, void* dlogits, int ld_dlogits,
+                      float* metrics, float* row_loss, void* stream);
+/* bf16-logit variant for large vocabularies (GPT-2 head): logits are overwritten in place by
+ * dlogits. */
+int b200_softmax_xent_bf16_inplace(void* logits_bf16, int ld, const int64_t* labels, int rows,
+                                   int classes, float grad_scale, float* metrics, float* row_loss,
+                                   void* stream);
+
+/* Column sums: out[N] (+)= sum_rows x[rows][ld] (bias gradients). x bf16, out fp32. */
+int b200_colsum_bf16(const void* x, int ld, int rows, int cols, float* out, int accumulate,
+                     void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * AdamW (optax.adamw semantics; reference: data_paral.py:106-108,214-217)
+ * over a flat fp32 buffer, fused with the gradient mean-scale and the bf16 working-copy cast.
+ *   step_count: device int32 holding the number of updates done so far (t = count + 1);
+ *   incremented by the kernel when bump_step != 0.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct b200_adamw_hparams {
+  float lr, beta1, beta2, eps, weight_decay, grad_scale;
+} b200_adamw_hparams;
+
+int b200_adamw(float* p, float* m, float* v, const float* g, void* p_bf16, int64_t n,
+               const b200_adamw_hparams* hp, int32_t* step_count, int bump_step, int zero_grad,
+               void* stream);
+
+/* fp32 -> bf16 cast of a flat buffer. */
+int b200_cast_f32_bf16(const float* src, void* dst, int64_t n, void* stream);
+int b200_cast_bf16_f32(const void* src, float* dst, int64_t n, void* stream);
+/* x[i] = scale * x[i] (fp32) / fill with zero */
+int b200_scale_f32(float* x, int64_t n, float scale, void* stream);
+
+/* RNG key evolution on the device: key[0] <- mix64(key[0] ^ salt_next); out_step[0] <-
+ * mix64(old ^ salt_step). Mirrors `rng, step_rng = split(state.rng)` (data_paral.py:199). */
+int b200_rng_split(uint64_t* key, uint64_t* out_step, uint64_t salt_next, uint64_t salt_step,
+                   void* stream);
+
+/* Activation / dropout as a stand-alone op (used when it cannot ride in a GEMM epilogue).
+ * y = dropout(act(x)) ; bwd: dx = dy * mask_scale * act'(x). bf16 in/out. */
+int b200_act_dropout_fwd(const void* x, void* y, int64_t rows, int cols, int ld, int act,
+                         const uint64_t* drop_key, uint64_t drop_salt, float drop_rate,
+                         void* stream);
+int b200_act_dropout_bwd(const void* x, const void* dy, void* dx, int64_t rows, int cols, int ld,
+                         int act, const uint64_t* drop_key, uint64_t drop_salt, float drop_rate,
+                         void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Transformer ops (not in the reference; required by BASELINE.json configs 2-5).
+ * ------------------------------------------------------------------------------------------ */
+/* LayerNorm over the last dim. x,y bf16 [rows][cols]; gamma/beta bf16 [cols];
+ * mean/rstd fp32 [rows] saved for backward. */
+int b200_layernorm_fwd(const void* x, const void* gamma, const void* beta, void* y, float* mean,
+                       float* rstd, int rows, int cols, float eps, void* stream);
+/* dx bf16; dgamma/dbeta fp32 [cols] accumulated (+=). */
+int b200_layernorm_bwd(const void* dy, const void* x, const void* gamma, const float* mean,
+                       const float* rstd, void* dx, float* dgamma, float* dbeta, int rows, int cols,
+                       void* stream);
+/* out[b,t,:] = wte[tok[b,t],:] + wpe[t,:]   (bf16 tables, int64 tokens) */
+int b200_embedding_fwd(const int64_t* tokens, const void* wte, const void* wpe, void* out,
+                       int batch, int seq, int dim, void* stream);
+/* dwte[tok] += dout ; dwpe[t] += dout   (fp32 grads, atomics) */
+int b200_embedding_bwd(const int64_t* tokens, const void* dout, float* dwte, float* dwpe, int batch,
+                       int seq, int dim, void* stream);
+/* Causal self-attention on tcgen05 (S = QK^T and O = PV on the tensor cores, online softmax in
+ * registers). qkv bf16 [batch][seq][3][heads][64]; out bf16 [batch][seq][heads][64];
+ * lse fp32 [batch][heads][seq]. head_dim is 64; seq must be a multiple of 128. */
+int b200_attention_fwd(const void* qkv, void* out, float* lse, int batch, int seq, int heads,
+                       void* stream);
+/* dqkv bf16 same layout as qkv. scratch: fp32 [batch][heads][seq] (row dot products D). */
+int b200_attention_bwd(const void* qkv, const void* out, const void* dout, const float* lse,
+                       void* dqkv, float* scratch_delta, int batch, int seq, int heads,
+                       void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Fused collective + optimizer kernels over NVSwitch (symmetric memory; see comm.cu).
+ * `peer_*` arrays are host arrays of `world` device pointers mapped into this process
+ * (torch symmetric memory buffer_ptrs); `mc_*` are multicast (NVLS) addresses or NULL to use
+ * the peer-pointer path; `signal_pads` are the per-rank signal pads.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct b200_comm_ctx {
+  int32_t rank, world;
+  void* const* peer_grad;   /* fp32 gradient buffers, one per rank (device-visible VAs)    */
+  void* const* peer_param;  /* fp32 master parameter buffers                                */
+  void* const* peer_bf16;   /* bf16 working-copy buffers                                    */
+  uint32_t* const* signal_pads;
+  void* mc_grad;            /* multicast VA of the gradient buffer or NULL                  */
+  void* mc_param;
+  void* mc_bf16;
+} b200_comm_ctx;
+
+/* Data-parallel step tail (reference: data_paral.py:210-217 pmean then apply_gradients):
+ * all-reduce-mean of grads[off, off+n) fused with AdamW on this rank's 1/world slice and the
+ * broadcast of the new fp32 + bf16 parameters to every rank. m/v are local slices of length
+ * n/world. One launch per bucket. */
+int b200_allreduce_adamw(const b200_comm_ctx* ctx, int64_t off, int64_t n, float* m_slice,
+                         float* v_slice, const b200_adamw_hparams* hp, int32_t* step_count,
+                         int bump_step, uint32_t epoch, int blocks, void* stream);
+/* FSDP step tail (reference: param_sharding.py:134-138 psum_scatter/axis_size, then the sharded
+ * apply_gradients at :353): reduce this rank's region [off, off+n) of every peer's full-gradient
+ * buffer, mean, AdamW on the local fp32 shard, write the bf16 shard that the next forward's
+ * all-gather GEMM reads. */
+int b200_reducescatter_adamw(const b200_comm_ctx* ctx, int64_t off, int64_t n, float* p_shard,
+                             float* m_shard, float* v_shard, void* bf16_shard,
+                             const b200_adamw_hparams* hp, int32_t* step_count, int bump_step,
+                             int zero_grad, uint32_t epoch, int blocks, void* stream);
+/* Cross-GPU barrier on the signal pads (all ranks must launch it with the same epoch). */
+int b200_signal_barrier(const b200_comm_ctx* ctx, uint32_t epoch, int slot, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200DIST_H_ */

@@ -1,0 +1,148 @@
+"""ctypes binding of ``libb200dist.so`` (C ABI in ``include/b200dist.h``).
+
+The library is loaded lazily. On a machine with a GPU a missing or stale library is an error
+(no silent fallback to PyTorch ops): the caller is told to run ``__graft_entry__.build()``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+from . import _build
+
+ABI_VERSION = 3
+
+_lib: Optional[C.CDLL] = None
+
+
+class GemmArgs(C.Structure):
+    _fields_ = [
+        ("a", C.c_void_p),
+        ("b_src", C.c_void_p * 8),
+        ("d", C.c_void_p),
+        ("m", C.c_int32), ("n", C.c_int32), ("k", C.c_int32),
+        ("lda", C.c_int32), ("ldb", C.c_int32), ("ldd", C.c_int32),
+        ("a_mn", C.c_int32), ("b_mn", C.c_int32),
+        ("b_nsrc", C.c_int32), ("b_shard_mode", C.c_int32), ("b_shard_len", C.c_int32),
+        ("b_rot", C.c_int32),
+        ("d_fp32", C.c_int32),
+        ("accumulate", C.c_int32),
+        ("alpha", C.c_float),
+        ("bias", C.c_void_p),
+        ("pre", C.c_void_p),
+        ("ldpre", C.c_int32),
+        ("act", C.c_int32),
+        ("resid", C.c_void_p),
+        ("ldres", C.c_int32),
+        ("bwd", C.c_int32),
+        ("aux", C.c_void_p),
+        ("ldaux", C.c_int32),
+        ("drop_key", C.c_void_p),
+        ("drop_salt", C.c_uint64),
+        ("drop_rate", C.c_float),
+        ("block_n", C.c_int32),
+    ]
+
+
+class AdamWHParams(C.Structure):
+    _fields_ = [
+        ("lr", C.c_float), ("beta1", C.c_float), ("beta2", C.c_float),
+        ("eps", C.c_float), ("weight_decay", C.c_float), ("grad_scale", C.c_float),
+    ]
+
+
+class CommCtx(C.Structure):
+    _fields_ = [
+        ("rank", C.c_int32), ("world", C.c_int32),
+        ("peer_grad", C.POINTER(C.c_void_p)),
+        ("peer_param", C.POINTER(C.c_void_p)),
+        ("peer_bf16", C.POINTER(C.c_void_p)),
+        ("signal_pads", C.POINTER(C.c_void_p)),
+        ("mc_grad", C.c_void_p),
+        ("mc_param", C.c_void_p),
+        ("mc_bf16", C.c_void_p),
+    ]
+
+
+class B200Error(RuntimeError):
+    pass
+
+
+def _declare(lib: C.CDLL) -> None:
+    vp, i32, i64, f32, u64 = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_uint64
+    lib.b200_last_error.restype = C.c_char_p
+    lib.b200_abi_version.restype = C.c_int
+    lib.b200_launch_count.restype = C.c_longlong
+    lib.b200_reset_launch_count.restype = None
+    sigs = {
+        "b200_gemm_bf16": [C.POINTER(GemmArgs), vp],
+        "b200_softmax_xent": [vp, i32, vp, i32, i32, f32, vp, i32, vp, vp, vp],
+        "b200_softmax_xent_bf16_inplace": [vp, i32, vp, i32, i32, f32, vp, vp, vp],
+        "b200_colsum_bf16": [vp, i32, i32, i32, vp, i32, vp],
+        "b200_adamw": [vp, vp, vp, vp, vp, i64, C.POINTER(AdamWHParams), vp, i32, i32, vp],
+        "b200_cast_f32_bf16": [vp, vp, i64, vp],
+        "b200_cast_bf16_f32": [vp, vp, i64, vp],
+        "b200_scale_f32": [vp, i64, f32, vp],
+        "b200_rng_split": [vp, vp, u64, u64, vp],
+        "b200_act_dropout_fwd": [vp, vp, i64, i32, i32, i32, vp, u64, f32, vp],
+        "b200_act_dropout_bwd": [vp, vp, vp, i64, i32, i32, i32, vp, u64, f32, vp],
+        "b200_layernorm_fwd": [vp, vp, vp, vp, vp, vp, i32, i32, f32, vp],
+        "b200_layernorm_bwd": [vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, vp],
+        "b200_embedding_fwd": [vp, vp, vp, vp, i32, i32, i32, vp],
+        "b200_embedding_bwd": [vp, vp, vp, vp, i32, i32, i32, vp],
+        "b200_attention_fwd": [vp, vp, vp, i32, i32, i32, vp],
+        "b200_attention_bwd": [vp, vp, vp, vp, vp, vp, i32, i32, i32, vp],
+        "b200_allreduce_adamw": [C.POINTER(CommCtx), i64, i64, vp, vp, C.POINTER(AdamWHParams), vp,
+                                 i32, C.c_uint32, i32, vp],
+        "b200_reducescatter_adamw": [C.POINTER(CommCtx), i64, i64, vp, vp, vp, vp,
+                                     C.POINTER(AdamWHParams), vp, i32, i32, C.c_uint32, i32, vp],
+        "b200_signal_barrier": [C.POINTER(CommCtx), C.c_uint32, i32, vp],
+    }
+    for name, argtypes in sigs.items():
+        fn = getattr(lib, name, None)
+        if fn is None:  # entry point not built yet
+            continue
+        fn.argtypes = argtypes
+        fn.restype = C.c_int
+
+
+def lib() -> C.CDLL:
+    """Returns the loaded kernel library, building it first if the sources are newer."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = _build.LIB_PATH
+    if not path.exists():
+        raise B200Error(
+            f"{path} is missing: build the CUDA library first "
+            "(python -c 'import __graft_entry__ as g; g.build()')"
+        )
+    handle = C.CDLL(str(path), mode=C.RTLD_GLOBAL)
+    _declare(handle)
+    got = handle.b200_abi_version()
+    if got != ABI_VERSION:
+        raise B200Error(f"{path} has ABI version {got}, expected {ABI_VERSION}: rebuild it")
+    _lib = handle
+    return handle
+
+
+def available() -> bool:
+    try:
+        lib()
+        return True
+    except (OSError, B200Error):
+        return False
+
+
+def check(rc: int) -> None:
+    if rc != 0:
+        msg = lib().b200_last_error()
+        raise B200Error(msg.decode("utf-8", "replace") if msg else f"b200 error {rc}")
+
+
+def launch_count() -> int:
+    return int(lib().b200_launch_count())
+
+
+def reset_launch_count() -> None:
+    lib().b200_reset_launch_count()
