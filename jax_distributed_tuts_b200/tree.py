@@ -109,6 +109,9 @@ class PartitionSpec(tuple):
     def __new__(cls, *names):
         return super().__new__(cls, names)
 
+    def __reduce__(self):
+        return (PartitionSpec, tuple(self))
+
     def __repr__(self):
         return "P(" + ", ".join(repr(n) for n in self) + ")"
 

@@ -1,0 +1,116 @@
+"""Worker functions for the multi-process (gloo) tests; must be importable for mp spawn."""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+import torch
+
+from jax_distributed_tuts_b200 import rng
+from jax_distributed_tuts_b200.comm import collectives as C
+from jax_distributed_tuts_b200.config import dp_config, fsdp_config
+from jax_distributed_tuts_b200.mesh import Mesh
+from jax_distributed_tuts_b200.models.mlp import Classifier
+from jax_distributed_tuts_b200.parallel import dp, fsdp
+from jax_distributed_tuts_b200.state import Batch
+from jax_distributed_tuts_b200.tree import get_partition_spec, is_partitioned, tree_leaves, unbox
+
+
+def make_batch(cfg):
+    key = rng.PRNGKey(cfg.seed)
+    model_rng, data_rng, label_rng = rng.split(key, 3)
+    inputs = torch.randn(cfg.data.batch_size, cfg.data.input_size, generator=rng.uniform_generator(data_rng))
+    labels = torch.randint(0, cfg.data.num_classes, (cfg.data.batch_size,),
+                           generator=rng.uniform_generator(label_rng))
+    return model_rng, Batch(inputs, labels)
+
+
+def collectives_worker(rank, world):
+    mesh = Mesh((world,), ("data",))
+    out = {}
+    with mesh:
+        x = torch.arange(4, dtype=torch.float32) + rank
+        out["psum"] = C.psum(x, "data")
+        out["pmean"] = C.pmean(x, "data")
+        out["idx"] = C.axis_index("data")
+        out["size"] = C.axis_size("data")
+        sh = torch.full((2, 3), float(rank))
+        out["ag0"] = C.all_gather(sh, "data", axis=0)
+        out["ag1"] = C.all_gather(sh, "data", axis=1)
+        full = torch.arange(world * 2 * 3, dtype=torch.float32).reshape(world * 2, 3) * (rank + 1)
+        out["rs0"] = C.psum_scatter(full, "data", scatter_dimension=0)
+        full1 = torch.arange(2 * world * 3, dtype=torch.float32).reshape(2, world * 3) * (rank + 1)
+        out["rs1"] = C.psum_scatter(full1, "data", scatter_dimension=1)
+        out["perm"] = C.ppermute(torch.full((2,), float(rank)), "data", [(i, (i + 1) % world) for i in range(world)])
+        out["perm_open"] = C.ppermute(torch.full((2,), float(rank + 1)), "data", [(i, i + 1) for i in range(world - 1)])
+        out["scalar"] = C.psum(3, "data")
+    return out
+
+
+def mesh2d_worker(rank, world):
+    mesh = Mesh((2, world // 2), ("data", "fsdp"))
+    with mesh:
+        x = torch.tensor([float(rank)])
+        return {"coords": mesh.coords, "sum_data": C.psum(x, "data"), "sum_fsdp": C.psum(x, "fsdp"),
+                "sum_both": C.psum(x, ("data", "fsdp")), "idx_both": mesh.axis_index(("data", "fsdp"))}
+
+
+def dp_worker(rank, world, steps, dropout):
+    cfg = dp_config()
+    cfg.model.dropout_rate = dropout
+    mesh = Mesh((world,), ("data",))
+    model = Classifier(cfg.model)
+    model_rng, batch = make_batch(cfg)
+    with mesh:
+        state = dp.init_dp(model_rng, batch.inputs, model)
+        step = dp.make_train_step_dp(mesh, num_minibatches=cfg.optimizer.num_minibatches)
+        local = dp.shard_batch(batch)
+        metrics = None
+        for _ in range(steps):
+            state, metrics = step(state, metrics, local)
+    return {"params": state.params, "metrics": metrics, "step": state.step}
+
+
+def fsdp_worker(rank, world, steps, lr, min_weight_size=16):
+    cfg = fsdp_config()
+    cfg.model.dropout_rate = 0.0
+    cfg.model.min_weight_size = min_weight_size
+    mesh = Mesh((world,), ("data",))
+    wrap = lambda m: fsdp.shard_module_params(m, axis_name="data", min_weight_size=cfg.model.min_weight_size)
+    model = Classifier(cfg.model, dense_wrapper=wrap)
+    model_rng, batch = make_batch(cfg)
+    with mesh:
+        state = fsdp.init_model(model_rng, batch.inputs, model, learning_rate=lr)
+        specs = get_partition_spec(state)
+        step = fsdp.make_train_step_fsdp(mesh, num_minibatches=cfg.num_minibatches)
+        local = dp.shard_batch(batch)
+        metrics = None
+        for _ in range(steps):
+            state, metrics = step(state, metrics, local)
+        full = fsdp.unshard_params(state.params)
+        local_shapes = {k: {kk: tuple((vv.value if is_partitioned(vv) else vv).shape) for kk, vv in v.items()}
+                        for k, v in state.params.items()}
+        names = {k: {kk: (vv.names if is_partitioned(vv) else None) for kk, vv in v.items()}
+                 for k, v in state.params.items()}
+        mu_names = {k: {kk: (vv.names if is_partitioned(vv) else None) for kk, vv in v.items()}
+                    for k, v in state.opt_state[0].mu.items()}
+    return {"params": full, "metrics": metrics, "local_shapes": local_shapes, "names": names,
+            "mu_names": mu_names, "spec_params": specs.params}
+
+
+def dp_lr_worker(rank, world, steps, lr):
+    """DP with the FSDP config (same seed/lr) for the FSDP == DP equivalence test."""
+    from jax_distributed_tuts_b200.optim import adamw
+    cfg = fsdp_config()
+    cfg.model.dropout_rate = 0.0
+    mesh = Mesh((world,), ("data",))
+    model = Classifier(cfg.model)
+    model_rng, batch = make_batch(cfg)
+    with mesh:
+        state = dp.init_dp(model_rng, batch.inputs, model, optimizer=adamw(lr))
+        step = dp.make_train_step_dp(mesh, num_minibatches=cfg.num_minibatches)
+        local = dp.shard_batch(batch)
+        metrics = None
+        for _ in range(steps):
+            state, metrics = step(state, metrics, local)
+    return {"params": state.params, "metrics": metrics}
