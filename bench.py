@@ -1,0 +1,241 @@
+"""Headline benchmark: train samples/sec of the data-parallel train step (BASELINE.json metric
+"train samples/sec (device-timed, max over ranks) at 1/2/4/8 B200"), on the reference's own
+workload by default: MLP 784->512->10 (SiLU, dropout 0.1), bf16 compute / fp32 master params,
+AdamW, 16 rows per device in 4 minibatches (global batch 128 on 8 devices; data_paral.py:39-72).
+
+    python bench.py --gpus N --steps K --warmup W            # N = 1: plain python
+    python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N --steps K --warmup W
+
+Prints ONE JSON line on rank 0. ``value`` is device-timed (CUDA events around every step, L2
+flushed between steps outside the events, sum over K steps, max over ranks); ``e2e`` is the
+same step through the public API with the batch copied from pinned host memory and the loss
+read back every step, wall-clock, max over ranks.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+
+CONFIGS = {
+    # name: (model, per-gpu batch, minibatches, hidden, input, classes)
+    "mlp_dp": dict(model="mlp_784_512_10", per_gpu_batch=16, minibatches=4, hidden=512, inp=784, classes=10,
+                   mode="dp"),
+    "mlp_dp_large": dict(model="mlp_784_8192_10", per_gpu_batch=32768, minibatches=4, hidden=8192, inp=784,
+                         classes=10, mode="dp"),
+    "mlp_fsdp": dict(model="mlp_784_512_10", per_gpu_batch=16, minibatches=4, hidden=512, inp=784, classes=10,
+                     mode="fsdp"),
+}
+
+
+def reference_arm(args) -> None:
+    """The reference cannot be installed or run on this image (recorded in DESIGN.md):
+    `pip install --no-index ... /root/reference` fails (no setup.py/pyproject.toml: it is four
+    loose scripts) and its imports (jax, flax, optax, ml_collections, absl, termcolor) are not
+    available offline."""
+    why = "reference is 4 loose JAX scripts: not pip-installable (no setup.py/pyproject) and jax/flax/optax are not in the offline image"
+    ref_dir = os.path.join(os.path.dirname(os.path.abspath(__file__)), "baseline", "_ref")
+    try:
+        sys.path.insert(0, ref_dir)
+        import jax  # noqa: F401
+        why = "jax import succeeded unexpectedly but the reference scripts raise NameError at import (util.py:32 uses os without importing it)"
+    except Exception:  # noqa: BLE001
+        pass
+    print(json.dumps({"impl": "reference", "unavailable": why}))
+
+
+class ClockSampler:
+    """Samples SM clock / throttle reasons with nvidia-smi while the timed region runs."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                       "-lms", "100", "-i", str(gpu_index)], stdout=self.f, stderr=subprocess.DEVNULL)
+        except Exception:  # noqa: BLE001
+            self.p = None
+
+    def stop(self) -> dict:
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.p is None:
+            return out
+        time.sleep(0.15)
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:  # noqa: BLE001
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        clocks, reasons, mx = [], set(), None
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.f.read().splitlines():
+            parts = [x.strip() for x in line.split(",")]
+            if len(parts) < 9:
+                continue
+            try:
+                clocks.append(float(parts[1]))
+                mx = float(parts[2])
+            except ValueError:
+                continue
+            for nm, val in zip(names, parts[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(nm)
+        try:
+            os.unlink(self.f.name)
+        except OSError:
+            pass
+        if clocks:
+            clocks.sort()
+            # median over the upper half = clocks under load (idle samples sit at the bottom)
+            upper = clocks[len(clocks) // 2:]
+            out.update(sm_mhz=upper[len(upper) // 2], sm_max_mhz=mx, reasons=sorted(reasons), samples=len(clocks))
+        return out
+
+
+def main() -> None:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default="mlp_dp", choices=sorted(CONFIGS))
+    ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        if int(os.environ.get("RANK", "0")) == 0:
+            reference_arm(args)
+        return
+    args.warmup = max(args.warmup, 3)
+
+    import torch
+    import torch.distributed as dist
+
+    from jax_distributed_tuts_b200 import rng
+    from jax_distributed_tuts_b200.config import dp_config
+    from jax_distributed_tuts_b200.engine import MLPEngine
+    from jax_distributed_tuts_b200.launch import init_from_env
+    from jax_distributed_tuts_b200.mesh import Mesh
+    from jax_distributed_tuts_b200.models.mlp import Classifier
+    from jax_distributed_tuts_b200.ops import _lib
+    from jax_distributed_tuts_b200.parallel import dp
+    from jax_distributed_tuts_b200.state import Batch
+
+    rank, world, device = init_from_env()
+    assert device.type == "cuda", "bench.py needs a GPU"
+    assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run"
+    c = CONFIGS[args.config]
+    cfg = dp_config()
+    cfg.model.hidden_size = c["hidden"]
+    B = c["per_gpu_batch"]
+    mesh = Mesh((world,), ("data",))
+    model = Classifier(cfg.model)
+    key = rng.PRNGKey(cfg.seed)
+    model_rng, data_rng, label_rng = rng.split(key, 3)
+    # synthetic data of the reference's shape; a distinct batch shard per rank, fixed across steps
+    # like the reference's single synthetic batch (data_paral.py:113-124)
+    gx = rng.uniform_generator(rng.fold_in(data_rng, rank))
+    x = torch.randn(B, c["inp"], generator=gx).pin_memory()
+    y = torch.randint(0, c["classes"], (B,), generator=rng.uniform_generator(rng.fold_in(label_rng, rank))).pin_memory()
+    with mesh:
+        init_state = dp.init_dp(model_rng, x[:4], model)
+        eng = MLPEngine(cfg.model, mesh, mode=c["mode"], batch_per_rank=B, lr=cfg.optimizer.learning_rate,
+                        num_minibatches=c["minibatches"], init_params=init_state.params, input_size=c["inp"],
+                        use_graph=not args.no_graph,
+                        min_weight_size=16 if c["mode"] == "fsdp" else 2 ** 18)
+        state = eng.make_state(model, init_state.rng)
+        step = dp.make_train_step_dp(mesh)
+        batch = Batch(x, y)
+
+        def sync():
+            torch.cuda.synchronize()
+            if world > 1:
+                dist.barrier()
+                torch.cuda.synchronize()
+
+        # ---- warm-up (untimed): includes the eager step and the graph capture ----
+        metrics = None
+        for _ in range(args.warmup):
+            state, metrics = step(state, metrics, batch)
+        sync()
+        flush = torch.empty(256 << 20, dtype=torch.uint8, device=device)  # > 126 MB L2
+
+        # ---- device-timed region: events around each step, L2 flushed in between ----
+        sampler = ClockSampler(torch.cuda.current_device()) if rank == 0 else None
+        evs = []
+        sync()
+        for _ in range(args.steps):
+            flush.zero_()
+            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            eng._load_batch(batch)      # H2D of the step's inputs is outside the events (kernel-only number)
+            s.record()
+            eng._run_step()
+            e.record()
+            evs.append((s, e))
+        sync()
+        dev_ms = sum(s.elapsed_time(e) for s, e in evs)
+        clocks = sampler.stop() if sampler else None
+
+        # ---- end-to-end region: public API, pinned H2D every step, loss read back every step ----
+        e2e_ms = None
+        if not args.no_e2e:
+            metrics = None
+            sync()
+            t0 = time.perf_counter()
+            for _ in range(args.steps):
+                state, metrics = step(state, None, batch)
+                _ = metrics["loss"][0].item()
+            sync()
+            e2e_ms = (time.perf_counter() - t0) * 1e3
+
+        t = torch.tensor([dev_ms, e2e_ms or 0.0], dtype=torch.float64, device=device)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dev_ms, e2e_max = t[0].item(), t[1].item()
+        final_loss = metrics["loss"][0].item() / metrics["loss"][1] if metrics else None
+
+    if rank == 0:
+        gb = B * world
+        ms_per_step = dev_ms / args.steps
+        out = {
+            "metric": "train samples/sec (device-timed, max over ranks)",
+            "value": gb / (ms_per_step * 1e-3),
+            "unit": "samples/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_per_step,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "bf16", "data": "synthetic (random-normal inputs, uniform labels, random-init weights)",
+            "impl": "ours",
+            "config": {"model": c["model"], "global_batch": gb, "per_gpu_batch": B, "minibatches": c["minibatches"],
+                       "seq_len": None, "parallelism": f"{c['mode']}{world}", "optimizer": "adamw",
+                       "name": args.config, "l2": "flushed between timed steps (256 MiB write)",
+                       "cuda_graph": not args.no_graph, "comm": eng.arena.backend},
+            "gpu_launches": int(getattr(eng, "launches_per_step", 0)) * args.steps,
+            "launches_per_step": int(getattr(eng, "launches_per_step", 0)),
+            "clocks": clocks,
+            "final_loss": final_loss,
+        }
+        if e2e_ms is not None:
+            out["e2e"] = {"value": gb / (e2e_max / args.steps * 1e-3), "unit": "samples/s",
+                          "ms_per_step": e2e_max / args.steps,
+                          "h2d_bytes_per_step": int(x.numel() * 4 + y.numel() * 8), "d2h_bytes_per_step": 4}
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -16,7 +16,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 3
+#define B200_ABI_VERSION 4
 
 const char* b200_last_error(void);
 int b200_abi_version(void);
@@ -165,39 +165,68 @@ int b200_attention_bwd(const void* qkv, const void* out, const void* dout, const
                        void* stream);
 
 /* ------------------------------------------------------------------------------------------
- * Fused collective + optimizer kernels over NVSwitch (symmetric memory; see comm.cu).
- * `peer_*` arrays are host arrays of `world` device pointers mapped into this process
- * (torch symmetric memory buffer_ptrs); `mc_*` are multicast (NVLS) addresses or NULL to use
- * the peer-pointer path; `signal_pads` are the per-rank signal pads.
+ * Fused collective + optimizer kernel over NVSwitch (csrc/comm.cu).
+ *
+ * All ranks launch the same kernel on buffers that live in symmetric memory (same size on every
+ * rank, every rank's copy mapped into every process; a multicast/NVLS address when the fabric
+ * has one). One launch does, for a list of segments of the flat gradient buffer:
+ *
+ *   start barrier  (all ranks have finished writing their local gradients)
+ *   g  = sum over ranks of grad[seg]            multimem.ld_reduce (in-switch) or P2P loads
+ *   g *= grad_scale                             (mean over devices and minibatches)
+ *   AdamW on this rank's fp32 master / m / v for the segment
+ *   publish: new fp32 + bf16 parameters         multimem.st / P2P stores to every rank  (DP)
+ *            or bf16 shard written locally, to be pulled by the all-gather GEMM        (FSDP)
+ *   metrics psum (optional, through the signal buffer)
+ *   end barrier    (all ranks are done reading my gradients / writing my parameters)
+ *
+ * Reference semantics: DP  = pmean(grads) then replicated apply_gradients
+ *                            (data_paral.py:210-217);
+ *                      FSDP = psum_scatter(g)/axis_size into the shard, sharded apply_gradients
+ *                            (param_sharding.py:134-138,353).
  * ------------------------------------------------------------------------------------------ */
+typedef struct b200_seg {
+  int64_t src_off;   /* element offset of the segment in every rank's gradient buffer        */
+  int64_t src_pitch; /* elements between consecutive rows (== row_len when contiguous)       */
+  int64_t dst_off;   /* broadcast mode: element offset in every rank's param buffers         */
+  int64_t loc_off;   /* element offset in this rank's local m / v (/ p_shard / bf16_shard)   */
+  int32_t rows, row_len;
+} b200_seg;
+
 typedef struct b200_comm_ctx {
   int32_t rank, world;
-  void* const* peer_grad;   /* fp32 gradient buffers, one per rank (device-visible VAs)    */
-  void* const* peer_param;  /* fp32 master parameter buffers                                */
-  void* const* peer_bf16;   /* bf16 working-copy buffers                                    */
-  uint32_t* const* signal_pads;
-  void* mc_grad;            /* multicast VA of the gradient buffer or NULL                  */
+  void* const* peer_grad;      /* host array[world]: fp32 gradient buffers                   */
+  void* const* peer_param;     /* host array[world]: fp32 master buffers (broadcast mode)    */
+  void* const* peer_bf16;      /* host array[world]: bf16 working copies (broadcast mode)    */
+  void* const* peer_signal;    /* host array[world]: uint32 signal buffers (B200_SIGNAL_WORDS)*/
+  void* mc_grad;               /* multicast addresses of the same buffers, or NULL           */
   void* mc_param;
   void* mc_bf16;
 } b200_comm_ctx;
 
-/* Data-parallel step tail (reference: data_paral.py:210-217 pmean then apply_gradients):
- * all-reduce-mean of grads[off, off+n) fused with AdamW on this rank's 1/world slice and the
- * broadcast of the new fp32 + bf16 parameters to every rank. m/v are local slices of length
- * n/world. One launch per bucket. */
-int b200_allreduce_adamw(const b200_comm_ctx* ctx, int64_t off, int64_t n, float* m_slice,
-                         float* v_slice, const b200_adamw_hparams* hp, int32_t* step_count,
-                         int bump_step, uint32_t epoch, int blocks, void* stream);
-/* FSDP step tail (reference: param_sharding.py:134-138 psum_scatter/axis_size, then the sharded
- * apply_gradients at :353): reduce this rank's region [off, off+n) of every peer's full-gradient
- * buffer, mean, AdamW on the local fp32 shard, write the bf16 shard that the next forward's
- * all-gather GEMM reads. */
-int b200_reducescatter_adamw(const b200_comm_ctx* ctx, int64_t off, int64_t n, float* p_shard,
-                             float* m_shard, float* v_shard, void* bf16_shard,
-                             const b200_adamw_hparams* hp, int32_t* step_count, int bump_step,
-                             int zero_grad, uint32_t epoch, int blocks, void* stream);
-/* Cross-GPU barrier on the signal pads (all ranks must launch it with the same epoch). */
-int b200_signal_barrier(const b200_comm_ctx* ctx, uint32_t epoch, int slot, void* stream);
+#define B200_SIGNAL_WORDS 8192
+#define B200_COMM_MAX_BLOCKS 64
+
+/* broadcast = 1 (DP):   p/bf16 written to all ranks at dst_off; m,v local at loc_off.
+ * broadcast = 0 (FSDP): p_local/bf16_local/m/v are this rank's shard buffers at loc_off.
+ * segs: device array of nseg segments. step_metrics / metrics_acc: optional fp32[nmetrics]
+ * (nmetrics <= 8): metrics_acc += sum over ranks of step_metrics. */
+int b200_fused_reduce_adamw(const b200_comm_ctx* ctx, const b200_seg* segs_dev, int nseg,
+                            int broadcast, float* p_local, void* bf16_local, float* m, float* v,
+                            const b200_adamw_hparams* hp, int32_t* step_count, int bump_step,
+                            const float* step_metrics, float* metrics_acc, int nmetrics,
+                            int blocks, void* stream);
+/* All-gather of small tensors through peer loads (no collective launch): for every segment and
+ * every rank p, dst[dst_off + p*nbytes, +nbytes) = peer_base[p][src_off, +nbytes).
+ * The FSDP engine uses it for sharded biases; the big weights are never gathered (the GEMM's
+ * TMA producer reads the shards in place). Reference: all_gather at param_sharding.py:140. */
+typedef struct b200_gather_seg {
+  int64_t src_off, dst_off, nbytes;
+} b200_gather_seg;
+int b200_peer_gather(void* const* peer_base, int world, const b200_gather_seg* segs_dev, int nseg,
+                     void* dst, int blocks, void* stream);
+/* Cross-GPU barrier on the signal buffers (every rank launches it). */
+int b200_signal_barrier(const b200_comm_ctx* ctx, void* stream);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,2 @@
+from .base import FlatLayout, FusedEngine, SymmetricArena  # noqa: F401
+from .mlp import MLPEngine  # noqa: F401

@@ -10,7 +10,7 @@ from typing import Optional
 
 from . import _build
 
-ABI_VERSION = 3
+ABI_VERSION = 4
 
 _lib: Optional[C.CDLL] = None
 
@@ -57,11 +57,26 @@ class CommCtx(C.Structure):
         ("peer_grad", C.POINTER(C.c_void_p)),
         ("peer_param", C.POINTER(C.c_void_p)),
         ("peer_bf16", C.POINTER(C.c_void_p)),
-        ("signal_pads", C.POINTER(C.c_void_p)),
+        ("peer_signal", C.POINTER(C.c_void_p)),
         ("mc_grad", C.c_void_p),
         ("mc_param", C.c_void_p),
         ("mc_bf16", C.c_void_p),
     ]
+
+
+class Seg(C.Structure):
+    _fields_ = [
+        ("src_off", C.c_int64), ("src_pitch", C.c_int64), ("dst_off", C.c_int64), ("loc_off", C.c_int64),
+        ("rows", C.c_int32), ("row_len", C.c_int32),
+    ]
+
+
+class GatherSeg(C.Structure):
+    _fields_ = [("src_off", C.c_int64), ("dst_off", C.c_int64), ("nbytes", C.c_int64)]
+
+
+SIGNAL_WORDS = 8192
+COMM_MAX_BLOCKS = 64
 
 
 class B200Error(RuntimeError):
@@ -92,11 +107,10 @@ def _declare(lib: C.CDLL) -> None:
         "b200_embedding_bwd": [vp, vp, vp, vp, i32, i32, i32, vp],
         "b200_attention_fwd": [vp, vp, vp, i32, i32, i32, vp],
         "b200_attention_bwd": [vp, vp, vp, vp, vp, vp, i32, i32, i32, vp],
-        "b200_allreduce_adamw": [C.POINTER(CommCtx), i64, i64, vp, vp, C.POINTER(AdamWHParams), vp,
-                                 i32, C.c_uint32, i32, vp],
-        "b200_reducescatter_adamw": [C.POINTER(CommCtx), i64, i64, vp, vp, vp, vp,
-                                     C.POINTER(AdamWHParams), vp, i32, i32, C.c_uint32, i32, vp],
-        "b200_signal_barrier": [C.POINTER(CommCtx), C.c_uint32, i32, vp],
+        "b200_fused_reduce_adamw": [C.POINTER(CommCtx), vp, i32, i32, vp, vp, vp, vp,
+                                    C.POINTER(AdamWHParams), vp, i32, vp, vp, i32, i32, vp],
+        "b200_signal_barrier": [C.POINTER(CommCtx), vp],
+        "b200_peer_gather": [C.POINTER(C.c_void_p), i32, vp, i32, vp, i32, vp],
     }
     for name, argtypes in sigs.items():
         fn = getattr(lib, name, None)

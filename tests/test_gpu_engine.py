@@ -1,0 +1,119 @@
+"""GPU tier: generic autograd path (our kernels behind torch.autograd) vs the CPU oracle, and
+the fused CUDA-graph engine vs the generic path, on the reference's MLP."""
+import pytest
+import torch
+
+from jax_distributed_tuts_b200 import rng
+from jax_distributed_tuts_b200.config import dp_config
+from jax_distributed_tuts_b200.mesh import Mesh
+from jax_distributed_tuts_b200.models.mlp import Classifier
+from jax_distributed_tuts_b200.parallel import dp
+from jax_distributed_tuts_b200.state import Batch
+from jax_distributed_tuts_b200.tree import tree_leaves, tree_map
+
+pytestmark = pytest.mark.gpu
+
+
+def _setup(device, batch=64, dropout=0.1):
+    cfg = dp_config()
+    cfg.model.dropout_rate = dropout
+    mesh = Mesh((1,), ("data",), device=torch.device(device))
+    model = Classifier(cfg.model)
+    key = rng.PRNGKey(cfg.seed)
+    model_rng, data_rng, label_rng = rng.split(key, 3)
+    x = torch.randn(batch, 784, generator=rng.uniform_generator(data_rng))
+    y = torch.randint(0, 10, (batch,), generator=rng.uniform_generator(label_rng))
+    with mesh:
+        state = dp.init_dp(model_rng, x, model)      # CPU init: identical values for every path
+    return cfg, mesh, model, state, Batch(x, y)
+
+
+def _to(state, device):
+    return state.replace(params=tree_map(lambda t: t.to(device), state.params),
+                         opt_state=state.tx.init(tree_map(lambda t: t.to(device), state.params)),
+                         rng=state.rng.to(device))
+
+
+def _mean_close(a, b, lr, steps):
+    d = (a.float().cpu() - b.float().cpu()).abs()
+    return d.max() <= 2.2 * lr * steps and d.mean() <= 0.06 * lr * steps
+
+
+def test_generic_gpu_path_matches_cpu_oracle_with_dropout():
+    cfg, mesh, model, state, batch = _setup("cpu")
+    steps, lr = 3, cfg.optimizer.learning_rate
+    step = dp.make_train_step_dp(mesh, num_minibatches=4)
+    s_cpu, m_cpu = state, None
+    for _ in range(steps):
+        s_cpu, m_cpu = step(s_cpu, m_cpu, batch)
+    mesh_g = Mesh((1,), ("data",), device=torch.device("cuda"))
+    step_g = dp.make_train_step_dp(mesh_g, num_minibatches=4)
+    s_gpu, m_gpu = _to(state, "cuda"), None
+    bg = batch.to("cuda")
+    for _ in range(steps):
+        s_gpu, m_gpu = step_g(s_gpu, m_gpu, bg)
+    for a, b in zip(tree_leaves(s_cpu.params), tree_leaves(s_gpu.params)):
+        assert _mean_close(a, b, lr, steps), (a.cpu() - b.cpu()).abs().mean()
+    l_cpu = float(m_cpu["loss"][0]) / m_cpu["loss"][1]
+    l_gpu = float(m_gpu["loss"][0]) / m_gpu["loss"][1]
+    assert abs(l_cpu - l_gpu) < 2e-2, (l_cpu, l_gpu)
+    assert abs(float(m_cpu["accuracy"][0]) - float(m_gpu["accuracy"][0])) <= 3
+
+
+@pytest.mark.parametrize("use_graph", [False, True])
+def test_fused_engine_matches_generic_path(use_graph):
+    from jax_distributed_tuts_b200.engine import MLPEngine
+    cfg, _, model, state, batch = _setup("cpu")
+    steps, lr = 4, cfg.optimizer.learning_rate
+    mesh_g = Mesh((1,), ("data",), device=torch.device("cuda"))
+    step = dp.make_train_step_dp(mesh_g, num_minibatches=4)
+    s_gen, m_gen = _to(state, "cuda"), None
+    bg = batch.to("cuda")
+    for _ in range(steps):
+        s_gen, m_gen = step(s_gen, m_gen, bg)
+    with mesh_g:
+        eng = MLPEngine(cfg.model, mesh_g, mode="dp", batch_per_rank=batch.inputs.shape[0], lr=lr,
+                        num_minibatches=4, init_params=state.params, use_graph=use_graph)
+        s_eng = eng.make_state(model, state.rng)
+        m_eng = None
+        pinned = Batch(batch.inputs.pin_memory(), batch.labels.pin_memory())
+        for _ in range(steps):
+            s_eng, m_eng = step(s_eng, m_eng, pinned)
+    torch.cuda.synchronize()
+    p_eng = eng.params_tree()
+    for k in ("input_dense", "output_dense"):
+        for kk in ("kernel", "bias"):
+            assert _mean_close(p_eng[k][kk], s_gen.params[k][kk], lr, steps), (k, kk)
+    l_gen = float(m_gen["loss"][0]) / m_gen["loss"][1]
+    l_eng = float(m_eng["loss"][0]) / m_eng["loss"][1]
+    assert m_eng["loss"][1] == m_gen["loss"][1] == steps * batch.inputs.shape[0]
+    assert abs(l_gen - l_eng) < 2e-2, (l_gen, l_eng)
+    assert s_eng.step == steps and int(eng.step_count.item()) == steps
+    assert eng.launches_per_step > 0
+
+
+def test_engine_fsdp_single_rank_matches_dp_engine():
+    from jax_distributed_tuts_b200.engine import MLPEngine
+    cfg, _, model, state, batch = _setup("cpu", dropout=0.1)
+    mesh_g = Mesh((1,), ("data",), device=torch.device("cuda"))
+    res = {}
+    with mesh_g:
+        for mode in ("dp", "fsdp"):
+            eng = MLPEngine(cfg.model, mesh_g, mode=mode, batch_per_rank=64, lr=1e-3, num_minibatches=4,
+                            init_params=state.params, use_graph=False, min_weight_size=16)
+            st = eng.make_state(model, state.rng)
+            m = None
+            for _ in range(3):
+                st, m = eng.train_step(st, m, batch)
+            torch.cuda.synchronize()
+            res[mode] = (eng.params_tree(), float(m["loss"][0]))
+    for k in ("input_dense", "output_dense"):
+        for kk in ("kernel", "bias"):
+            a, b = res["dp"][0][k][kk], res["fsdp"][0][k][kk]
+            assert torch.allclose(a.float(), b.float().reshape(a.shape), atol=1e-6), (k, kk)
+    assert abs(res["dp"][1] - res["fsdp"][1]) < 1e-4
+
+
+def test_smoke_entry_point():
+    import __graft_entry__ as g
+    g.smoke()

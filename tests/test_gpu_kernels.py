@@ -1,0 +1,25 @@
+"""Single-GPU kernel tier: every sm_100a kernel against a plain PyTorch fp32 reference.
+The case lists live in tools/gpu_check_kernels.py (also runnable stand-alone on a GPU box)."""
+import pytest
+
+from tools import gpu_check_kernels as G
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("group", ["gemm_kmajor", "gemm_mnmajor", "gemm_epilogue", "gemm_sharded", "elementwise"])
+def test_kernel_group(group):
+    import torch
+    assert getattr(G, "group_" + group)()
+    torch.cuda.synchronize()
+
+
+def test_library_is_the_native_one():
+    from jax_distributed_tuts_b200.ops import _lib
+    before = _lib.launch_count()
+    import torch
+    from jax_distributed_tuts_b200.ops import kernels as K
+    x = torch.ones(1024, device="cuda")
+    K.scale_(x, 2.0)
+    torch.cuda.synchronize()
+    assert _lib.launch_count() == before + 1 and x[0].item() == 2.0
