@@ -258,7 +258,7 @@ __device__ __forceinline__ float gelu_grad_f(float x) {
 }
 
 // ---- counter-based dropout RNG ----
-// seed = mix64(*key ^ mix64(salt)); one 32-bit hash per element pair gives two 16-bit uniforms.
+// seed = mix64(*key ^ salt_word) with salt_word = mix64(salt) computed on the host; one 32-bit hash per element pair gives two 16-bit uniforms.
 __host__ __device__ __forceinline__ uint64_t mix64(uint64_t z) {
   z += 0x9E3779B97F4A7C15ull;
   z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;

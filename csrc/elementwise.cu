@@ -283,7 +283,7 @@ __global__ void act_dropout_kernel(const __nv_bfloat16* __restrict__ x, const __
                                    const uint64_t* __restrict__ key, uint64_t salt, uint32_t thresh16, float scale,
                                    int bwd) {
   uint64_t seed = 0;
-  if (key != nullptr) seed = mix64(*key ^ mix64(salt));
+  if (key != nullptr) seed = mix64(*key ^ salt);
   const int64_t total = rows * cols;
   const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
   for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {

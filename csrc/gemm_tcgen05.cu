@@ -43,6 +43,8 @@ struct GemmDev {
   int ldaux;
   const uint64_t* drop_key;
   uint64_t drop_salt;
+  int drop_nsalt, drop_rows_per_salt;
+  uint64_t drop_salts[16];
   uint32_t drop_thresh16;
   float drop_scale;
   int vec_d, vec_pre, vec_aux, vec_res;  // 16-byte vector access allowed
@@ -234,8 +236,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
   } else {
     // ===================== epilogue (warps 2..5) =====================
     const int quad = warp & 3;  // TMEM lane quadrant this warp may read
-    uint64_t seed = 0;
-    if (p.drop_key != nullptr) seed = mix64(*p.drop_key ^ mix64(p.drop_salt));
+    uint64_t key = 0, seed = 0;
+    if (p.drop_key != nullptr) {
+      key = *p.drop_key;
+      seed = mix64(key ^ p.drop_salt);
+    }
     int local = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
       const int as = local & 1;
@@ -245,6 +250,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
       tc_fence_after();
       const int row = tc.m0 + quad * 32 + lane;
       const bool row_ok = row < p.M;
+      int drop_row = row;
+      if (p.drop_key != nullptr && p.drop_nsalt > 0) {
+        int blk = row / p.drop_rows_per_salt;
+        drop_row = row - blk * p.drop_rows_per_salt;
+        seed = mix64(key ^ p.drop_salts[blk < p.drop_nsalt ? blk : p.drop_nsalt - 1]);
+      }
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + as * BN;
 #pragma unroll 1
       for (int c = 0; c < BN / 32; ++c) {
@@ -321,7 +332,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
             }
           }
           if (p.drop_key != nullptr) {
-            const uint64_t base = static_cast<uint64_t>(row) * static_cast<uint64_t>(p.N) + col;
+            const uint64_t base = static_cast<uint64_t>(drop_row) * static_cast<uint64_t>(p.N) + col;
 #pragma unroll
             for (int j = 0; j < 8; ++j)
               v[j] = dropout_keep(seed, base + j, p.drop_thresh16) ? v[j] * p.drop_scale : 0.0f;
@@ -489,6 +500,10 @@ extern "C" int b200_gemm_bf16(const b200_gemm_args* args, void* stream) {
   dev.aux = static_cast<const __nv_bfloat16*>(a.aux); dev.ldaux = a.ldaux;
   dev.drop_key = (a.drop_rate > 0.0f) ? a.drop_key : nullptr;
   dev.drop_salt = a.drop_salt;
+  B200_REQUIRE(a.drop_nsalt >= 0 && a.drop_nsalt <= 16, "gemm: at most 16 dropout row blocks (got %d)", a.drop_nsalt);
+  dev.drop_nsalt = a.drop_nsalt;
+  dev.drop_rows_per_salt = a.drop_rows_per_salt > 0 ? a.drop_rows_per_salt : 1;
+  for (int i = 0; i < a.drop_nsalt; ++i) dev.drop_salts[i] = a.drop_salts[i];
   float keep = 1.0f - a.drop_rate;
   dev.drop_thresh16 = (uint32_t)(keep * 65536.0f + 0.5f);
   dev.drop_scale = keep > 0.f ? 1.0f / keep : 0.f;

@@ -1,0 +1,248 @@
+// LayerNorm and embedding kernels for the GPT-2 configurations (BASELINE.json configs 2-5; the
+// reference itself has no transformer). Memory-bound: one warp per row, 16-byte accesses, rows
+// kept in registers between the statistics pass and the normalisation pass.
+#include "../include/b200dist.h"
+#include "common.cuh"
+
+namespace b200 {
+
+constexpr int LN_MAX_CHUNKS = 8;  // 8 chunks x 32 lanes x 8 elements = 2048 columns max
+
+__device__ __forceinline__ void unpack8(const uint4& w, float (&f)[8]) {
+  f[0] = __uint_as_float(w.x << 16); f[1] = __uint_as_float(w.x & 0xFFFF0000u);
+  f[2] = __uint_as_float(w.y << 16); f[3] = __uint_as_float(w.y & 0xFFFF0000u);
+  f[4] = __uint_as_float(w.z << 16); f[5] = __uint_as_float(w.z & 0xFFFF0000u);
+  f[6] = __uint_as_float(w.w << 16); f[7] = __uint_as_float(w.w & 0xFFFF0000u);
+}
+__device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
+  __nv_bfloat162 a = __floats2bfloat162_rn(f[0], f[1]), b = __floats2bfloat162_rn(f[2], f[3]);
+  __nv_bfloat162 c = __floats2bfloat162_rn(f[4], f[5]), d = __floats2bfloat162_rn(f[6], f[7]);
+  uint4 w;
+  w.x = *reinterpret_cast<uint32_t*>(&a); w.y = *reinterpret_cast<uint32_t*>(&b);
+  w.z = *reinterpret_cast<uint32_t*>(&c); w.w = *reinterpret_cast<uint32_t*>(&d);
+  return w;
+}
+
+// cols % 8 == 0, cols <= 2048
+__global__ void __launch_bounds__(128)
+layernorm_fwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ gamma,
+                     const __nv_bfloat16* __restrict__ beta, __nv_bfloat16* __restrict__ y,
+                     float* __restrict__ mean, float* __restrict__ rstd, int rows, int cols, float eps) {
+  const int lane = threadIdx.x & 31;
+  const int wpb = blockDim.x >> 5;
+  const int nchunk = cols >> 3;
+  for (int row = blockIdx.x * wpb + (threadIdx.x >> 5); row < rows; row += gridDim.x * wpb) {
+    const uint4* xr = reinterpret_cast<const uint4*>(x + static_cast<size_t>(row) * cols);
+    float v[LN_MAX_CHUNKS][8];
+    float s = 0.f;
+#pragma unroll
+    for (int c = 0; c < LN_MAX_CHUNKS; ++c) {
+      int idx = c * 32 + lane;
+      if (idx < nchunk) {
+        unpack8(xr[idx], v[c]);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s += v[c][j];
+      }
+    }
+    s = warp_sum(s);
+    const float mu = s / cols;
+    float q = 0.f;
+#pragma unroll
+    for (int c = 0; c < LN_MAX_CHUNKS; ++c) {
+      int idx = c * 32 + lane;
+      if (idx < nchunk) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { float d = v[c][j] - mu; q += d * d; }
+      }
+    }
+    q = warp_sum(q);
+    const float rs = rsqrtf(q / cols + eps);
+    uint4* yr = reinterpret_cast<uint4*>(y + static_cast<size_t>(row) * cols);
+#pragma unroll
+    for (int c = 0; c < LN_MAX_CHUNKS; ++c) {
+      int idx = c * 32 + lane;
+      if (idx < nchunk) {
+        float g[8], b[8], o[8];
+        unpack8(reinterpret_cast<const uint4*>(gamma)[idx], g);
+        unpack8(reinterpret_cast<const uint4*>(beta)[idx], b);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = (v[c][j] - mu) * rs * g[j] + b[j];
+        yr[idx] = pack8(o);
+      }
+    }
+    if (lane == 0) { mean[row] = mu; rstd[row] = rs; }
+  }
+}
+
+// dx = rstd * (dy*g - mean(dy*g) - xhat * mean(dy*g*xhat)); dgamma += dy*xhat; dbeta += dy.
+// Each block keeps fp32 partial dgamma/dbeta in shared memory over the rows it owns and flushes
+// them with one atomicAdd per column at the end.
+__global__ void __launch_bounds__(256)
+layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
+                     const __nv_bfloat16* __restrict__ gamma, const float* __restrict__ mean,
+                     const float* __restrict__ rstd, __nv_bfloat16* __restrict__ dx, float* __restrict__ dgamma,
+                     float* __restrict__ dbeta, int rows, int cols) {
+  extern __shared__ float sm[];
+  float* s_dg = sm;
+  float* s_db = sm + cols;
+  for (int i = threadIdx.x; i < 2 * cols; i += blockDim.x) sm[i] = 0.f;
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  const int wpb = blockDim.x >> 5;
+  const int nchunk = cols >> 3;
+  for (int row = blockIdx.x * wpb + (threadIdx.x >> 5); row < rows; row += gridDim.x * wpb) {
+    const uint4* xr = reinterpret_cast<const uint4*>(x + static_cast<size_t>(row) * cols);
+    const uint4* dr = reinterpret_cast<const uint4*>(dy + static_cast<size_t>(row) * cols);
+    const float mu = mean[row], rs = rstd[row];
+    float xh[LN_MAX_CHUNKS][8], dg[LN_MAX_CHUNKS][8];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int c = 0; c < LN_MAX_CHUNKS; ++c) {
+      int idx = c * 32 + lane;
+      if (idx < nchunk) {
+        float xv[8], dv[8], g[8];
+        unpack8(xr[idx], xv);
+        unpack8(dr[idx], dv);
+        unpack8(reinterpret_cast<const uint4*>(gamma)[idx], g);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          xh[c][j] = (xv[j] - mu) * rs;
+          dg[c][j] = dv[j] * g[j];
+          s1 += dg[c][j];
+          s2 += dg[c][j] * xh[c][j];
+          atomicAdd(&s_dg[idx * 8 + j], dv[j] * xh[c][j]);
+          atomicAdd(&s_db[idx * 8 + j], dv[j]);
+        }
+      }
+    }
+    s1 = warp_sum(s1) / cols;
+    s2 = warp_sum(s2) / cols;
+    uint4* or_ = reinterpret_cast<uint4*>(dx + static_cast<size_t>(row) * cols);
+#pragma unroll
+    for (int c = 0; c < LN_MAX_CHUNKS; ++c) {
+      int idx = c * 32 + lane;
+      if (idx < nchunk) {
+        float o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = rs * (dg[c][j] - s1 - xh[c][j] * s2);
+        or_[idx] = pack8(o);
+      }
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < cols; i += blockDim.x) {
+    atomicAdd(&dgamma[i], s_dg[i]);
+    atomicAdd(&dbeta[i], s_db[i]);
+  }
+}
+
+__global__ void __launch_bounds__(128)
+embedding_fwd_kernel(const int64_t* __restrict__ tokens, const __nv_bfloat16* __restrict__ wte,
+                     const __nv_bfloat16* __restrict__ wpe, __nv_bfloat16* __restrict__ out, int rows, int seq,
+                     int dim) {
+  const int lane = threadIdx.x & 31;
+  const int wpb = blockDim.x >> 5;
+  const int nchunk = dim >> 3;
+  for (int row = blockIdx.x * wpb + (threadIdx.x >> 5); row < rows; row += gridDim.x * wpb) {
+    const int64_t tok = tokens[row];
+    const int t = row % seq;
+    const uint4* a = reinterpret_cast<const uint4*>(wte + static_cast<size_t>(tok) * dim);
+    const uint4* b = reinterpret_cast<const uint4*>(wpe + static_cast<size_t>(t) * dim);
+    uint4* o = reinterpret_cast<uint4*>(out + static_cast<size_t>(row) * dim);
+    for (int idx = lane; idx < nchunk; idx += 32) {
+      float fa[8], fb[8];
+      unpack8(a[idx], fa);
+      unpack8(b[idx], fb);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) fa[j] += fb[j];
+      o[idx] = pack8(fa);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(128)
+embedding_bwd_kernel(const int64_t* __restrict__ tokens, const __nv_bfloat16* __restrict__ dout,
+                     float* __restrict__ dwte, float* __restrict__ dwpe, int rows, int seq, int dim) {
+  const int lane = threadIdx.x & 31;
+  const int wpb = blockDim.x >> 5;
+  const int nchunk = dim >> 3;
+  for (int row = blockIdx.x * wpb + (threadIdx.x >> 5); row < rows; row += gridDim.x * wpb) {
+    const int64_t tok = tokens[row];
+    const int t = row % seq;
+    const uint4* d = reinterpret_cast<const uint4*>(dout + static_cast<size_t>(row) * dim);
+    float* gt = dwte + static_cast<size_t>(tok) * dim;
+    float* gp = dwpe + static_cast<size_t>(t) * dim;
+    for (int idx = lane; idx < nchunk; idx += 32) {
+      float f[8];
+      unpack8(d[idx], f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        if (dwte != nullptr) atomicAdd(&gt[idx * 8 + j], f[j]);
+        if (dwpe != nullptr) atomicAdd(&gp[idx * 8 + j], f[j]);
+      }
+    }
+  }
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_layernorm_fwd(const void* x, const void* gamma, const void* beta, void* y, float* mean,
+                                  float* rstd, int rows, int cols, float eps, void* stream) {
+  B200_REQUIRE(rows > 0 && cols > 0 && cols % 8 == 0 && cols <= 2048, "layernorm: cols=%d must be a multiple of 8, <= 2048", cols);
+  int blocks = (rows + 3) / 4;
+  int cap = num_sms() * 16;
+  if (blocks > cap) blocks = cap;
+  layernorm_fwd_kernel<<<blocks, 128, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(gamma),
+      static_cast<const __nv_bfloat16*>(beta), static_cast<__nv_bfloat16*>(y), mean, rstd, rows, cols, eps);
+  count_launch();
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200_layernorm_bwd(const void* dy, const void* x, const void* gamma, const float* mean,
+                                  const float* rstd, void* dx, float* dgamma, float* dbeta, int rows, int cols,
+                                  void* stream) {
+  B200_REQUIRE(rows > 0 && cols > 0 && cols % 8 == 0 && cols <= 2048, "layernorm: cols=%d must be a multiple of 8, <= 2048", cols);
+  int blocks = (rows + 7) / 8;
+  int cap = num_sms() * 2;
+  if (blocks > cap) blocks = cap;
+  layernorm_bwd_kernel<<<blocks, 256, 2 * cols * sizeof(float), static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(x),
+      static_cast<const __nv_bfloat16*>(gamma), mean, rstd, static_cast<__nv_bfloat16*>(dx), dgamma, dbeta, rows,
+      cols);
+  count_launch();
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200_embedding_fwd(const int64_t* tokens, const void* wte, const void* wpe, void* out, int batch,
+                                  int seq, int dim, void* stream) {
+  B200_REQUIRE(batch > 0 && seq > 0 && dim % 8 == 0, "embedding: dim=%d must be a multiple of 8", dim);
+  int rows = batch * seq;
+  int blocks = (rows + 3) / 4;
+  int cap = num_sms() * 16;
+  if (blocks > cap) blocks = cap;
+  embedding_fwd_kernel<<<blocks, 128, 0, static_cast<cudaStream_t>(stream)>>>(
+      tokens, static_cast<const __nv_bfloat16*>(wte), static_cast<const __nv_bfloat16*>(wpe),
+      static_cast<__nv_bfloat16*>(out), rows, seq, dim);
+  count_launch();
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200_embedding_bwd(const int64_t* tokens, const void* dout, float* dwte, float* dwpe, int batch,
+                                  int seq, int dim, void* stream) {
+  B200_REQUIRE(batch > 0 && seq > 0 && dim % 8 == 0, "embedding: dim=%d must be a multiple of 8", dim);
+  int rows = batch * seq;
+  int blocks = (rows + 3) / 4;
+  int cap = num_sms() * 16;
+  if (blocks > cap) blocks = cap;
+  embedding_bwd_kernel<<<blocks, 128, 0, static_cast<cudaStream_t>(stream)>>>(
+      tokens, static_cast<const __nv_bfloat16*>(dout), dwte, dwpe, rows, seq, dim);
+  count_launch();
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}

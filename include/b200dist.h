@@ -16,7 +16,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 4
+#define B200_ABI_VERSION 5
 
 const char* b200_last_error(void);
 int b200_abi_version(void);
@@ -74,10 +74,16 @@ typedef struct b200_gemm_args {
   const void* aux; /* bf16 [M][ldaux]: the forward's saved pre-activation */
   int32_t ldaux;
   /* dropout (either direction); disabled when drop_key == NULL */
-  const uint64_t* drop_key; /* device pointer to the 64-bit step key */
-  uint64_t drop_salt;       /* host constant folded into the key (minibatch, rank, layer) */
+  const uint64_t* drop_key; /* device pointer to the 64-bit key state */
+  uint64_t drop_salt;       /* host constant: seed = mix64(*drop_key ^ drop_salt) */
   float drop_rate;
   int32_t block_n; /* 0 = choose, else 64/128/256 */
+  /* Gradient accumulation folded into one GEMM: rows [i*drop_rows_per_salt, (i+1)*...) form
+   * minibatch i with its own RNG stream drop_salts[i] and element index restarting at 0, so the
+   * masks equal those of a loop over minibatches (reference: util.py:51,58-66).
+   * drop_nsalt = 0 uses drop_salt for all rows. */
+  int32_t drop_nsalt, drop_rows_per_salt;
+  uint64_t drop_salts[16];
 } b200_gemm_args;
 
 int b200_gemm_bf16(const b200_gemm_args* args, void* stream);

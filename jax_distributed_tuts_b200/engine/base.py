@@ -231,7 +231,9 @@ class FusedEngine:
         captures it into a CUDA graph and replays it, later calls only replay. Every call performs
         exactly one real training step."""
         if not self.use_graph:
+            before = _lib.launch_count()
             self._step_body()
+            self.launches_per_step = _lib.launch_count() - before
             return
         if self.graph is None:
             if not getattr(self, "_warmed", False):

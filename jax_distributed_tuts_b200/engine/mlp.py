@@ -48,7 +48,8 @@ _LEAVES = ("input_dense/kernel", "input_dense/bias", "output_dense/kernel", "out
 class MLPEngine(FusedEngine):
     def __init__(self, config, mesh: Mesh, *, mode: str = "dp", batch_per_rank: int, lr: float,
                  num_minibatches: int = 4, min_weight_size: int = 2 ** 18, seed_key: Optional[_rng.Key] = None,
-                 init_params: Optional[Dict] = None, input_size: int = 784, overlap: bool = True, **kw):
+                 init_params: Optional[Dict] = None, input_size: int = 784, overlap: bool = True,
+                 fuse_minibatches: bool = True, **kw):
         super().__init__(mesh, lr=lr, num_minibatches=num_minibatches,
                          data_axis_name=config.get("data_axis_name", "data"), **kw)
         assert mode in ("dp", "fsdp")
@@ -59,6 +60,10 @@ class MLPEngine(FusedEngine):
         self.In, self.H, self.Cn = input_size, config.hidden_size, config.num_classes
         self.rate = float(config.dropout_rate)
         self.overlap = overlap and self.world > 1
+        # Gradient accumulation folded into the GEMMs: all minibatches go through one set of
+        # launches, the wgrad K loop does the summation and the dropout epilogue switches RNG
+        # stream per minibatch row block, so results equal the reference's loop (util.py:58-77).
+        self.fuse_minibatches = fuse_minibatches and num_minibatches <= 16
         self.min_weight_size = min_weight_size
         W = self.world
         # bucket 0 = output layer (gradients complete first in backward), bucket 1 = input layer
@@ -93,7 +98,7 @@ class MLPEngine(FusedEngine):
         self.ctx = self._make_ctx(self.arena, "grad", "param" if mode == "dp" else None, "bf16", "signal")
         self._build_segments()
         # activations (static, reused every minibatch)
-        mb = self.mb
+        mb = self.B if self.fuse_minibatches else self.mb
         pad8 = lambda c: _round_up(c, 8)
         self.x_in = torch.zeros(self.B, self.In, dtype=torch.float32, device=d)
         self.labels = torch.zeros(self.B, dtype=torch.int64, device=d)
@@ -312,77 +317,77 @@ class MLPEngine(FusedEngine):
         return self.B * self.world
 
     def _step_body(self) -> None:
-        nmb, mb, W = self.num_minibatches, self.mb, self.world
+        nmb, mb = self.num_minibatches, self.mb
         key = _rng.Key(self.rng_base, 0)
         next_rng, step_rng = _rng.split(key, 2)
         mb_keys = _rng.split(step_rng, nmb)
         axis_idx = self.mesh.axis_index(self.data_axis_name)
+        salts = [_rng.salt_word(_rng.fold_in(mb_keys[i], axis_idx)) for i in range(nmb)]
         K.scale_(self.step_metrics, 0.0)
         xb = self.x_bf[:, : self.In]
         if self.x_bf.shape[1] == self.In:
             K.cast_f32_bf16(self.x_in, self.x_bf)
         else:
             xb.copy_(self.x_in)
-        lay = self.layout
-        g = lambda p: lay.view2d(self.g32, p)
         if self.mode == "fsdp":
             self._gather_biases()
-        if self.mode == "dp":
-            W1, W2 = lay.view2d(self.pb, "input_dense/kernel"), lay.view2d(self.pb, "output_dense/kernel")
-            b1, b2 = lay.view(self.pb, "input_dense/bias"), lay.view(self.pb, "output_dense/bias")
-        logits = self.logits[:, : self.Cn]
-        dlogits = self.dlogits[:, : self.Cn]
-        main = torch.cuda.current_stream()
-        for i in range(nmb):
-            xs = xb[i * mb:(i + 1) * mb]
-            lab = self.labels[i * mb:(i + 1) * mb]
-            dk = _rng.fold_in(mb_keys[i], axis_idx)
-            salt = _rng.salt_word(dk)
-            acc = i > 0
-            last = i == nmb - 1
-            if self.mode == "dp":
-                K.gemm(xs, W1, self.h, b_mn=True, bias=b1, act="silu", pre=self.pre, drop_key=self.rng_base,
-                       drop_salt=salt, drop_rate=self.rate)
-                K.gemm(self.h, W2, logits, b_mn=True, bias=b2)
-            else:
-                self._fsdp_gemm_fwd(xs, "input_dense", self.h, act="silu", pre=self.pre, salt=salt)
-                self._fsdp_gemm_fwd(self.h, "output_dense", logits)
-            K.softmax_xent(logits, lab, grad_scale=1.0 / mb, dlogits=dlogits, metrics=self.step_metrics)
-            K.gemm(self.h, dlogits, g("output_dense/kernel"), a_mn=True, b_mn=True, accumulate=acc)
-            K.colsum(dlogits, lay.view(self.g32, "output_dense/bias"), accumulate=acc)
-            if last and self.overlap:
-                # bucket 0 is complete: reduce + update it under the rest of the backward
-                self.side_stream.wait_stream(main)
-                with torch.cuda.stream(self.side_stream):
-                    self._sync_bucket(0, last=False)
-            if self.mode == "dp":
-                K.gemm(dlogits, W2, self.dpre, bwd=True, aux=self.pre, act="silu", drop_key=self.rng_base,
-                       drop_salt=salt, drop_rate=self.rate)
-            else:
-                self._fsdp_gemm_dgrad(dlogits, "output_dense", self.dpre, aux=self.pre, act="silu", salt=salt)
-            K.gemm(xs, self.dpre, g("input_dense/kernel"), a_mn=True, b_mn=True, accumulate=acc)
-            K.colsum(self.dpre, lay.view(self.g32, "input_dense/bias"), accumulate=acc)
+        if self.fuse_minibatches:
+            self._fwd_bwd(xb, self.labels, salts, mb, accumulate=False, last=True)
+        else:
+            for i in range(nmb):
+                self._fwd_bwd(xb[i * mb:(i + 1) * mb], self.labels[i * mb:(i + 1) * mb], [salts[i]], mb,
+                              accumulate=i > 0, last=i == nmb - 1)
         if self.overlap:
-            main.wait_stream(self.side_stream)   # the two fused launches share the signal words: serialise
+            torch.cuda.current_stream().wait_stream(self.side_stream)   # the fused launches share signal words
         else:
             self._sync_bucket(0, last=False)
         self._sync_bucket(1, last=True)
         # state.rng <- rebase(next_rng): the salt folds into the device-resident key in place
         K.rng_split_(self.rng_base, None, _rng.salt_word(next_rng), 0)
 
+    def _fwd_bwd(self, xs, lab, salts, rows_per_salt: int, *, accumulate: bool, last: bool) -> None:
+        """Forward + backward of one row block (a minibatch, or all minibatches at once)."""
+        lay = self.layout
+        g = lambda p: lay.view2d(self.g32, p)
+        logits = self.logits[:, : self.Cn]
+        dlogits = self.dlogits[:, : self.Cn]
+        drop = dict(drop_key=self.rng_base, drop_rate=self.rate, drop_salts=salts, drop_rows_per_salt=rows_per_salt)
+        main = torch.cuda.current_stream()
+        if self.mode == "dp":
+            W1, W2 = lay.view2d(self.pb, "input_dense/kernel"), lay.view2d(self.pb, "output_dense/kernel")
+            b1, b2 = lay.view(self.pb, "input_dense/bias"), lay.view(self.pb, "output_dense/bias")
+            K.gemm(xs, W1, self.h, b_mn=True, bias=b1, act="silu", pre=self.pre, **drop)
+            K.gemm(self.h, W2, logits, b_mn=True, bias=b2)
+        else:
+            self._fsdp_gemm_fwd(xs, "input_dense", self.h, act="silu", pre=self.pre, drop=drop)
+            self._fsdp_gemm_fwd(self.h, "output_dense", logits)
+        K.softmax_xent(logits, lab, grad_scale=1.0 / self.mb, dlogits=dlogits, metrics=self.step_metrics)
+        K.gemm(self.h, dlogits, g("output_dense/kernel"), a_mn=True, b_mn=True, accumulate=accumulate)
+        K.colsum(dlogits, lay.view(self.g32, "output_dense/bias"), accumulate=accumulate)
+        if last and self.overlap:
+            # bucket 0 (output layer) is complete: reduce + update it under the rest of the backward
+            self.side_stream.wait_stream(main)
+            with torch.cuda.stream(self.side_stream):
+                self._sync_bucket(0, last=False)
+        if self.mode == "dp":
+            K.gemm(dlogits, W2, self.dpre, bwd=True, aux=self.pre, act="silu", **drop)
+        else:
+            self._fsdp_gemm_dgrad(dlogits, "output_dense", self.dpre, aux=self.pre, act="silu", drop=drop)
+        K.gemm(xs, self.dpre, g("input_dense/kernel"), a_mn=True, b_mn=True, accumulate=accumulate)
+        K.colsum(self.dpre, lay.view(self.g32, "input_dense/bias"), accumulate=accumulate)
+
     # FSDP GEMMs: B comes from the peers' shards (all-gather fused into the GEMM)
-    def _fsdp_gemm_fwd(self, x, layer: str, out, act=None, pre=None, salt: int = 0):
+    def _fsdp_gemm_fwd(self, x, layer: str, out, act=None, pre=None, drop=None):
         kw, shard = self._weight(f"{layer}/kernel")
         bias = self._bias(layer)
         extra = {}
         if shard is not None:
             last_dim, shard_len = shard
             extra = dict(shard_mode=2 if last_dim else 1, shard_len=shard_len, rot=self.rank)
-        drop = dict(drop_key=self.rng_base, drop_salt=salt, drop_rate=self.rate) if act is not None else {}
         b = kw.pop("b")
-        K.gemm(x, b, out, b_mn=True, bias=bias, act=act, pre=pre, **drop, **kw, **extra)
+        K.gemm(x, b, out, b_mn=True, bias=bias, act=act, pre=pre, **(drop or {}), **kw, **extra)
 
-    def _fsdp_gemm_dgrad(self, dy, layer: str, out, aux=None, act=None, salt: int = 0):
+    def _fsdp_gemm_dgrad(self, dy, layer: str, out, aux=None, act=None, drop=None):
         kw, shard = self._weight(f"{layer}/kernel")
         extra = {}
         if shard is not None:
@@ -390,8 +395,7 @@ class MLPEngine(FusedEngine):
             # dx = dy W^T: the (in,out) kernel is the K-major B operand [N'=in][K'=out]
             extra = dict(shard_mode=1 if last_dim else 2, shard_len=shard_len, rot=self.rank)
         b = kw.pop("b")
-        K.gemm(dy, b, out, bwd=True, aux=aux, act=act, drop_key=self.rng_base, drop_salt=salt,
-               drop_rate=self.rate, **kw, **extra)
+        K.gemm(dy, b, out, bwd=True, aux=aux, act=act, **(drop or {}), **kw, **extra)
 
     def _bias(self, layer: str) -> torch.Tensor:
         """Biases are tiny: sharded ones are gathered once per step into a local bf16 vector by the

@@ -10,7 +10,7 @@ from typing import Optional
 
 from . import _build
 
-ABI_VERSION = 4
+ABI_VERSION = 5
 
 _lib: Optional[C.CDLL] = None
 
@@ -41,6 +41,8 @@ class GemmArgs(C.Structure):
         ("drop_salt", C.c_uint64),
         ("drop_rate", C.c_float),
         ("block_n", C.c_int32),
+        ("drop_nsalt", C.c_int32), ("drop_rows_per_salt", C.c_int32),
+        ("drop_salts", C.c_uint64 * 16),
     ]
 
 

@@ -48,6 +48,8 @@ def gemm(
     drop_key: Optional[torch.Tensor] = None,
     drop_salt: int = 0,
     drop_rate: float = 0.0,
+    drop_salts: Optional[Sequence[int]] = None,
+    drop_rows_per_salt: int = 0,
     shard_mode: int = 0,
     shard_len: int = 0,
     rot: int = 0,
@@ -109,6 +111,11 @@ def gemm(
         args.drop_key = drop_key.data_ptr()
         args.drop_salt = drop_salt & 0xFFFFFFFFFFFFFFFF
         args.drop_rate = drop_rate
+        if drop_salts is not None:
+            assert len(drop_salts) <= 16 and drop_rows_per_salt > 0
+            args.drop_nsalt, args.drop_rows_per_salt = len(drop_salts), drop_rows_per_salt
+            for i, sv in enumerate(drop_salts):
+                args.drop_salts[i] = sv & 0xFFFFFFFFFFFFFFFF
     args.block_n = block_n
     _lib.check(_lib.lib().b200_gemm_bf16(C.byref(args), _stream()))
     return out

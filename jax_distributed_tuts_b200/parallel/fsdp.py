@@ -149,7 +149,9 @@ def init_model(rng: _rng.Key, x: torch.Tensor, model, learning_rate: float = 1e-
     variables = model.init({"params": init_rng}, x, train=False)
     params = variables.pop("params")
     tx = optimizer if optimizer is not None else adamw(learning_rate)
-    return TrainState.create(apply_fn=model.apply, params=params, tx=tx, rng=rng)
+    # the stored key is always in rebased form (salt folded into the 64-bit state), the same
+    # form every train step leaves it in
+    return TrainState.create(apply_fn=model.apply, params=params, tx=tx, rng=_rng.rebase(rng))
 
 
 def sync_gradients(grads: Pytree, axis_names: Sequence[str], mesh: Optional[Mesh] = None) -> Pytree:

@@ -60,8 +60,8 @@ def test_generic_gpu_path_matches_cpu_oracle_with_dropout():
     assert abs(float(m_cpu["accuracy"][0]) - float(m_gpu["accuracy"][0])) <= 3
 
 
-@pytest.mark.parametrize("use_graph", [False, True])
-def test_fused_engine_matches_generic_path(use_graph):
+@pytest.mark.parametrize("use_graph,fuse", [(False, False), (False, True), (True, True)])
+def test_fused_engine_matches_generic_path(use_graph, fuse):
     from jax_distributed_tuts_b200.engine import MLPEngine
     cfg, _, model, state, batch = _setup("cpu")
     steps, lr = 4, cfg.optimizer.learning_rate
@@ -73,7 +73,8 @@ def test_fused_engine_matches_generic_path(use_graph):
         s_gen, m_gen = step(s_gen, m_gen, bg)
     with mesh_g:
         eng = MLPEngine(cfg.model, mesh_g, mode="dp", batch_per_rank=batch.inputs.shape[0], lr=lr,
-                        num_minibatches=4, init_params=state.params, use_graph=use_graph)
+                        num_minibatches=4, init_params=state.params, use_graph=use_graph,
+                        fuse_minibatches=fuse)
         s_eng = eng.make_state(model, state.rng)
         m_eng = None
         pinned = Batch(batch.inputs.pin_memory(), batch.labels.pin_memory())
