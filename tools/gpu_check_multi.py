@@ -1,0 +1,129 @@
+"""Multi-GPU checks (launch with torchrun, one rank per GPU):
+
+  torchrun --standalone --local-addr 127.0.0.1 --nproc-per-node 2 tools/gpu_check_multi.py
+
+1. fused DP engine (NVLS multicast path, then the P2P path) == generic DP over NCCL;
+   replicas bit-identical
+2. fused FSDP engine (all-gather fused into the GEMM + reduce-scatter fused with AdamW) == DP engine
+3. step timing of each, device-timed, max over ranks
+"""
+from __future__ import annotations
+
+import os
+import sys
+import time
+import traceback
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+import torch
+import torch.distributed as dist
+
+from jax_distributed_tuts_b200 import rng
+from jax_distributed_tuts_b200.config import dp_config
+from jax_distributed_tuts_b200.engine import MLPEngine
+from jax_distributed_tuts_b200.launch import init_from_env
+from jax_distributed_tuts_b200.mesh import Mesh
+from jax_distributed_tuts_b200.models.mlp import Classifier
+from jax_distributed_tuts_b200.parallel import dp
+from jax_distributed_tuts_b200.state import Batch
+from jax_distributed_tuts_b200.tree import tree_leaves, tree_map
+
+
+def log(*a):
+    if dist.get_rank() == 0:
+        print(*a, flush=True)
+
+
+def close(a, b, lr, steps):
+    d = (a.float() - b.float().reshape(a.shape)).abs()
+    return bool(d.max() <= 2.2 * lr * steps and d.mean() <= 0.06 * lr * steps), d.max().item(), d.mean().item()
+
+
+def main():
+    rank, world, device = init_from_env()
+    per_rank, steps, lr = 64, 4, 1e-3
+    cfg = dp_config()
+    mesh = Mesh((world,), ("data",))
+    model = Classifier(cfg.model)
+    key = rng.PRNGKey(cfg.seed)
+    model_rng, data_rng, label_rng = rng.split(key, 3)
+    gB = per_rank * world
+    x = torch.randn(gB, 784, generator=rng.uniform_generator(data_rng))
+    y = torch.randint(0, 10, (gB,), generator=rng.uniform_generator(label_rng))
+    ok_all = True
+    with mesh:
+        init = dp.init_dp(model_rng, x, model)
+        local = dp.shard_batch(Batch(x, y))
+        # ---- generic DP over NCCL ----
+        to_dev = lambda t: t.to(device)
+        gen = init.replace(params=tree_map(to_dev, init.params), rng=init.rng.to(device))
+        gen = gen.replace(opt_state=gen.tx.init(gen.params))
+        step = dp.make_train_step_dp(mesh, num_minibatches=4)
+        lb = local.to(device)
+        m_gen = None
+        for _ in range(steps):
+            gen, m_gen = step(gen, m_gen, lb)
+        torch.cuda.synchronize()
+        log(f"generic NCCL DP: loss {float(m_gen['loss'][0]) / m_gen['loss'][1]:.5f} count {m_gen['loss'][1]}")
+        results = {}
+        for name, mode, env in (("dp/nvls", "dp", "0"), ("dp/p2p", "dp", "1"), ("fsdp/nvls", "fsdp", "0"),
+                                ("fsdp/p2p", "fsdp", "1")):
+            try:
+                os.environ["B200DIST_NO_MULTICAST"] = env
+                eng = MLPEngine(cfg.model, mesh, mode=mode, batch_per_rank=per_rank, lr=lr, num_minibatches=4,
+                                init_params=init.params, min_weight_size=16, use_graph=True)
+                st = eng.make_state(model, init.rng)
+                pinned = Batch(local.inputs.pin_memory(), local.labels.pin_memory())
+                m = None
+                for _ in range(steps):
+                    st, m = eng.train_step(st, m, pinned)
+                torch.cuda.synchronize()
+                tree = eng.params_tree()
+                good = True
+                for k in ("input_dense", "output_dense"):
+                    for kk in ("kernel", "bias"):
+                        c, mx, mean = close(tree[k][kk], gen.params[k][kk], lr, steps)
+                        good &= c
+                        if not c:
+                            log(f"  [{name}] {k}/{kk} mismatch max {mx:.2e} mean {mean:.2e}")
+                # replicas identical
+                flat = torch.cat([t.reshape(-1).float() for kk in tree.values() for t in kk.values()])
+                ref = flat.clone()
+                dist.broadcast(ref, 0)
+                same = bool(torch.equal(ref, flat))
+                t = torch.tensor([int(same)], device=device)
+                dist.all_reduce(t, op=dist.ReduceOp.MIN)
+                loss = float(m["loss"][0]) / m["loss"][1]
+                lg = float(m_gen["loss"][0]) / m_gen["loss"][1]
+                good &= abs(loss - lg) < 2e-2 and m["loss"][1] == m_gen["loss"][1]
+                # timing
+                evs = []
+                for _ in range(30):
+                    eng._load_batch(pinned)
+                    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    s.record(); eng._run_step(); e.record()
+                    evs.append((s, e))
+                torch.cuda.synchronize()
+                ms = sorted(a.elapsed_time(b) for a, b in evs)[len(evs) // 2]
+                tt = torch.tensor([ms], device=device)
+                dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+                log(f"[{'ok' if good and t.item() == 1 else 'FAIL'}] {name}: backend={eng.arena.backend} loss {loss:.5f} "
+                    f"(generic {lg:.5f}) replicas_identical={bool(t.item())} median step {tt.item() * 1e3:.1f} us "
+                    f"launches/step {eng.launches_per_step}")
+                ok_all &= good and t.item() == 1
+                results[name] = tree
+                del eng
+            except Exception as e:  # noqa: BLE001
+                traceback.print_exc()
+                log(f"[FAIL] {name}: {type(e).__name__}: {e}")
+                ok_all = False
+                break
+    log("MULTI-GPU CHECK", "PASS" if ok_all else "FAIL")
+    dist.barrier()
+    dist.destroy_process_group()
+    sys.exit(0 if ok_all else 1)
+
+
+if __name__ == "__main__":
+    main()
