@@ -16,7 +16,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 5
+#define B200_ABI_VERSION 6
 
 const char* b200_last_error(void);
 int b200_abi_version(void);
@@ -160,15 +160,19 @@ int b200_embedding_fwd(const int64_t* tokens, const void* wte, const void* wpe, 
 /* dwte[tok] += dout ; dwpe[t] += dout   (fp32 grads, atomics) */
 int b200_embedding_bwd(const int64_t* tokens, const void* dout, float* dwte, float* dwpe, int batch,
                        int seq, int dim, void* stream);
-/* Causal self-attention on tcgen05 (S = QK^T and O = PV on the tensor cores, online softmax in
- * registers). qkv bf16 [batch][seq][3][heads][64]; out bf16 [batch][seq][heads][64];
- * lse fp32 [batch][heads][seq]. head_dim is 64; seq must be a multiple of 128. */
+/* Causal self-attention on tcgen05 (S = QK^T and O = PV on the tensor cores with TMEM
+ * accumulators, K/V tiles by TMA, online softmax in registers on rows read with tcgen05.ld).
+ * qkv bf16 [batch][seq][3][heads][64]; out bf16 [batch][seq][heads][64];
+ * lse fp32 [batch][heads][seq] (log2 units of the scaled scores). head_dim is 64; seq must be a
+ * multiple of 128. */
 int b200_attention_fwd(const void* qkv, void* out, float* lse, int batch, int seq, int heads,
                        void* stream);
-/* dqkv bf16 same layout as qkv. scratch: fp32 [batch][heads][seq] (row dot products D). */
+/* Backward: dqkv bf16, same layout as qkv. `scratch` is caller-provided device memory of
+ * b200_attention_bwd_scratch_bytes() bytes, 16-byte aligned: the fp32 dQ accumulator that the
+ * kv-tile CTAs add into, and the row dot products delta = sum(dO*O). It is overwritten. */
+long long b200_attention_bwd_scratch_bytes(int batch, int seq, int heads);
 int b200_attention_bwd(const void* qkv, const void* out, const void* dout, const float* lse,
-                       void* dqkv, float* scratch_delta, int batch, int seq, int heads,
-                       void* stream);
+                       void* dqkv, float* scratch, int batch, int seq, int heads, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * Fused collective + optimizer kernel over NVSwitch (csrc/comm.cu).

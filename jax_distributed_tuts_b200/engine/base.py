@@ -119,10 +119,6 @@ class SymmetricArena:
         if self.world > 1:
             import torch.distributed._symmetric_memory as symm_mem
             gname = dist.group.WORLD.group_name
-            try:
-                symm_mem.enable_symm_mem_for_group(gname)   # no-op / deprecated on recent versions
-            except Exception:  # noqa: BLE001
-                pass
             self.buf = symm_mem.empty(self.nbytes, dtype=torch.uint8, device=device)
             self.buf.zero_()
             hdl = symm_mem.rendezvous(self.buf, gname)

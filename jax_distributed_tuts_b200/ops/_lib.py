@@ -10,7 +10,7 @@ from typing import Optional
 
 from . import _build
 
-ABI_VERSION = 5
+ABI_VERSION = 6
 
 _lib: Optional[C.CDLL] = None
 
@@ -91,6 +91,9 @@ def _declare(lib: C.CDLL) -> None:
     lib.b200_abi_version.restype = C.c_int
     lib.b200_launch_count.restype = C.c_longlong
     lib.b200_reset_launch_count.restype = None
+    if hasattr(lib, "b200_attention_bwd_scratch_bytes"):
+        lib.b200_attention_bwd_scratch_bytes.restype = C.c_longlong
+        lib.b200_attention_bwd_scratch_bytes.argtypes = [C.c_int, C.c_int, C.c_int]
     sigs = {
         "b200_gemm_bf16": [C.POINTER(GemmArgs), vp],
         "b200_softmax_xent": [vp, i32, vp, i32, i32, f32, vp, i32, vp, vp, vp],

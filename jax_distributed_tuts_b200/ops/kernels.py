@@ -233,7 +233,13 @@ def attention_fwd(qkv, out, lse, batch: int, seq: int, heads: int):
     return out
 
 
-def attention_bwd(qkv, out, dout, lse, dqkv, delta, batch: int, seq: int, heads: int):
+def attention_bwd_scratch_numel(batch: int, seq: int, heads: int) -> int:
+    """fp32 elements of scratch that ``attention_bwd`` needs."""
+    return int(_lib.lib().b200_attention_bwd_scratch_bytes(batch, seq, heads)) // 4
+
+
+def attention_bwd(qkv, out, dout, lse, dqkv, scratch, batch: int, seq: int, heads: int):
+    assert scratch.dtype == torch.float32 and scratch.numel() >= attention_bwd_scratch_numel(batch, seq, heads)
     _lib.check(_lib.lib().b200_attention_bwd(qkv.data_ptr(), out.data_ptr(), dout.data_ptr(), lse.data_ptr(),
-                                              dqkv.data_ptr(), delta.data_ptr(), batch, seq, heads, _stream()))
+                                              dqkv.data_ptr(), scratch.data_ptr(), batch, seq, heads, _stream()))
     return dqkv

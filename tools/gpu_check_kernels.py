@@ -346,8 +346,9 @@ def group_attention():
         ok &= _report(f"attention fwd b={b} t={t} h={h}", _rel_err(out.permute(0, 2, 1, 3), ref), 1.5e-2)
         dout = torch.randn(b, t, h, 64, device="cuda").bfloat16()
         ref.backward(dout.float().permute(0, 2, 1, 3))
-        dqkv = torch.empty_like(qkv); delta = torch.empty(b, h, t, device="cuda")
-        K.attention_bwd(qkv, out, dout, lse, dqkv, delta, b, t, h)
+        dqkv = torch.empty_like(qkv)
+        scratch = torch.empty(K.attention_bwd_scratch_numel(b, t, h), device="cuda")
+        K.attention_bwd(qkv, out, dout, lse, dqkv, scratch, b, t, h)
         for i, (nm, gref) in enumerate((("dq", q.grad), ("dk", k.grad), ("dv", v.grad))):
             ok &= _report(f"attention {nm}", _rel_err(dqkv[:, :, i].permute(0, 2, 1, 3), gref), 2e-2)
     return ok
