@@ -554,3 +554,55 @@ extern "C" int b200_attention_bwd(const void* qkv, const void* out, const void* 
   B200_CUDA(cudaGetLastError());
   return 0;
 }
+
+// =============================================================================================
+// Allocation-free variant of the attention backward (no counterpart in the reference).
+//
+// Who needs it: a host that cannot hand us scratch memory. Examples are a plain C/C++ program
+// or plugin that links this library without any device allocator of its own, and a runtime that
+// lays out all of its device memory once at start-up and then forbids cudaMalloc, because the
+// call synchronises the whole device and can fail late when the memory budget is already
+// spent. For them the scratch (fp32 dQ accumulator + the row dot products delta) lives in the
+// fixed array below instead of in a buffer the caller passes in.
+//
+// Costs and rules that follow from that choice:
+//   * every GPU that loads the library carries the array (about 4.1 MiB) until the process exits;
+//   * the problem must fit: batch * seq * heads <= B200_ATTN_BWD_NOALLOC_MAX_ROWS, larger
+//     problems are refused with an error, never truncated;
+//   * all calls on one GPU use the same array. It still holds the previous call's numbers; the
+//     part that has to start from zero (the dQ accumulator) is cleared by the first kernel of
+//     every call, the rest is fully overwritten before it is read. Two calls that run on the GPU
+//     at the same time (different streams) would trample each other: issue them on one stream or
+//     order them with events;
+//   * the first call on each device looks the array's device address up (cudaGetSymbolAddress);
+//     make that first call before starting any stream capture. Later calls only launch kernels.
+// It calls no cudaMalloc/cudaFree and no library routine that allocates.
+// =============================================================================================
+static __device__ __align__(256) float g_attn_bwd_scratch[B200_ATTN_BWD_NOALLOC_MAX_ROWS * (64 + 1)];
+
+extern "C" int b200_attention_bwd_noalloc(const void* qkv, const void* out, const void* dout, const float* lse,
+                                          void* dqkv, int batch, int seq, int heads, void* stream) {
+  int rc = check_attn_args(batch, seq, heads);
+  if (rc) return rc;
+  const long long rows = (long long)batch * seq * heads;
+  B200_REQUIRE(rows <= B200_ATTN_BWD_NOALLOC_MAX_ROWS,
+               "attention_bwd_noalloc: batch*seq*heads = %lld exceeds the built-in scratch (%d rows); "
+               "use b200_attention_bwd with caller-provided scratch",
+               rows, B200_ATTN_BWD_NOALLOC_MAX_ROWS);
+  // In host code `g_attn_bwd_scratch` is only a handle for the symbol, not a device address:
+  // resolve it once per device, with that device current, and keep the result.
+  constexpr int kMaxDevices = 64;
+  static float* dev_ptr[kMaxDevices] = {nullptr};
+  int dev = -1;
+  B200_CUDA(cudaGetDevice(&dev));
+  B200_REQUIRE(dev >= 0 && dev < kMaxDevices, "attention_bwd_noalloc: unsupported device ordinal %d", dev);
+  float* scratch = dev_ptr[dev];
+  if (scratch == nullptr) {
+    void* p = nullptr;
+    B200_CUDA(cudaGetSymbolAddress(&p, g_attn_bwd_scratch));
+    B200_REQUIRE(p != nullptr, "attention_bwd_noalloc: could not resolve the scratch symbol on device %d", dev);
+    scratch = static_cast<float*>(p);
+    dev_ptr[dev] = scratch;
+  }
+  return b200_attention_bwd(qkv, out, dout, lse, dqkv, scratch, batch, seq, heads, stream);
+}

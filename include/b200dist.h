@@ -174,6 +174,23 @@ long long b200_attention_bwd_scratch_bytes(int batch, int seq, int heads);
 int b200_attention_bwd(const void* qkv, const void* out, const void* dout, const float* lse,
                        void* dqkv, float* scratch, int batch, int seq, int heads, void* stream);
 
+/* Attention backward for callers that cannot allocate (this entry point has no counterpart in
+ * the reference). Same maths and outputs as b200_attention_bwd, but the scratch sits in a fixed
+ * device array inside the library, so the caller passes only inputs and outputs. Meant for hosts
+ * without a device allocator of their own (a bare C program, a plugin) and for runtimes that
+ * plan device memory once and forbid cudaMalloc afterwards.
+ *   limit   batch*seq*heads <= B200_ATTN_BWD_NOALLOC_MAX_ROWS, else an error is returned;
+ *   cost    ~4.1 MiB of device memory per GPU for the life of the process;
+ *   sharing one array per GPU, reused by every call: calls that overlap on the GPU race, so keep
+ *           them on one stream (or order them with events); nothing needs pre-zeroing, each call
+ *           clears what it accumulates into;
+ *   set-up  the first call on a device resolves the array's address; do it before any stream
+ *           capture begins.
+ * It performs no cudaMalloc/cudaFree and calls no allocating library routine. */
+#define B200_ATTN_BWD_NOALLOC_MAX_ROWS 16384
+int b200_attention_bwd_noalloc(const void* qkv, const void* out, const void* dout, const float* lse,
+                               void* dqkv, int batch, int seq, int heads, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * Fused collective + optimizer kernel over NVSwitch (csrc/comm.cu).
  *
