@@ -273,16 +273,19 @@ __host__ __device__ __forceinline__ uint32_t hash32(uint32_t x) {
   x ^= x >> 16;
   return x;
 }
-// keep-decision for element `idx` (row-major flat index of the activation matrix).
-// thresh16 = round(keep_prob * 65536).
-__host__ __device__ __forceinline__ bool dropout_keep(uint64_t seed, uint64_t idx,
-                                                      uint32_t thresh16) {
-  uint64_t pair = idx >> 1;
-  uint32_t h = hash32(static_cast<uint32_t>(pair) ^ static_cast<uint32_t>(seed)) ^
-               hash32(static_cast<uint32_t>(pair >> 32) + static_cast<uint32_t>(seed >> 32));
-  h = hash32(h);
-  uint32_t u = (idx & 1) ? (h >> 16) : (h & 0xFFFFu);
-  return u < thresh16;
+// Keep-decisions for the 4 elements (row, 4*colgroup .. 4*colgroup+3) of an activation matrix:
+// bit j of the result is set when element j is kept. Three 32-bit hashes give four 16-bit
+// uniforms; thresh16 = round(keep_prob * 65536). rng.dropout_mask (Python) computes the same.
+__host__ __device__ __forceinline__ uint32_t dropout_keep4(uint64_t seed, uint32_t row, uint32_t colgroup,
+                                                           uint32_t thresh16) {
+  const uint32_t k0 = hash32(static_cast<uint32_t>(seed) ^ (row * 0x9E3779B1u) ^ (colgroup * 0x85EBCA77u));
+  const uint32_t k1 = hash32(k0 ^ static_cast<uint32_t>(seed >> 32));
+  const uint32_t k2 = hash32(k1 + 0x6C8E9CF5u);
+  return ((k1 & 0xFFFFu) < thresh16 ? 1u : 0u) | ((k1 >> 16) < thresh16 ? 2u : 0u) |
+         ((k2 & 0xFFFFu) < thresh16 ? 4u : 0u) | ((k2 >> 16) < thresh16 ? 8u : 0u);
+}
+__host__ __device__ __forceinline__ bool dropout_keep(uint64_t seed, uint32_t row, uint32_t col, uint32_t thresh16) {
+  return (dropout_keep4(seed, row, col >> 2, thresh16) >> (col & 3)) & 1u;
 }
 
 __device__ __forceinline__ float warp_sum(float v) {

@@ -299,7 +299,7 @@ __global__ void act_dropout_kernel(const __nv_bfloat16* __restrict__ x, const __
       float d = act == B200_ACT_SILU ? silu_grad_f(xv) : act == B200_ACT_GELU ? gelu_grad_f(xv) : 1.0f;
       v = gy * d;
     }
-    if (key != nullptr) v = dropout_keep(seed, static_cast<uint64_t>(i), thresh16) ? v * scale : 0.f;
+    if (key != nullptr) v = dropout_keep(seed, static_cast<uint32_t>(r), static_cast<uint32_t>(c), thresh16) ? v * scale : 0.f;
     out[off] = __float2bfloat16_rn(v);
   }
 }

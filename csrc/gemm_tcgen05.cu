@@ -19,7 +19,7 @@ namespace b200 {
 constexpr int BM = 128;
 constexpr int BK = 64;       // 64 bf16 = one 128-byte swizzle row
 constexpr int UMMA_K = 16;
-constexpr int GEMM_THREADS = 192;
+constexpr int GEMM_THREADS = 320;   // TMA warp + MMA warp + 8 epilogue warps
 
 struct TmapSet {
   CUtensorMap m[8];
@@ -55,10 +55,11 @@ struct GemmCfg {
   static constexpr int A_BYTES = BM * BK * 2;
   static constexpr int B_BYTES = BN * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = (BN == 256) ? 4 : (BN == 128) ? 6 : 8;
+  static constexpr int STAGES = (BN == 256) ? 4 : (BN == 128) ? 5 : 6;
+  static constexpr int EPI_STAGE_BYTES = 8 * 32 * 32 * 4 + 8 * 16 * 8;   // per-warp 32x32 fp32 transpose buffers + dropout seed tables
   static constexpr uint32_t TMEM_COLS = (2 * BN <= 32) ? 32 : (2 * BN <= 64) ? 64 : (2 * BN <= 128) ? 128 : (2 * BN <= 256) ? 256 : 512;
-  static constexpr int BAR_BYTES = (2 * STAGES + 4) * 8 + 16;
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + BAR_BYTES + 1024;  // + alignment slack
+  static constexpr int BAR_BYTES = 256;   // (2*STAGES + 4) mbarriers + the TMEM base address, 16-byte multiple
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + BAR_BYTES + EPI_STAGE_BYTES + 1024;  // + alignment slack
 };
 
 struct TileCoord {
@@ -137,7 +138,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tmem_full[s], 1);
-      mbar_init(&tmem_empty[s], 4);
+      mbar_init(&tmem_empty[s], 8);
     }
     mbar_fence_init();
   }
@@ -234,13 +235,27 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
       }
     }
   } else {
-    // ===================== epilogue (warps 2..5) =====================
-    const int quad = warp & 3;  // TMEM lane quadrant this warp may read
-    uint64_t key = 0, seed = 0;
+    // ===================== epilogue (warps 2..9) =====================
+    // Two warps per TMEM lane quadrant; each takes half of the tile's columns. A 32-row x 32-col
+    // fp32 chunk goes TMEM -> registers (thread = row) -> per-warp swizzled staging in shared
+    // memory -> registers again with 8 lanes per row (lane = 4 consecutive columns), so that every
+    // global access of the epilogue (bias, saved pre-activation, residual, output) is a
+    // row-contiguous vector access and the element-wise math runs on all 32 lanes whatever M is.
+    const int ew = warp - 2;
+    const int quad = warp & 3;          // TMEM lane quadrant this warp may read
+    const int half = ew >> 2;           // which half of the tile's columns
+    float* stage = reinterpret_cast<float*>(smem + STAGES * Cfg::STAGE_BYTES + Cfg::BAR_BYTES) + ew * (32 * 32);
+    const int lrow = lane >> 3;         // row within a group of 4 rows
+    const int lchunk = lane & 7;        // 16-byte chunk (4 columns) within the 32-column row
+    uint64_t seed = 0;
+    uint64_t* seed_tab = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE_BYTES + Cfg::BAR_BYTES + 8 * 32 * 32 * 4) + ew * 16;
     if (p.drop_key != nullptr) {
-      key = *p.drop_key;
+      const uint64_t key = *p.drop_key;
       seed = mix64(key ^ p.drop_salt);
+      if (lane < p.drop_nsalt) seed_tab[lane] = mix64(key ^ p.drop_salts[lane]);   // one RNG stream per minibatch
+      __syncwarp();
     }
+    constexpr int CHUNKS = BN / 64;     // 32-column chunks per warp
     int local = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
       const int as = local & 1;
@@ -248,152 +263,144 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
       TileCoord tc = tile_coord(p, tile, m_tiles, BN);
       mbar_wait(&tmem_full[as], aphase);
       tc_fence_after();
-      const int row = tc.m0 + quad * 32 + lane;
-      const bool row_ok = row < p.M;
-      int drop_row = row;
-      if (p.drop_key != nullptr && p.drop_nsalt > 0) {
-        int blk = row / p.drop_rows_per_salt;
-        drop_row = row - blk * p.drop_rows_per_salt;
-        seed = mix64(key ^ p.drop_salts[blk < p.drop_nsalt ? blk : p.drop_nsalt - 1]);
-      }
-      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + as * BN;
+      const int row_base = tc.m0 + quad * 32;
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + as * BN + half * (BN / 2);
+      const int col_base = tc.n0 + half * (BN / 2);
+      const bool warp_active = row_base < p.M && col_base < tc.n_limit;
+      uint32_t r[32];
+      if (warp_active) tmem_ld_32x32b_x32(taddr, r);
 #pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
-        const int col0 = tc.n0 + c * 32;
-        if (col0 >= tc.n_limit) break;  // warp-uniform
-        uint32_t r[32];
-        tmem_ld_32x32b_x32(taddr + c * 32, r);
+      for (int c = 0; c < CHUNKS; ++c) {
+        const int col0 = col_base + c * 32;
+        if (!warp_active || col0 >= tc.n_limit) break;  // warp-uniform
         tmem_ld_wait();
-        // keep the warp converged around the .sync.aligned TMEM loads: predicate, don't branch out
-        if (row_ok) {
+        // registers (thread = row) -> staging, 16-byte chunks XOR-swizzled by row: conflict-free
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          const int col = col0 + g * 8;
-          if (col >= tc.n_limit) break;
-          const bool full8 = col + 8 <= tc.n_limit;
-          float v[8];
+        for (int j = 0; j < 8; ++j) {
+          float4 v4 = make_float4(__uint_as_float(r[j * 4 + 0]), __uint_as_float(r[j * 4 + 1]),
+                                  __uint_as_float(r[j * 4 + 2]), __uint_as_float(r[j * 4 + 3]));
+          *reinterpret_cast<float4*>(stage + lane * 32 + ((j ^ (lane & 7)) << 2)) = v4;
+        }
+        __syncwarp();
+        // prefetch the next chunk from TMEM while this one is being processed
+        if (c + 1 < CHUNKS && col0 + 32 < tc.n_limit) tmem_ld_32x32b_x32(taddr + (c + 1) * 32, r);
+        const int col = col0 + lchunk * 4;
+        const bool full4 = col + 4 <= tc.n_limit;
+        const bool col_ok = col < tc.n_limit;
+        float bias4[4] = {0.f, 0.f, 0.f, 0.f};
+        if (!p.bwd && p.bias != nullptr && col_ok) {
 #pragma unroll
-          for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[g * 8 + j]) * p.alpha;
+          for (int j = 0; j < 4; ++j)
+            if (col + j < tc.n_limit) bias4[j] = __bfloat162float(p.bias[col + j]);
+        }
+#pragma unroll 2
+        for (int i = 0; i < 8; ++i) {
+          const int lr = i * 4 + lrow;          // row within the warp's 32 rows
+          const int row = row_base + lr;
+          if (row_base + i * 4 >= p.M) break;   // warp-uniform: nothing left in this tile
+          if (row >= p.M || !col_ok) continue;
+          const float4 a4 = *reinterpret_cast<const float4*>(stage + lr * 32 + ((lchunk ^ (lr & 7)) << 2));
+          float v[4] = {a4.x * p.alpha, a4.y * p.alpha, a4.z * p.alpha, a4.w * p.alpha};
           if (!p.bwd) {
-            if (p.bias != nullptr) {
 #pragma unroll
-              for (int j = 0; j < 8; ++j)
-                if (col + j < tc.n_limit) v[j] += __bfloat162float(p.bias[col + j]);
-            }
+            for (int j = 0; j < 4; ++j) v[j] += bias4[j];
             if (p.pre != nullptr) {
               __nv_bfloat16* pp = p.pre + static_cast<size_t>(row) * p.ldpre + col;
-              if (full8 && p.vec_pre) {
-                uint4 w;
-                __nv_bfloat162 t0 = __floats2bfloat162_rn(v[0], v[1]);
-                __nv_bfloat162 t1 = __floats2bfloat162_rn(v[2], v[3]);
-                __nv_bfloat162 t2 = __floats2bfloat162_rn(v[4], v[5]);
-                __nv_bfloat162 t3 = __floats2bfloat162_rn(v[6], v[7]);
-                w.x = *reinterpret_cast<uint32_t*>(&t0);
-                w.y = *reinterpret_cast<uint32_t*>(&t1);
-                w.z = *reinterpret_cast<uint32_t*>(&t2);
-                w.w = *reinterpret_cast<uint32_t*>(&t3);
-                *reinterpret_cast<uint4*>(pp) = w;
+              __nv_bfloat162 t0 = __floats2bfloat162_rn(v[0], v[1]), t1 = __floats2bfloat162_rn(v[2], v[3]);
+              if (full4 && p.vec_pre) {
+                *reinterpret_cast<uint2*>(pp) = make_uint2(*reinterpret_cast<uint32_t*>(&t0), *reinterpret_cast<uint32_t*>(&t1));
               } else {
+                __nv_bfloat16 tv[4] = {t0.x, t0.y, t1.x, t1.y};
 #pragma unroll
-                for (int j = 0; j < 8; ++j)
-                  if (col + j < tc.n_limit) pp[j] = __float2bfloat16_rn(v[j]);
+                for (int j = 0; j < 4; ++j)
+                  if (col + j < tc.n_limit) pp[j] = tv[j];
               }
               // the activation sees the value as it was stored (bf16), like the backward will
-#pragma unroll
-              for (int j = 0; j < 8; ++j) v[j] = __bfloat162float(__float2bfloat16_rn(v[j]));
+              v[0] = __bfloat162float(t0.x); v[1] = __bfloat162float(t0.y);
+              v[2] = __bfloat162float(t1.x); v[3] = __bfloat162float(t1.y);
             }
             if (p.act == B200_ACT_SILU) {
 #pragma unroll
-              for (int j = 0; j < 8; ++j) v[j] = silu_f(v[j]);
+              for (int j = 0; j < 4; ++j) v[j] = silu_f(v[j]);
             } else if (p.act == B200_ACT_GELU) {
 #pragma unroll
-              for (int j = 0; j < 8; ++j) v[j] = gelu_f(v[j]);
+              for (int j = 0; j < 4; ++j) v[j] = gelu_f(v[j]);
             }
           } else if (p.aux != nullptr) {
             const __nv_bfloat16* ap = p.aux + static_cast<size_t>(row) * p.ldaux + col;
-            float x[8];
-            if (full8 && p.vec_aux) {
-              uint4 w = *reinterpret_cast<const uint4*>(ap);
+            float x[4];
+            if (full4 && p.vec_aux) {
+              const uint2 w = *reinterpret_cast<const uint2*>(ap);
               x[0] = bf16_bits_to_f(w.x & 0xFFFF); x[1] = bf16_bits_to_f(w.x >> 16);
               x[2] = bf16_bits_to_f(w.y & 0xFFFF); x[3] = bf16_bits_to_f(w.y >> 16);
-              x[4] = bf16_bits_to_f(w.z & 0xFFFF); x[5] = bf16_bits_to_f(w.z >> 16);
-              x[6] = bf16_bits_to_f(w.w & 0xFFFF); x[7] = bf16_bits_to_f(w.w >> 16);
             } else {
 #pragma unroll
-              for (int j = 0; j < 8; ++j)
-                x[j] = (col + j < tc.n_limit) ? __bfloat162float(ap[j]) : 0.0f;
+              for (int j = 0; j < 4; ++j) x[j] = (col + j < tc.n_limit) ? __bfloat162float(ap[j]) : 0.0f;
             }
             if (p.act == B200_ACT_SILU) {
 #pragma unroll
-              for (int j = 0; j < 8; ++j) v[j] *= silu_grad_f(x[j]);
+              for (int j = 0; j < 4; ++j) v[j] *= silu_grad_f(x[j]);
             } else if (p.act == B200_ACT_GELU) {
 #pragma unroll
-              for (int j = 0; j < 8; ++j) v[j] *= gelu_grad_f(x[j]);
+              for (int j = 0; j < 4; ++j) v[j] *= gelu_grad_f(x[j]);
             }
           }
           if (p.drop_key != nullptr) {
-            const uint64_t base = static_cast<uint64_t>(drop_row) * static_cast<uint64_t>(p.N) + col;
+            int drow = row;
+            uint64_t sd = seed;
+            if (p.drop_nsalt > 0) {
+              int blk = row / p.drop_rows_per_salt;
+              drow = row - blk * p.drop_rows_per_salt;
+              sd = seed_tab[blk < p.drop_nsalt ? blk : p.drop_nsalt - 1];
+            }
+            const uint32_t keep = dropout_keep4(sd, static_cast<uint32_t>(drow), static_cast<uint32_t>(col) >> 2,
+                                                p.drop_thresh16);
 #pragma unroll
-            for (int j = 0; j < 8; ++j)
-              v[j] = dropout_keep(seed, base + j, p.drop_thresh16) ? v[j] * p.drop_scale : 0.0f;
+            for (int j = 0; j < 4; ++j) v[j] = ((keep >> j) & 1u) ? v[j] * p.drop_scale : 0.0f;
           }
           if (!p.bwd && p.resid != nullptr) {
             const __nv_bfloat16* rp = p.resid + static_cast<size_t>(row) * p.ldres + col;
-            if (full8 && p.vec_res) {
-              uint4 w = *reinterpret_cast<const uint4*>(rp);
+            if (full4 && p.vec_res) {
+              const uint2 w = *reinterpret_cast<const uint2*>(rp);
               v[0] += bf16_bits_to_f(w.x & 0xFFFF); v[1] += bf16_bits_to_f(w.x >> 16);
               v[2] += bf16_bits_to_f(w.y & 0xFFFF); v[3] += bf16_bits_to_f(w.y >> 16);
-              v[4] += bf16_bits_to_f(w.z & 0xFFFF); v[5] += bf16_bits_to_f(w.z >> 16);
-              v[6] += bf16_bits_to_f(w.w & 0xFFFF); v[7] += bf16_bits_to_f(w.w >> 16);
             } else {
 #pragma unroll
-              for (int j = 0; j < 8; ++j)
+              for (int j = 0; j < 4; ++j)
                 if (col + j < tc.n_limit) v[j] += __bfloat162float(rp[j]);
             }
           }
           // ---- store ----
           if (p.d_fp32) {
             float* dp = reinterpret_cast<float*>(p.d) + static_cast<size_t>(row) * p.ldd + col;
-            if (full8 && p.vec_d) {
-              float4 o0 = make_float4(v[0], v[1], v[2], v[3]);
-              float4 o1 = make_float4(v[4], v[5], v[6], v[7]);
+            if (full4 && p.vec_d) {
+              float4 o = make_float4(v[0], v[1], v[2], v[3]);
               if (p.accumulate) {
-                float4 c0 = *reinterpret_cast<float4*>(dp);
-                float4 c1 = *reinterpret_cast<float4*>(dp + 4);
-                o0.x += c0.x; o0.y += c0.y; o0.z += c0.z; o0.w += c0.w;
-                o1.x += c1.x; o1.y += c1.y; o1.z += c1.z; o1.w += c1.w;
+                const float4 c4 = *reinterpret_cast<const float4*>(dp);
+                o.x += c4.x; o.y += c4.y; o.z += c4.z; o.w += c4.w;
               }
-              *reinterpret_cast<float4*>(dp) = o0;
-              *reinterpret_cast<float4*>(dp + 4) = o1;
+              *reinterpret_cast<float4*>(dp) = o;
             } else {
 #pragma unroll
-              for (int j = 0; j < 8; ++j)
+              for (int j = 0; j < 4; ++j)
                 if (col + j < tc.n_limit) dp[j] = p.accumulate ? dp[j] + v[j] : v[j];
             }
           } else {
-            __nv_bfloat16* dp =
-                reinterpret_cast<__nv_bfloat16*>(p.d) + static_cast<size_t>(row) * p.ldd + col;
-            if (full8 && p.vec_d) {
-              uint4 w;
-              __nv_bfloat162 t0 = __floats2bfloat162_rn(v[0], v[1]);
-              __nv_bfloat162 t1 = __floats2bfloat162_rn(v[2], v[3]);
-              __nv_bfloat162 t2 = __floats2bfloat162_rn(v[4], v[5]);
-              __nv_bfloat162 t3 = __floats2bfloat162_rn(v[6], v[7]);
-              w.x = *reinterpret_cast<uint32_t*>(&t0);
-              w.y = *reinterpret_cast<uint32_t*>(&t1);
-              w.z = *reinterpret_cast<uint32_t*>(&t2);
-              w.w = *reinterpret_cast<uint32_t*>(&t3);
-              *reinterpret_cast<uint4*>(dp) = w;
+            __nv_bfloat16* dp = reinterpret_cast<__nv_bfloat16*>(p.d) + static_cast<size_t>(row) * p.ldd + col;
+            __nv_bfloat162 t0 = __floats2bfloat162_rn(v[0], v[1]), t1 = __floats2bfloat162_rn(v[2], v[3]);
+            if (full4 && p.vec_d) {
+              *reinterpret_cast<uint2*>(dp) = make_uint2(*reinterpret_cast<uint32_t*>(&t0), *reinterpret_cast<uint32_t*>(&t1));
             } else {
+              __nv_bfloat16 tv[4] = {t0.x, t0.y, t1.x, t1.y};
 #pragma unroll
-              for (int j = 0; j < 8; ++j)
-                if (col + j < tc.n_limit) dp[j] = __float2bfloat16_rn(v[j]);
+              for (int j = 0; j < 4; ++j)
+                if (col + j < tc.n_limit) dp[j] = tv[j];
             }
           }
         }
-        }  // row_ok
-        __syncwarp();
+        __syncwarp();   // staging is reused by the next chunk
       }
+      if (warp_active) tmem_ld_wait();
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tmem_empty[as]);
@@ -507,15 +514,13 @@ extern "C" int b200_gemm_bf16(const b200_gemm_args* args, void* stream) {
   float keep = 1.0f - a.drop_rate;
   dev.drop_thresh16 = (uint32_t)(keep * 65536.0f + 0.5f);
   dev.drop_scale = keep > 0.f ? 1.0f / keep : 0.f;
-  int dvec = a.d_fp32 ? 4 : 8;
-  dev.vec_d = aligned16(a.d) && (a.ldd % dvec == 0) &&
-              (a.b_shard_mode != 2 || a.b_shard_len % 8 == 0);
-  dev.vec_pre = a.pre && aligned16(a.pre) && (a.ldpre % 8 == 0) && dev.vec_d;
-  dev.vec_aux = a.aux && aligned16(a.aux) && (a.ldaux % 8 == 0) && dev.vec_d;
-  dev.vec_res = a.resid && aligned16(a.resid) && (a.ldres % 8 == 0) && dev.vec_d;
-  if (a.b_shard_mode == 2 && a.b_shard_len % 8 != 0) {
-    dev.vec_pre = dev.vec_aux = dev.vec_res = 0;
-  }
+  // the epilogue moves 4 elements per lane: 16 bytes of fp32 or 8 bytes of bf16; column offsets
+  // are multiples of 4 unless an N-shard boundary is not
+  const bool cols_ok = a.b_shard_mode != 2 || a.b_shard_len % 4 == 0;
+  dev.vec_d = aligned16(a.d) && (a.ldd % 4 == 0) && cols_ok;
+  dev.vec_pre = a.pre && aligned16(a.pre) && (a.ldpre % 4 == 0) && cols_ok;
+  dev.vec_aux = a.aux && aligned16(a.aux) && (a.ldaux % 4 == 0) && cols_ok;
+  dev.vec_res = a.resid && aligned16(a.resid) && (a.ldres % 4 == 0) && cols_ok;
 
   int bn = a.block_n;
   if (bn == 0) {

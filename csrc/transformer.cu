@@ -80,7 +80,8 @@ layernorm_fwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* _
 __global__ void __launch_bounds__(256)
 layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
                      const __nv_bfloat16* __restrict__ gamma, const float* __restrict__ mean,
-                     const float* __restrict__ rstd, __nv_bfloat16* __restrict__ dx, float* __restrict__ dgamma,
+                     const float* __restrict__ rstd, const __nv_bfloat16* __restrict__ dresid,
+                     __nv_bfloat16* __restrict__ dx, float* __restrict__ dgamma,
                      float* __restrict__ dbeta, int rows, int cols) {
   extern __shared__ float sm[];
   float* s_dg = sm;
@@ -125,6 +126,12 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
         float o[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) o[j] = rs * (dg[c][j] - s1 - xh[c][j] * s2);
+        if (dresid != nullptr) {   // gradient arriving through the residual connection
+          float rr[8];
+          unpack8(reinterpret_cast<const uint4*>(dresid + static_cast<size_t>(row) * cols)[idx], rr);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[j] += rr[j];
+        }
         or_[idx] = pack8(o);
       }
     }
@@ -203,16 +210,16 @@ extern "C" int b200_layernorm_fwd(const void* x, const void* gamma, const void* 
 }
 
 extern "C" int b200_layernorm_bwd(const void* dy, const void* x, const void* gamma, const float* mean,
-                                  const float* rstd, void* dx, float* dgamma, float* dbeta, int rows, int cols,
-                                  void* stream) {
+                                  const float* rstd, const void* dresid, void* dx, float* dgamma, float* dbeta,
+                                  int rows, int cols, void* stream) {
   B200_REQUIRE(rows > 0 && cols > 0 && cols % 8 == 0 && cols <= 2048, "layernorm: cols=%d must be a multiple of 8, <= 2048", cols);
   int blocks = (rows + 7) / 8;
   int cap = num_sms() * 2;
   if (blocks > cap) blocks = cap;
   layernorm_bwd_kernel<<<blocks, 256, 2 * cols * sizeof(float), static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(x),
-      static_cast<const __nv_bfloat16*>(gamma), mean, rstd, static_cast<__nv_bfloat16*>(dx), dgamma, dbeta, rows,
-      cols);
+      static_cast<const __nv_bfloat16*>(gamma), mean, rstd, static_cast<const __nv_bfloat16*>(dresid),
+      static_cast<__nv_bfloat16*>(dx), dgamma, dbeta, rows, cols);
   count_launch();
   B200_CUDA(cudaGetLastError());
   return 0;

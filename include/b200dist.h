@@ -16,7 +16,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 6
+#define B200_ABI_VERSION 7
 
 const char* b200_last_error(void);
 int b200_abi_version(void);
@@ -150,10 +150,11 @@ int b200_act_dropout_bwd(const void* x, const void* dy, void* dx, int64_t rows, 
  * mean/rstd fp32 [rows] saved for backward. */
 int b200_layernorm_fwd(const void* x, const void* gamma, const void* beta, void* y, float* mean,
                        float* rstd, int rows, int cols, float eps, void* stream);
-/* dx bf16; dgamma/dbeta fp32 [cols] accumulated (+=). */
+/* dx bf16 = LN-backward(dy) (+ dresid if not NULL: the gradient of the residual branch; must not
+ * alias dx); dgamma/dbeta fp32 [cols] accumulated (+=). */
 int b200_layernorm_bwd(const void* dy, const void* x, const void* gamma, const float* mean,
-                       const float* rstd, void* dx, float* dgamma, float* dbeta, int rows, int cols,
-                       void* stream);
+                       const float* rstd, const void* dresid, void* dx, float* dgamma, float* dbeta,
+                       int rows, int cols, void* stream);
 /* out[b,t,:] = wte[tok[b,t],:] + wpe[t,:]   (bf16 tables, int64 tokens) */
 int b200_embedding_fwd(const int64_t* tokens, const void* wte, const void* wpe, void* out,
                        int batch, int seq, int dim, void* stream);

@@ -23,6 +23,7 @@ from ..ops import _lib
 from ..ops import kernels as K
 from ..ops._lib import AdamWHParams, CommCtx, Seg
 from ..state import Batch, Metrics, TrainState
+from ..parallel.fsdp import choose_shard_dim
 from ..tree import Partitioned, Pytree
 
 
@@ -150,81 +151,344 @@ class SymmetricArena:
 
 
 class FusedEngine:
-    """Common machinery; subclasses provide the layout and the per-minibatch forward/backward."""
+    """Common machinery: flat symmetric buffers, shard planning (the reference's shard rule),
+    weight access for the GEMMs (in place from peer shards in FSDP mode), the fused
+    collective+optimizer launches, CUDA-graph capture, metrics and RNG bookkeeping.
+    Subclasses provide the leaf list and the forward/backward schedule.
+
+    Modes
+      dp    parameters replicated; every rank reduces + updates 1/world of each bucket and
+            multicasts the result (data_paral.py:210-217).
+      fsdp  leaves sharded over ``shard_axis`` by the reference's rule (param_sharding.py:89-113);
+            gradients are reduced over *all* ranks of the mesh (so on a 2-D ``(data, fsdp)`` mesh
+            the data-axis mean of ``sync_gradients``, param_sharding.py:293-322, is the same
+            launch), weights are read from the peers of the rank's shard group.
+    """
 
     metric_names = ("loss", "accuracy")
 
-    def __init__(self, mesh: Mesh, *, lr: float, b1: float = 0.9, b2: float = 0.999, eps: float = 1e-8,
-                 weight_decay: float = 1e-4, num_minibatches: int = 4, data_axis_name: str = "data",
-                 use_graph: bool = True, comm_blocks: int = 16):
+    def __init__(self, mesh: Mesh, *, mode: str = "dp", lr: float, b1: float = 0.9, b2: float = 0.999,
+                 eps: float = 1e-8, weight_decay: float = 1e-4, num_minibatches: int = 4,
+                 data_axis_name: str = "data", shard_axis: Optional[str] = None, min_weight_size: int = 2 ** 18,
+                 use_graph: bool = True, comm_blocks: int = 16, overlap: bool = True):
         if not torch.cuda.is_available():
             raise RuntimeError("the fused engine needs a CUDA device; use the generic tier on CPU")
         _lib.lib()  # fail loudly if the kernel library is missing
-        self.mesh = mesh
+        assert mode in ("dp", "fsdp")
+        self.mesh, self.mode = mesh, mode
         self.device = torch.device("cuda", torch.cuda.current_device())
         self.world, self.rank = mesh.size, mesh.rank
         self.hp = dict(lr=lr, beta1=b1, beta2=b2, eps=eps, weight_decay=weight_decay)
         self.num_minibatches = num_minibatches
         self.data_axis_name = data_axis_name
+        self.shard_axis = shard_axis or data_axis_name
+        self.S = mesh.axis_size(self.shard_axis) if mode == "fsdp" else 1
+        self.sidx = mesh.axis_index(self.shard_axis) if mode == "fsdp" else 0
+        self.shard_peer_ranks = list(mesh.group_ranks(self.shard_axis)) if (mode == "fsdp" and self.S > 1) else [self.rank]
+        self.min_weight_size = min_weight_size
         self.use_graph = use_graph
         self.comm_blocks = comm_blocks
+        self.overlap = overlap and self.world > 1
         self.graph: Optional[torch.cuda.CUDAGraph] = None
         self._last_metrics = None
         self._counts = [0, 0]
         self.side_stream = torch.cuda.Stream()
         self.steps_done = 0
+        self._keep: list = []
 
-    # -- buffers shared by all engines -------------------------------------------------------
-    def _alloc_common(self) -> None:
-        d = self.device
+    # ---------------------------------------------------------------- buffers -----------------
+    def _setup_buffers(self, layout: FlatLayout) -> None:
+        self.layout = layout
+        d, n, W = self.device, layout.total, self.world
         self.step_count = torch.zeros(1, dtype=torch.int32, device=d)
         self.step_metrics = torch.zeros(8, dtype=torch.float32, device=d)
         self.metrics_acc = torch.zeros(8, dtype=torch.float32, device=d)
+        sizes = {"grad": n * 4, "signal": _lib.SIGNAL_WORDS * 4}
+        if self.mode == "dp":
+            sizes.update({"param": n * 4, "bf16": n * 2})
+        else:
+            self._plan_shards()
+            sizes.update({"bf16": self.local_total * 2})   # every rank's bf16 slices at the same local offsets
+        self.arena = SymmetricArena(sizes, self.mesh, d)
+        self.g32 = self.arena.tensor("grad", torch.float32, n)
+        if self.mode == "dp":
+            self.p32 = self.arena.tensor("param", torch.float32, n)
+            self.pb = self.arena.tensor("bf16", torch.bfloat16, n)
+            self.m = torch.zeros(n // W, dtype=torch.float32, device=d)
+            self.v = torch.zeros(n // W, dtype=torch.float32, device=d)
+        else:
+            self.p_loc = torch.zeros(self.local_total, dtype=torch.float32, device=d)
+            self.m = torch.zeros(self.local_total, dtype=torch.float32, device=d)
+            self.v = torch.zeros(self.local_total, dtype=torch.float32, device=d)
+            self.pb = self.arena.tensor("bf16", torch.bfloat16, self.local_total)
+            self._setup_bias_gather()
+        self.ctx = self._make_ctx(self.arena, "grad", "param" if self.mode == "dp" else None, "bf16", "signal")
+        self._build_segments()
 
+    def _plan_shards(self) -> None:
+        self.shard_dim: Dict[str, Optional[int]] = {}
+        self.loc_off: Dict[str, int] = {}
+        loc = 0
+        for path, sp in self.layout.leaves.items():
+            numel = 1
+            for s_ in sp.shape:
+                numel *= s_
+            dim = None
+            if numel > self.min_weight_size:
+                dim = choose_shard_dim(sp.shape, (None,) * len(sp.shape), self.S)
+            self.shard_dim[path] = dim
+            self.loc_off[path] = loc
+            loc = _round_up(loc + self._local_numel(path), 64)
+        self.local_total = _round_up(loc, 64)
+
+    def _local_shape2d(self, path: str) -> Tuple[int, int, int]:
+        """(rows, cols, ld) of this rank's slice of a leaf in padded 2-D form."""
+        sp = self.layout.leaves[path]
+        dim = self.shard_dim[path]
+        if dim is None:
+            return sp.rows, sp.cols, sp.ld
+        if len(sp.shape) == 1 or dim == len(sp.shape) - 1:
+            cols = sp.cols // self.S
+            return sp.rows, cols, _round_up(cols, 8)
+        assert dim == 0, "leaves are sharded on their first or last dimension"
+        return sp.rows // self.S, sp.cols, sp.ld
+
+    def _local_numel(self, path: str) -> int:
+        r, _, ld = self._local_shape2d(path)
+        return r * ld
+
+    def _local_view(self, buf: torch.Tensor, path: str) -> torch.Tensor:
+        r, c, ld = self._local_shape2d(path)
+        o = self.loc_off[path]
+        return buf[o: o + r * ld].view(r, ld)[:, :c]
+
+    def _setup_bias_gather(self) -> None:
+        """Sharded 1-D leaves (biases, norm scales) are re-assembled once per step by peer loads."""
+        from ..ops._lib import GatherSeg
+        self.bias_full: Dict[str, torch.Tensor] = {}
+        segs, off, spans = [], 0, {}
+        for path, sp in self.layout.leaves.items():
+            if len(sp.shape) == 1 and self.shard_dim[path] is not None:
+                per = sp.cols // self.S
+                segs.append(GatherSeg(self.loc_off[path] * 2, off, per * 2))
+                spans[path] = (off // 2, sp.cols)
+                off = _round_up(off + sp.cols * 2, 64)
+        self._bias_nseg = len(segs)
+        if segs:
+            self._bias_buf = torch.zeros(off // 2, dtype=torch.bfloat16, device=self.device)
+            self._bias_segs = self._segs_to_device(segs)
+            arr = (C.c_void_p * self.S)()
+            for i, r in enumerate(self.shard_peer_ranks):
+                arr[i] = self.arena.peer_ptrs[r] + self.arena.offsets["bf16"]
+            self._bias_peers = arr
+            self.bias_full = {k: self._bias_buf[o: o + n_] for k, (o, n_) in spans.items()}
+
+    def _gather_small(self) -> None:
+        if self.mode != "fsdp" or not self._bias_nseg:
+            return
+        _lib.check(_lib.lib().b200_peer_gather(C.cast(self._bias_peers, C.POINTER(C.c_void_p)), self.S,
+                                                self._bias_segs.data_ptr(), self._bias_nseg,
+                                                self._bias_buf.data_ptr(), 2,
+                                                torch.cuda.current_stream().cuda_stream))
+
+    # ---------------------------------------------------------------- parameters --------------
+    def load_flat_params(self, flat: Dict[str, torch.Tensor]) -> None:
+        """Loads *global* (unsharded) parameter values, path -> tensor; every rank passes the same
+        values (the reference initialises the full parameter on every device from one rng and keeps
+        its slice, param_sharding.py:227-241)."""
+        for path, sp in self.layout.leaves.items():
+            v = flat[path]
+            v = (v.value if isinstance(v, Partitioned) else v).to(self.device, dtype=torch.float32)
+            v2 = v.reshape(sp.rows, sp.cols)
+            if self.mode == "dp":
+                self.layout.view2d(self.p32, path).copy_(v2)
+                continue
+            dim = self.shard_dim[path]
+            r, c, ld = self._local_shape2d(path)
+            if dim is not None:
+                v2 = v2[:, self.sidx * c:(self.sidx + 1) * c] if c != sp.cols else v2[self.sidx * r:(self.sidx + 1) * r]
+            self._local_view(self.p_loc, path).copy_(v2)
+        if self.mode == "dp":
+            K.cast_f32_bf16(self.p32, self.pb)
+        else:
+            K.cast_f32_bf16(self.p_loc, self.pb)
+        torch.cuda.synchronize()
+        if self.world > 1:
+            dist.barrier()
+
+    def flat_params(self, gather: bool = True) -> Dict[str, object]:
+        """path -> fp32 tensor. DP: views of the replicated master. FSDP: full arrays gathered over
+        the shard axis (``gather=True``) or ``Partitioned`` boxes of the local slices."""
+        out: Dict[str, object] = {}
+        for path, sp in self.layout.leaves.items():
+            if self.mode == "dp":
+                out[path] = self.layout.view(self.p32, path)
+                continue
+            loc = self._local_view(self.p_loc, path)          # [rows, cols] view of the local slice
+            dim = self.shard_dim[path]
+            if len(sp.shape) == 1:
+                loc = loc.reshape(-1)
+            if dim is None:
+                out[path] = loc.reshape(sp.shape)
+            elif gather:
+                from ..comm import collectives as Cc
+                full = Cc.all_gather(loc.contiguous(), self.shard_axis, axis=dim, mesh=self.mesh) if self.S > 1 else loc
+                out[path] = full.reshape(sp.shape)
+            else:
+                names = tuple(self.shard_axis if i == dim else None for i in range(len(sp.shape)))
+                out[path] = Partitioned(loc, names)
+        return out
+
+    @staticmethod
+    def _nest(flat: Dict[str, object], order: Optional[Sequence[str]] = None) -> Dict:
+        out: Dict = {}
+        for path in (order or flat.keys()):
+            node = out
+            *parents, last = path.split("/")
+            for p_ in parents:
+                node = node.setdefault(p_, {})
+            node[last] = flat[path]
+        return out
+
+    def opt_state_tree(self) -> Tuple:
+        """optax-shaped optimizer state. DP keeps m/v only for the rank's 1/world slice of every
+        bucket (owner-update), FSDP for its shards; the tree exposes those flat slices."""
+        from ..optim.adamw import EmptyState, ScaleByAdamState
+        return (ScaleByAdamState(count=self.step_count, mu={"flat_slice": self.m}, nu={"flat_slice": self.v}),
+                EmptyState(), EmptyState())
+
+    # ---------------------------------------------------------------- collectives -------------
     def _make_ctx(self, arena: SymmetricArena, grad: str, param: Optional[str], bf16: Optional[str],
                   signal: str) -> CommCtx:
         ctx = CommCtx()
         ctx.rank, ctx.world = self.rank, self.world
-        self._keep = getattr(self, "_keep", [])
+
         def arr(name):
             a = arena.peer_ptr_array(name)
             self._keep.append(a)
             return C.cast(a, C.POINTER(C.c_void_p))
+
         ctx.peer_grad = arr(grad)
         if param:
             ctx.peer_param = arr(param)
             ctx.mc_param = arena.mc_ptr(param)
         if bf16:
             ctx.peer_bf16 = arr(bf16)
-            ctx.mc_bf16 = arena.mc_ptr(bf16)
+            if param:
+                ctx.mc_bf16 = arena.mc_ptr(bf16)
         ctx.peer_signal = arr(signal)
         ctx.mc_grad = arena.mc_ptr(grad)
         return ctx
 
-    def _segs_to_device(self, segs: List[Seg]) -> torch.Tensor:
+    def _segs_to_device(self, segs: List) -> torch.Tensor:
         raw = b"".join(bytes(s) for s in segs)
-        t = torch.frombuffer(bytearray(raw), dtype=torch.uint8).to(self.device)
-        return t
+        return torch.frombuffer(bytearray(raw), dtype=torch.uint8).to(self.device)
 
-    def _fused_update(self, ctx: CommCtx, segs_dev: torch.Tensor, nseg: int, *, broadcast: bool,
-                      p_local, bf16_local, m, v, grad_scale: float, bump: bool, with_metrics: bool) -> None:
+    def _build_segments(self) -> None:
+        W, r = self.world, self.rank
+        self.bucket_segs: List[Tuple[torch.Tensor, int]] = []
+        if self.mode == "dp":
+            for (b0, b1) in self.layout.bucket_ranges:
+                sl = (b1 - b0) // W
+                seg = Seg(src_off=b0 + r * sl, src_pitch=sl, dst_off=b0 + r * sl, loc_off=b0 // W, rows=1, row_len=sl)
+                self.bucket_segs.append((self._segs_to_device([seg]), 1))
+            return
+        per_bucket: Dict[int, List[Seg]] = {}
+        for path, sp in self.layout.leaves.items():
+            dim = self.shard_dim[path]
+            rws, c, ld = self._local_shape2d(path)
+            if dim is None:     # replicated leaf: every rank applies the same all-reduced update
+                seg = Seg(src_off=sp.offset, src_pitch=sp.ld, dst_off=0, loc_off=self.loc_off[path],
+                          rows=sp.rows, row_len=sp.ld)
+            elif c != sp.cols:  # sharded on the last dim: strided rows
+                assert ld == c, f"{path}: last-dim shards must be multiples of 8 wide"
+                seg = Seg(src_off=sp.offset + self.sidx * c, src_pitch=sp.ld, dst_off=0, loc_off=self.loc_off[path],
+                          rows=sp.rows, row_len=c)
+            else:               # sharded on rows: contiguous
+                seg = Seg(src_off=sp.offset + self.sidx * rws * sp.ld, src_pitch=sp.ld, dst_off=0,
+                          loc_off=self.loc_off[path], rows=rws, row_len=sp.ld)
+            per_bucket.setdefault(sp.bucket, []).append(seg)
+        order = sorted(per_bucket)
+        assert order == list(range(len(order))), "bucket ids must be 0..n-1"
+        for b in order:
+            self.bucket_segs.append((self._segs_to_device(per_bucket[b]), len(per_bucket[b])))
+
+    def _sync_bucket(self, b: int, last: bool) -> None:
+        """Fused reduce + mean + AdamW + publish of one gradient bucket (one launch)."""
+        segs, nseg = self.bucket_segs[b]
         hp = AdamWHParams(self.hp["lr"], self.hp["beta1"], self.hp["beta2"], self.hp["eps"],
-                          self.hp["weight_decay"], grad_scale)
+                          self.hp["weight_decay"], 1.0 / (self.num_minibatches * self.world))
         nmet = len(self.metric_names)
+        dp = self.mode == "dp"
         _lib.check(_lib.lib().b200_fused_reduce_adamw(
-            C.byref(ctx), segs_dev.data_ptr(), nseg, int(broadcast),
-            None if p_local is None else p_local.data_ptr(),
-            None if bf16_local is None else bf16_local.data_ptr(),
-            m.data_ptr(), v.data_ptr(), C.byref(hp), self.step_count.data_ptr(), int(bump),
-            self.step_metrics.data_ptr() if with_metrics else None,
-            self.metrics_acc.data_ptr() if with_metrics else None, nmet if with_metrics else 0,
-            self.comm_blocks, torch.cuda.current_stream().cuda_stream))
+            C.byref(self.ctx), segs.data_ptr(), nseg, int(dp),
+            None if dp else self.p_loc.data_ptr(), None if dp else self.pb.data_ptr(),
+            self.m.data_ptr(), self.v.data_ptr(), C.byref(hp), self.step_count.data_ptr(), int(last),
+            self.step_metrics.data_ptr() if last else None, self.metrics_acc.data_ptr() if last else None,
+            nmet if last else 0, self.comm_blocks, torch.cuda.current_stream().cuda_stream))
 
-    # -- step driver --------------------------------------------------------------------------
+    def _sync_bucket_async(self, b: int) -> None:
+        """Launches bucket ``b``'s fused update on the side stream, after everything already
+        queued on the current stream (its gradients), so it runs under the rest of the backward.
+        The fused launches share the signal words, hence they are serialised on the side stream."""
+        main = torch.cuda.current_stream()
+        self.side_stream.wait_stream(main)
+        with torch.cuda.stream(self.side_stream):
+            self._sync_bucket(b, last=False)
+
+    # ---------------------------------------------------------------- weights for GEMMs -------
+    def grad2d(self, path: str) -> torch.Tensor:
+        return self.layout.view2d(self.g32, path)
+
+    def grad1d(self, path: str) -> torch.Tensor:
+        return self.layout.view(self.g32, path)
+
+    def vec(self, path: str) -> torch.Tensor:
+        """bf16 working copy of a 1-D leaf (bias / norm scale), full length."""
+        if self.mode == "dp":
+            return self.layout.view(self.pb, path)
+        if self.shard_dim[path] is None:
+            return self._local_view(self.pb, path).reshape(-1)
+        return self.bias_full[path]
+
+    def _weight(self, path: str):
+        sp = self.layout.leaves[path]
+        if self.mode == "dp":
+            return self.layout.view2d(self.pb, path), {}, None
+        if self.shard_dim[path] is None or self.S == 1:
+            return self._local_view(self.pb, path), {}, None
+        r, c, ld = self._local_shape2d(path)
+        srcs = [self.arena.peer_ptrs[g] + self.arena.offsets["bf16"] + self.loc_off[path] * 2
+                for g in self.shard_peer_ranks]
+        last_dim = c != sp.cols
+        return srcs, dict(b_shape=(sp.rows, sp.cols), ldb=ld), (last_dim, c if last_dim else r)
+
+    def gemm_w(self, x: torch.Tensor, path: str, out: torch.Tensor, **kw) -> None:
+        """``out = epilogue(x @ W)`` with W the (in, out) kernel at ``path``. In FSDP mode W is read
+        from the peers' shards by the GEMM's TMA producer (all-gather fused into the GEMM;
+        reference: gather_params then Dense, param_sharding.py:146-175)."""
+        b, extra, shard = self._weight(path)
+        if shard is not None:
+            last_dim, shard_len = shard
+            extra.update(shard_mode=2 if last_dim else 1, shard_len=shard_len, rot=self.sidx)
+        K.gemm(x, b, out, b_mn=True, **extra, **kw)
+
+    def gemm_wT(self, dy: torch.Tensor, path: str, out: torch.Tensor, **kw) -> None:
+        """``out = epilogue(dy @ W^T)`` (dgrad): the (in, out) kernel is the K-major B operand."""
+        b, extra, shard = self._weight(path)
+        if shard is not None:
+            last_dim, shard_len = shard
+            extra.update(shard_mode=1 if last_dim else 2, shard_len=shard_len, rot=self.sidx)
+        K.gemm(dy, b, out, **extra, **kw)
+
+    # ---------------------------------------------------------------- step driver -------------
     def _load_batch(self, batch: Batch) -> None:  # pragma: no cover - interface
         raise NotImplementedError
 
     def _step_body(self) -> None:  # pragma: no cover - interface
+        raise NotImplementedError
+
+    def _rows_per_step(self) -> int:  # pragma: no cover - interface
         raise NotImplementedError
 
     def _run_step(self) -> None:
@@ -259,7 +523,6 @@ class FusedEngine:
     def train_step(self, state: TrainState, metrics: Optional[Metrics], batch: Batch) -> Tuple[TrainState, Metrics]:
         """``(state, metrics, batch) -> (state, metrics)`` like the reference's jitted steps. The
         state's buffers are updated in place; the returned state replaces the argument."""
-        # running metrics: continue in place if the caller passes back what we returned last
         if metrics is None or metrics is not self._last_metrics:
             self.metrics_acc.zero_()
             self._counts = [0, 0]
@@ -277,8 +540,16 @@ class FusedEngine:
             self._counts[i] += per_step
             out[name] = (self.metrics_acc[i], self._counts[i])
         self._last_metrics = out
-        new_state = dataclasses.replace(state, step=state.step + 1)
-        return new_state, out
+        return dataclasses.replace(state, step=state.step + 1), out
 
-    def _rows_per_step(self) -> int:  # pragma: no cover - interface
-        raise NotImplementedError
+    def make_state(self, model, rng: _rng.Key, params_tree: Optional[Dict] = None) -> TrainState:
+        from ..optim import adamw as _adamw
+        self.rng_base = rng.base.to(self.device).clone()
+        if rng.salt != 0:
+            self.rng_base = _rng.rebase(_rng.Key(self.rng_base, rng.salt)).base
+        key = _rng.Key(self.rng_base, 0)
+        return TrainState(step=0, apply_fn=model.apply, params=params_tree if params_tree is not None else self.params_tree(gather=False),
+                          tx=_adamw(self.hp["lr"]), opt_state=self.opt_state_tree(), rng=key, engine=self)
+
+    def params_tree(self, gather: bool = True) -> Dict:
+        return self._nest(self.flat_params(gather=gather))

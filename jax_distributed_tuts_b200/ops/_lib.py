@@ -10,7 +10,7 @@ from typing import Optional
 
 from . import _build
 
-ABI_VERSION = 6
+ABI_VERSION = 7
 
 _lib: Optional[C.CDLL] = None
 
@@ -107,7 +107,7 @@ def _declare(lib: C.CDLL) -> None:
         "b200_act_dropout_fwd": [vp, vp, i64, i32, i32, i32, vp, u64, f32, vp],
         "b200_act_dropout_bwd": [vp, vp, vp, i64, i32, i32, i32, vp, u64, f32, vp],
         "b200_layernorm_fwd": [vp, vp, vp, vp, vp, vp, i32, i32, f32, vp],
-        "b200_layernorm_bwd": [vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, vp],
+        "b200_layernorm_bwd": [vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, vp],
         "b200_embedding_fwd": [vp, vp, vp, vp, i32, i32, i32, vp],
         "b200_embedding_bwd": [vp, vp, vp, vp, i32, i32, i32, vp],
         "b200_attention_fwd": [vp, vp, vp, i32, i32, i32, vp],

@@ -158,3 +158,138 @@ def softmax_cross_entropy_with_integer_labels(logits: torch.Tensor, labels: torc
         loss = torch.logsumexp(lg, dim=-1) - lg.gather(-1, labels[:, None]).squeeze(-1)
         correct = (lg.argmax(-1) == labels).sum().to(torch.float32)
     return (loss, correct) if return_correct else loss
+
+
+# ------------------------------------------------------------------------------------------------
+# Transformer ops (GPT-2 configurations of BASELINE.json; not present in the reference)
+# ------------------------------------------------------------------------------------------------
+class _LayerNormCUDA(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, scale, bias, eps):
+        lead, c = x.shape[:-1], x.shape[-1]
+        x2 = x.reshape(-1, c).to(torch.bfloat16).contiguous()
+        g, b = scale.to(torch.bfloat16).contiguous(), bias.to(torch.bfloat16).contiguous()
+        y = torch.empty_like(x2)
+        mean = torch.empty(x2.shape[0], dtype=torch.float32, device=x.device)
+        rstd = torch.empty_like(mean)
+        K.layernorm_fwd(x2, g, b, y, mean, rstd, eps)
+        ctx.save_for_backward(x2, g, mean, rstd)
+        ctx.meta = (lead, c, x.dtype, scale.dtype)
+        return y.reshape(*lead, c)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, g, mean, rstd = ctx.saved_tensors
+        lead, c, xdt, pdt = ctx.meta
+        dy2 = dy.reshape(-1, c).to(torch.bfloat16).contiguous()
+        dx = torch.empty_like(x2)
+        dg = torch.zeros(c, dtype=torch.float32, device=dy.device)
+        db = torch.zeros(c, dtype=torch.float32, device=dy.device)
+        K.layernorm_bwd(dy2, x2, g, mean, rstd, dx, dg, db)
+        return dx.reshape(*lead, c).to(xdt), dg.to(pdt), db.to(pdt), None
+
+
+def layer_norm(x: torch.Tensor, scale: torch.Tensor, bias: torch.Tensor, eps: float = 1e-5) -> torch.Tensor:
+    """LayerNorm over the last dim; bf16 in/out, fp32 statistics."""
+    if x.is_cuda:
+        return _LayerNormCUDA.apply(x, scale, bias, eps)
+    xf = x.to(torch.bfloat16).float()
+    y = F.layer_norm(xf, (x.shape[-1],), scale.to(torch.bfloat16).float(), bias.to(torch.bfloat16).float(), eps)
+    return y.to(torch.bfloat16)
+
+
+class _AttentionCUDA(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, qkv, heads):
+        b, t, c3 = qkv.shape
+        q2 = qkv.to(torch.bfloat16).contiguous()
+        out = torch.empty(b, t, c3 // 3, dtype=torch.bfloat16, device=qkv.device)
+        lse = torch.empty(b, heads, t, dtype=torch.float32, device=qkv.device)
+        K.attention_fwd(q2, out, lse, b, t, heads)
+        ctx.save_for_backward(q2, out, lse)
+        ctx.meta = (b, t, heads, qkv.dtype)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        q2, out, lse = ctx.saved_tensors
+        b, t, heads, dt = ctx.meta
+        dqkv = torch.empty_like(q2)
+        scratch = torch.empty(K.attention_bwd_scratch_numel(b, t, heads), dtype=torch.float32, device=dout.device)
+        K.attention_bwd(q2, out, dout.to(torch.bfloat16).contiguous(), lse, dqkv, scratch, b, t, heads)
+        return dqkv.to(dt), None
+
+
+def causal_self_attention(qkv: torch.Tensor, heads: int) -> torch.Tensor:
+    """qkv [batch, seq, 3*C] laid out [q | k | v], each [heads, 64] -> [batch, seq, C]. head_dim 64."""
+    b, t, c3 = qkv.shape
+    c = c3 // 3
+    assert c == heads * 64, "the attention kernel is specialised for head_dim 64"
+    if qkv.is_cuda:
+        return _AttentionCUDA.apply(qkv, heads)
+    q, k, v = (z.reshape(b, t, heads, 64).permute(0, 2, 1, 3).to(torch.bfloat16).float() for z in qkv.split(c, dim=-1))
+    o = F.scaled_dot_product_attention(q, k, v, is_causal=True)
+    return o.permute(0, 2, 1, 3).reshape(b, t, c).to(torch.bfloat16)
+
+
+class _EmbeddingCUDA(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, tokens, wte, wpe):
+        b, t = tokens.shape
+        wb, pb = to_bf16_padded(wte), to_bf16_padded(wpe)
+        out = torch.empty(b, t, wte.shape[1], dtype=torch.bfloat16, device=wte.device)
+        K.embedding_fwd(tokens.contiguous(), wb, pb, out)
+        ctx.save_for_backward(tokens)
+        ctx.meta = (wte.shape, wpe.shape, wte.dtype)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        (tokens,) = ctx.saved_tensors
+        ws, ps, dt = ctx.meta
+        dwte = torch.zeros(ws, dtype=torch.float32, device=dout.device)
+        dwpe = torch.zeros(ps, dtype=torch.float32, device=dout.device)
+        K.embedding_bwd(tokens.contiguous(), dout.to(torch.bfloat16).contiguous(), dwte, dwpe)
+        return None, dwte.to(dt), dwpe.to(dt)
+
+
+def embedding(tokens: torch.Tensor, wte: torch.Tensor, wpe: torch.Tensor) -> torch.Tensor:
+    """``wte[tokens] + wpe[positions]`` in bf16."""
+    if wte.is_cuda:
+        return _EmbeddingCUDA.apply(tokens, wte, wpe)
+    t = tokens.shape[1]
+    return (wte.to(torch.bfloat16).float()[tokens] + wpe.to(torch.bfloat16).float()[:t]).to(torch.bfloat16)
+
+
+class _TiedHeadCUDA(torch.autograd.Function):
+    """logits = x @ wte^T (weight tying with the token embedding)."""
+
+    @staticmethod
+    def forward(ctx, x, wte):
+        lead, c = x.shape[:-1], x.shape[-1]
+        x2 = to_bf16_padded(x.reshape(-1, c))
+        wb = to_bf16_padded(wte)
+        v = wte.shape[0]
+        out = torch.empty(x2.shape[0], _pad8(v), dtype=torch.float32, device=x.device)[:, :v]
+        K.gemm(x2, wb, out)             # B stored [N=vocab][K=C]: K-major
+        ctx.save_for_backward(x2, wb)
+        ctx.meta = (lead, c, x.dtype, wte.dtype)
+        return out.reshape(*lead, v)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, wb = ctx.saved_tensors
+        lead, c, xdt, wdt = ctx.meta
+        v = wb.shape[0]
+        dy2 = to_bf16_padded(dy.reshape(-1, v))
+        dx = torch.empty(x2.shape[0], c, dtype=torch.bfloat16, device=dy.device)
+        K.gemm(dy2, wb, dx, b_mn=True)                       # dx = dy @ wte
+        dw = torch.zeros(v, c, dtype=torch.float32, device=dy.device)
+        K.gemm(dy2, x2, dw, a_mn=True, b_mn=True)            # dwte = dy^T @ x
+        return dx.reshape(*lead, c).to(xdt), dw.to(wdt)
+
+
+def tied_lm_head(x: torch.Tensor, wte: torch.Tensor) -> torch.Tensor:
+    if x.is_cuda:
+        return _TiedHeadCUDA.apply(x, wte)
+    return x.to(torch.bfloat16).float() @ wte.to(torch.bfloat16).float().t()

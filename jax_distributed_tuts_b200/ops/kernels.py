@@ -206,10 +206,10 @@ def layernorm_fwd(x, gamma, beta, y, mean, rstd, eps: float = 1e-5):
     return y
 
 
-def layernorm_bwd(dy, x, gamma, mean, rstd, dx, dgamma, dbeta):
+def layernorm_bwd(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, dresid=None):
     rows, cols = x.shape
     _lib.check(_lib.lib().b200_layernorm_bwd(dy.data_ptr(), x.data_ptr(), gamma.data_ptr(), mean.data_ptr(),
-                                              rstd.data_ptr(), dx.data_ptr(), dgamma.data_ptr(),
+                                              rstd.data_ptr(), _ptr(dresid), dx.data_ptr(), dgamma.data_ptr(),
                                               dbeta.data_ptr(), rows, cols, _stream()))
     return dx
 

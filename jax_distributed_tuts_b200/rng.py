@@ -103,15 +103,19 @@ def _hash32(x: torch.Tensor) -> torch.Tensor:
 
 
 def dropout_mask(seed: int, rows: int, cols: int, rate: float, device="cpu") -> torch.Tensor:
-    """Boolean keep-mask identical to ``b200::dropout_keep`` over a row-major [rows, cols] matrix."""
+    """Boolean keep-mask identical to ``b200::dropout_keep4`` over a [rows, cols] matrix: three
+    32-bit hashes of (seed, row, col // 4) give the four 16-bit uniforms of a 4-column group."""
+    m32 = 0xFFFFFFFF
     thresh = int((1.0 - rate) * 65536.0 + 0.5)
-    idx = torch.arange(rows * cols, dtype=torch.int64, device=device)
-    pair = idx >> 1
-    s_lo, s_hi = seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF
-    h = _hash32((pair & 0xFFFFFFFF) ^ s_lo) ^ _hash32(((pair >> 32) + s_hi) & 0xFFFFFFFF)
-    h = _hash32(h)
-    u = torch.where((idx & 1) == 1, h >> 16, h & 0xFFFF)
-    return (u < thresh).view(rows, cols)
+    ngroups = (cols + 3) // 4
+    r = torch.arange(rows, dtype=torch.int64, device=device)[:, None]
+    g = torch.arange(ngroups, dtype=torch.int64, device=device)[None, :]
+    s_lo, s_hi = seed & m32, (seed >> 32) & m32
+    k0 = _hash32(s_lo ^ ((r * 0x9E3779B1) & m32) ^ ((g * 0x85EBCA77) & m32))
+    k1 = _hash32(k0 ^ s_hi)
+    k2 = _hash32((k1 + 0x6C8E9CF5) & m32)
+    u = torch.stack([k1 & 0xFFFF, k1 >> 16, k2 & 0xFFFF, k2 >> 16], dim=-1)   # [rows, ngroups, 4]
+    return (u < thresh).reshape(rows, ngroups * 4)[:, :cols]
 
 
 def uniform_generator(key: Key) -> torch.Generator:
