@@ -167,6 +167,33 @@ embedding_fwd_kernel(const int64_t* __restrict__ tokens, const __nv_bfloat16* __
   }
 }
 
+// Row-sharded tables in peer memory (FSDP): row `tok` lives on shard tok / rows_per_shard.
+struct TablePeers { const __nv_bfloat16* p[8]; };
+__global__ void __launch_bounds__(128)
+embedding_fwd_sharded_kernel(const int64_t* __restrict__ tokens, const TablePeers wte, int64_t wte_rows,
+                             const TablePeers wpe, int64_t wpe_rows, __nv_bfloat16* __restrict__ out, int rows,
+                             int seq, int dim) {
+  const int lane = threadIdx.x & 31;
+  const int wpb = blockDim.x >> 5;
+  const int nchunk = dim >> 3;
+  for (int row = blockIdx.x * wpb + (threadIdx.x >> 5); row < rows; row += gridDim.x * wpb) {
+    const int64_t tok = tokens[row];
+    const int64_t t = row % seq;
+    const int64_t ws = tok / wte_rows, ps = t / wpe_rows;
+    const uint4* a = reinterpret_cast<const uint4*>(wte.p[ws] + static_cast<size_t>(tok - ws * wte_rows) * dim);
+    const uint4* b = reinterpret_cast<const uint4*>(wpe.p[ps] + static_cast<size_t>(t - ps * wpe_rows) * dim);
+    uint4* o = reinterpret_cast<uint4*>(out + static_cast<size_t>(row) * dim);
+    for (int idx = lane; idx < nchunk; idx += 32) {
+      float fa[8], fb[8];
+      unpack8(a[idx], fa);
+      unpack8(b[idx], fb);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) fa[j] += fb[j];
+      o[idx] = pack8(fa);
+    }
+  }
+}
+
 __global__ void __launch_bounds__(128)
 embedding_bwd_kernel(const int64_t* __restrict__ tokens, const __nv_bfloat16* __restrict__ dout,
                      float* __restrict__ dwte, float* __restrict__ dwpe, int rows, int seq, int dim) {
@@ -249,6 +276,28 @@ extern "C" int b200_embedding_bwd(const int64_t* tokens, const void* dout, float
   if (blocks > cap) blocks = cap;
   embedding_bwd_kernel<<<blocks, 128, 0, static_cast<cudaStream_t>(stream)>>>(
       tokens, static_cast<const __nv_bfloat16*>(dout), dwte, dwpe, rows, seq, dim);
+  count_launch();
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200_embedding_fwd_sharded(const int64_t* tokens, void* const* wte_peers, int n_wte,
+                                          int64_t wte_rows_per_shard, void* const* wpe_peers, int n_wpe,
+                                          int64_t wpe_rows_per_shard, void* out, int batch, int seq, int dim,
+                                          void* stream) {
+  B200_REQUIRE(batch > 0 && seq > 0 && dim % 8 == 0, "embedding: dim=%d must be a multiple of 8", dim);
+  B200_REQUIRE(n_wte >= 1 && n_wte <= 8 && n_wpe >= 1 && n_wpe <= 8, "embedding: 1..8 shards per table");
+  TablePeers a, b;
+  memset(&a, 0, sizeof(a));
+  memset(&b, 0, sizeof(b));
+  for (int i = 0; i < n_wte; ++i) a.p[i] = static_cast<const __nv_bfloat16*>(wte_peers[i]);
+  for (int i = 0; i < n_wpe; ++i) b.p[i] = static_cast<const __nv_bfloat16*>(wpe_peers[i]);
+  int rows = batch * seq;
+  int blocks = (rows + 3) / 4;
+  int cap = num_sms() * 16;
+  if (blocks > cap) blocks = cap;
+  embedding_fwd_sharded_kernel<<<blocks, 128, 0, static_cast<cudaStream_t>(stream)>>>(
+      tokens, a, wte_rows_per_shard, b, wpe_rows_per_shard, static_cast<__nv_bfloat16*>(out), rows, seq, dim);
   count_launch();
   B200_CUDA(cudaGetLastError());
   return 0;

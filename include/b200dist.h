@@ -158,6 +158,12 @@ int b200_layernorm_bwd(const void* dy, const void* x, const void* gamma, const f
 /* out[b,t,:] = wte[tok[b,t],:] + wpe[t,:]   (bf16 tables, int64 tokens) */
 int b200_embedding_fwd(const int64_t* tokens, const void* wte, const void* wpe, void* out,
                        int batch, int seq, int dim, void* stream);
+/* The same lookup over row-sharded tables that live on several GPUs (FSDP): shard s of a table
+ * holds rows [s*rows_per_shard, (s+1)*rows_per_shard) and is read through its peer mapping. */
+int b200_embedding_fwd_sharded(const int64_t* tokens, void* const* wte_peers, int n_wte,
+                               int64_t wte_rows_per_shard, void* const* wpe_peers, int n_wpe,
+                               int64_t wpe_rows_per_shard, void* out, int batch, int seq, int dim,
+                               void* stream);
 /* dwte[tok] += dout ; dwpe[t] += dout   (fp32 grads, atomics) */
 int b200_embedding_bwd(const int64_t* tokens, const void* dout, float* dwte, float* dwpe, int batch,
                        int seq, int dim, void* stream);

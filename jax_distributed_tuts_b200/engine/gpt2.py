@@ -1,0 +1,223 @@
+"""Fused engine for GPT-2 (small / medium shapes): the transformer configurations of
+BASELINE.json (data-parallel, FSDP with the all-gather fused into the GEMMs, 2-D data x fsdp mesh).
+
+Forward and backward are an explicit schedule of our kernels over flat buffers:
+
+    embedding -> [ LN -> GEMM(qkv,+bias) -> attention -> GEMM(proj,+bias,+residual)
+                   -> LN -> GEMM(fc,+bias,GELU) -> GEMM(proj,+bias,+residual) ] x L
+              -> LN -> GEMM(tied head) -> softmax-xent (in place: logits become dlogits)
+
+Backward mirrors it; weight gradients accumulate straight into the flat fp32 gradient buffer
+(``accumulate`` over minibatches = the reference's accum_grads, util.py:41-78), GELU' rides in the
+dgrad epilogue, LayerNorm backward adds the residual-branch gradient. Each layer is one gradient
+bucket: as soon as a layer's backward is queued its fused reduce+AdamW launch goes to the side
+stream and overlaps the backward of the layers below it (DP: NVLS all-reduce, data_paral.py:210-217;
+FSDP: reduce-scatter + sharded update, param_sharding.py:134-138,353).
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional
+
+import torch
+
+from .. import rng as _rng
+from ..mesh import Mesh
+from ..models.gpt2 import padded_vocab
+from ..ops import kernels as K
+from ..state import Batch
+from .base import FlatLayout, FusedEngine
+
+
+def _layer_leaves(i: int, c: int, bucket: int):
+    p = f"h_{i}/"
+    return [
+        (p + "ln_1/scale", (c,), bucket), (p + "ln_1/bias", (c,), bucket),
+        (p + "attn/c_attn/kernel", (c, 3 * c), bucket), (p + "attn/c_attn/bias", (3 * c,), bucket),
+        (p + "attn/c_proj/kernel", (c, c), bucket), (p + "attn/c_proj/bias", (c,), bucket),
+        (p + "ln_2/scale", (c,), bucket), (p + "ln_2/bias", (c,), bucket),
+        (p + "mlp/c_fc/kernel", (c, 4 * c), bucket), (p + "mlp/c_fc/bias", (4 * c,), bucket),
+        (p + "mlp/c_proj/kernel", (4 * c, c), bucket), (p + "mlp/c_proj/bias", (c,), bucket),
+    ]
+
+
+class GPT2Engine(FusedEngine):
+    def __init__(self, config, mesh: Mesh, *, mode: str = "dp", batch_per_rank: int, seq_len: Optional[int] = None,
+                 lr: float = 3e-4, num_minibatches: int = 1, init_params: Optional[Dict] = None, **kw):
+        super().__init__(mesh, mode=mode, lr=lr, num_minibatches=num_minibatches,
+                         data_axis_name=config.get("data_axis_name", "data"), **kw)
+        self.cfg = config
+        self.L, self.Hh, self.C = config.n_layer, config.n_head, config.d_model
+        self.T = seq_len or config.n_ctx
+        assert self.T % 128 == 0 and self.T <= config.n_ctx
+        self.V = config.vocab_size
+        self.Vp = padded_vocab(self.V)
+        self.B = batch_per_rank
+        assert self.B % num_minibatches == 0
+        self.mbB = self.B // num_minibatches
+        self.M = self.mbB * self.T
+        c, L = self.C, self.L
+        # buckets in gradient-ready order: final norm, layers L-1 .. 0, embeddings
+        leaves = [("ln_f/scale", (c,), 0), ("ln_f/bias", (c,), 0)]
+        for j, i in enumerate(range(L - 1, -1, -1)):
+            leaves += _layer_leaves(i, c, 1 + j)
+        leaves += [("wte", (self.Vp, c), L + 1), ("wpe", (config.n_ctx, c), L + 1)]
+        self._setup_buffers(FlatLayout(leaves, self.world))
+        if self.mode == "fsdp":
+            for path in ("wte", "wpe"):
+                assert self.shard_dim[path] in (None, 0), f"{path} must be row-sharded or replicated"
+        d, M = self.device, self.M
+        bf, f32 = torch.bfloat16, torch.float32
+        self.tokens = torch.zeros(self.B, self.T, dtype=torch.int64, device=d)
+        self.targets = torch.zeros(self.B, self.T, dtype=torch.int64, device=d)
+        z = lambda *s, dt=bf: torch.zeros(*s, dtype=dt, device=d)
+        self.x0 = z(M, c)
+        self.acts: List[Dict[str, torch.Tensor]] = []
+        for _ in range(L):
+            self.acts.append(dict(a=z(M, c), qkv=z(M, 3 * c), att=z(M, c), x1=z(M, c), m2=z(M, c), hpre=z(M, 4 * c),
+                                  hact=z(M, 4 * c), x2=z(M, c), mean1=z(M, dt=f32), rstd1=z(M, dt=f32),
+                                  mean2=z(M, dt=f32), rstd2=z(M, dt=f32), lse=z(self.mbB * self.Hh * self.T, dt=f32)))
+        self.xf, self.meanf, self.rstdf = z(M, c), z(M, dt=f32), z(M, dt=f32)
+        self.logits = z(M, self.Vp)
+        # backward temporaries
+        self.dxa, self.dxb = z(M, c), z(M, c)
+        self.dh, self.dm = z(M, 4 * c), z(M, c)
+        self.dqkv = z(M, 3 * c)
+        self.att_scratch = z(K.attention_bwd_scratch_numel(self.mbB, self.T, self.Hh), dt=f32)
+        self.rng_base = None
+        if init_params is not None:
+            self.load_params(init_params)
+
+    # ------------------------------------------------------------------ parameters ------------
+    @staticmethod
+    def _flatten(tree: Dict, prefix: str = "") -> Dict[str, torch.Tensor]:
+        out = {}
+        for k, v in tree.items():
+            if isinstance(v, dict):
+                out.update(GPT2Engine._flatten(v, f"{prefix}{k}/"))
+            else:
+                out[f"{prefix}{k}"] = v
+        return out
+
+    def load_params(self, params: Dict) -> None:
+        self.load_flat_params(self._flatten(params))
+
+    def params_tree(self, gather: bool = True) -> Dict:
+        flat = self.flat_params(gather=gather)
+        order = ["wte", "wpe"] + [p for i in range(self.L) for p, _, _ in _layer_leaves(i, self.C, 0)] + ["ln_f/scale", "ln_f/bias"]
+        return self._nest(flat, order)
+
+    # ------------------------------------------------------------------ step ------------------
+    def _load_batch(self, batch: Batch) -> None:
+        self.tokens.copy_(batch.inputs, non_blocking=True)
+        self.targets.copy_(batch.labels, non_blocking=True)
+
+    def _rows_per_step(self) -> int:
+        return self.B * self.T * self.world
+
+    def _embed(self, tok: torch.Tensor) -> None:
+        if self.mode == "fsdp" and self.S > 1 and (self.shard_dim["wte"] is not None or self.shard_dim["wpe"] is not None):
+            K.embedding_fwd_sharded(tok, self._table_peers("wte"), self._table_peers("wpe"), self.x0, self.C)
+        else:
+            K.embedding_fwd(tok, self._table("wte"), self._table("wpe"), self.x0)
+
+    def _table(self, path: str) -> torch.Tensor:
+        return self.layout.view2d(self.pb, path) if self.mode == "dp" else self._local_view(self.pb, path)
+
+    def _table_peers(self, path: str):
+        r, c, ld = self._local_shape2d(path)
+        if self.shard_dim[path] is None:
+            return [self._local_view(self.pb, path).data_ptr()], 1 << 30
+        return ([self.arena.peer_ptrs[g] + self.arena.offsets["bf16"] + self.loc_off[path] * 2
+                 for g in self.shard_peer_ranks], r)
+
+    def _step_body(self) -> None:
+        nmb = self.num_minibatches
+        K.scale_(self.step_metrics, 0.0)
+        self._gather_small()
+        next_rng = _rng.split(_rng.Key(self.rng_base, 0), 2)[0]
+        for i in range(nmb):
+            sl = slice(i * self.mbB, (i + 1) * self.mbB)
+            self._forward(self.tokens[sl])
+            self._backward(self.tokens[sl], self.targets[sl], accumulate=i > 0, last=i == nmb - 1)
+        if self.overlap:
+            torch.cuda.current_stream().wait_stream(self.side_stream)
+        else:
+            for b in range(self.L + 1):
+                self._sync_bucket(b, last=False)
+        self._sync_bucket(self.L + 1, last=True)
+        K.rng_split_(self.rng_base, None, _rng.salt_word(next_rng), 0)
+
+    def _forward(self, tok: torch.Tensor) -> None:
+        c = self.C
+        self._embed(tok)
+        x = self.x0
+        for i in range(self.L):
+            p, A = f"h_{i}/", self.acts[i]
+            K.layernorm_fwd(x, self.vec(p + "ln_1/scale"), self.vec(p + "ln_1/bias"), A["a"], A["mean1"], A["rstd1"])
+            self.gemm_w(A["a"], p + "attn/c_attn/kernel", A["qkv"], bias=self.vec(p + "attn/c_attn/bias"))
+            K.attention_fwd(A["qkv"], A["att"], A["lse"], self.mbB, self.T, self.Hh)
+            self.gemm_w(A["att"], p + "attn/c_proj/kernel", A["x1"], bias=self.vec(p + "attn/c_proj/bias"), resid=x)
+            K.layernorm_fwd(A["x1"], self.vec(p + "ln_2/scale"), self.vec(p + "ln_2/bias"), A["m2"], A["mean2"], A["rstd2"])
+            self.gemm_w(A["m2"], p + "mlp/c_fc/kernel", A["hact"], bias=self.vec(p + "mlp/c_fc/bias"), act="gelu",
+                        pre=A["hpre"])
+            self.gemm_w(A["hact"], p + "mlp/c_proj/kernel", A["x2"], bias=self.vec(p + "mlp/c_proj/bias"), resid=A["x1"])
+            A["x_in"] = x
+            x = A["x2"]
+        K.layernorm_fwd(x, self.vec("ln_f/scale"), self.vec("ln_f/bias"), self.xf, self.meanf, self.rstdf)
+        self.gemm_wT(self.xf, "wte", self.logits)          # tied head: logits = xf @ wte^T
+        self._x_last = x
+
+    def _backward(self, tok: torch.Tensor, tgt: torch.Tensor, *, accumulate: bool, last: bool) -> None:
+        c, M = self.C, self.M
+        g2, g1 = self.grad2d, self.grad1d
+        acc = accumulate
+        logits = self.logits[:, : self.V]
+        K.softmax_xent_bf16_(logits, tgt.reshape(-1), grad_scale=1.0 / M, metrics=self.step_metrics)
+        dlog = self.logits                                   # now the gradient (pad columns stay zero)
+        K.gemm(dlog, self.xf, g2("wte"), a_mn=True, b_mn=True, accumulate=acc)      # dwte = dlogits^T xf
+        self.gemm_w(dlog, "wte", self.dm)                                            # dxf = dlogits wte
+        dx, spare = self.dxa, self.dxb
+        if not acc:
+            K.scale_(g1("ln_f/scale"), 0.0)
+            K.scale_(g1("ln_f/bias"), 0.0)
+        K.layernorm_bwd(self.dm, self._x_last, self.vec("ln_f/scale"), self.meanf, self.rstdf, dx, g1("ln_f/scale"),
+                        g1("ln_f/bias"))
+        if last and self.overlap:
+            self._sync_bucket_async(0)
+        for j, i in enumerate(range(self.L - 1, -1, -1)):
+            p, A = f"h_{i}/", self.acts[i]
+            # x2 = x1 + gelu(m2 Wfc + bfc) Wproj + bproj
+            K.gemm(A["hact"], dx, g2(p + "mlp/c_proj/kernel"), a_mn=True, b_mn=True, accumulate=acc)
+            K.colsum(dx, g1(p + "mlp/c_proj/bias"), accumulate=acc)
+            self.gemm_wT(dx, p + "mlp/c_proj/kernel", self.dh, bwd=True, aux=A["hpre"], act="gelu")
+            K.gemm(A["m2"], self.dh, g2(p + "mlp/c_fc/kernel"), a_mn=True, b_mn=True, accumulate=acc)
+            K.colsum(self.dh, g1(p + "mlp/c_fc/bias"), accumulate=acc)
+            self.gemm_wT(self.dh, p + "mlp/c_fc/kernel", self.dm)
+            if not acc:
+                for q in ("ln_1/scale", "ln_1/bias", "ln_2/scale", "ln_2/bias"):
+                    K.scale_(g1(p + q), 0.0)
+            K.layernorm_bwd(self.dm, A["x1"], self.vec(p + "ln_2/scale"), A["mean2"], A["rstd2"], spare,
+                            g1(p + "ln_2/scale"), g1(p + "ln_2/bias"), dresid=dx)
+            dx, spare = spare, dx                           # dx = d(x1)
+            # x1 = x + att Wo + bo
+            K.gemm(A["att"], dx, g2(p + "attn/c_proj/kernel"), a_mn=True, b_mn=True, accumulate=acc)
+            K.colsum(dx, g1(p + "attn/c_proj/bias"), accumulate=acc)
+            self.gemm_wT(dx, p + "attn/c_proj/kernel", self.dm)                      # d(att)
+            K.attention_bwd(A["qkv"], A["att"], self.dm, A["lse"], self.dqkv, self.att_scratch, self.mbB, self.T, self.Hh)
+            K.gemm(A["a"], self.dqkv, g2(p + "attn/c_attn/kernel"), a_mn=True, b_mn=True, accumulate=acc)
+            K.colsum(self.dqkv, g1(p + "attn/c_attn/bias"), accumulate=acc)
+            self.gemm_wT(self.dqkv, p + "attn/c_attn/kernel", self.dm)               # d(a)
+            K.layernorm_bwd(self.dm, A["x_in"], self.vec(p + "ln_1/scale"), A["mean1"], A["rstd1"], spare,
+                            g1(p + "ln_1/scale"), g1(p + "ln_1/bias"), dresid=dx)
+            dx, spare = spare, dx                           # dx = d(x_in)
+            if last and self.overlap:
+                self._sync_bucket_async(1 + j)
+        if not acc:
+            K.scale_(self.grad2d_full("wpe"), 0.0)
+        K.embedding_bwd(tok, dx, self.grad2d_full("wte"), self.grad2d_full("wpe"))
+
+    def grad2d_full(self, path: str) -> torch.Tensor:
+        """Contiguous [rows, ld] gradient region of a 2-D leaf whose last dim needs no padding."""
+        sp = self.layout.leaves[path]
+        assert sp.ld == sp.cols
+        return self.g32[sp.offset: sp.offset + sp.rows * sp.ld].view(sp.rows, sp.cols)

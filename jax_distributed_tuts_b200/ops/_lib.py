@@ -110,6 +110,8 @@ def _declare(lib: C.CDLL) -> None:
         "b200_layernorm_bwd": [vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, vp],
         "b200_embedding_fwd": [vp, vp, vp, vp, i32, i32, i32, vp],
         "b200_embedding_bwd": [vp, vp, vp, vp, i32, i32, i32, vp],
+        "b200_embedding_fwd_sharded": [vp, C.POINTER(C.c_void_p), i32, i64, C.POINTER(C.c_void_p), i32, i64, vp,
+                                       i32, i32, i32, vp],
         "b200_attention_fwd": [vp, vp, vp, i32, i32, i32, vp],
         "b200_attention_bwd": [vp, vp, vp, vp, vp, vp, i32, i32, i32, vp],
         "b200_fused_reduce_adamw": [C.POINTER(CommCtx), vp, i32, i32, vp, vp, vp, vp,

@@ -243,3 +243,15 @@ def attention_bwd(qkv, out, dout, lse, dqkv, scratch, batch: int, seq: int, head
     _lib.check(_lib.lib().b200_attention_bwd(qkv.data_ptr(), out.data_ptr(), dout.data_ptr(), lse.data_ptr(),
                                               dqkv.data_ptr(), scratch.data_ptr(), batch, seq, heads, _stream()))
     return dqkv
+
+
+def embedding_fwd_sharded(tokens, wte_peers, wpe_peers, out, dim: int):
+    """Embedding lookup over row-sharded tables that live in peer memory (FSDP): a token's row is
+    read from the rank that owns it. ``*_peers`` = (list of device pointers, rows per shard)."""
+    b, t = tokens.shape
+    (wp, wrows), (pp, prows) = wte_peers, wpe_peers
+    wa = (C.c_void_p * 8)(*(list(wp) + [None] * (8 - len(wp))))
+    pa = (C.c_void_p * 8)(*(list(pp) + [None] * (8 - len(pp))))
+    _lib.check(_lib.lib().b200_embedding_fwd_sharded(tokens.data_ptr(), wa, len(wp), wrows, pa, len(pp), prows,
+                                                      out.data_ptr(), b, t, dim, _stream()))
+    return out

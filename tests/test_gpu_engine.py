@@ -118,3 +118,70 @@ def test_engine_fsdp_single_rank_matches_dp_engine():
 def test_smoke_entry_point():
     import __graft_entry__ as g
     g.smoke()
+
+
+def _gpt_setup(name="tiny", batch=4, seq=128):
+    from jax_distributed_tuts_b200.models.gpt2 import GPT2, gpt2_config
+    cfg = gpt2_config(name)
+    model = GPT2(cfg)
+    g = torch.Generator().manual_seed(0)
+    tok = torch.randint(0, cfg.vocab_size, (batch, seq + 1), generator=g)
+    params = model.init({"params": rng.PRNGKey(3)}, tok[:, :seq])["params"]
+    return cfg, model, params, Batch(tok[:, :seq].contiguous(), tok[:, 1:].contiguous())
+
+
+def _leaves_with_path(tree):
+    from jax_distributed_tuts_b200.tree import tree_leaves_with_path
+    return tree_leaves_with_path(tree)
+
+
+def test_gpt2_generic_gpu_matches_cpu_oracle():
+    from jax_distributed_tuts_b200.autodiff import value_and_grad
+    from jax_distributed_tuts_b200.models.gpt2 import lm_loss_fn
+    cfg, model, params, batch = _gpt_setup()
+    vg = value_and_grad(lm_loss_fn, has_aux=True)
+    (l_cpu, _), g_cpu = vg(params, model.apply, batch, rng.PRNGKey(1))
+    pg = tree_map(lambda t: t.cuda(), params)
+    (l_gpu, m_gpu), g_gpu = vg(pg, model.apply, batch.to("cuda"), rng.PRNGKey(1))
+    assert abs(l_cpu.item() - l_gpu.item()) < 2e-2, (l_cpu.item(), l_gpu.item())
+    for (pa, a), (pb, b) in zip(_leaves_with_path(g_cpu), _leaves_with_path(g_gpu)):
+        denom = a.abs().max().clamp_min(1e-6)
+        rel = ((a - b.cpu().float()).abs().max() / denom).item()
+        assert rel < 6e-2, (pa, rel)
+
+
+@pytest.mark.parametrize("nmb", [1, 2])
+def test_gpt2_engine_matches_generic_path(nmb):
+    from jax_distributed_tuts_b200.engine import GPT2Engine
+    from jax_distributed_tuts_b200.models.gpt2 import lm_loss_fn
+    from jax_distributed_tuts_b200.optim import adamw
+    from jax_distributed_tuts_b200.state import TrainState
+    cfg, model, params, batch = _gpt_setup()
+    lr, steps = 1e-3, 3
+    mesh_g = Mesh((1,), ("data",), device=torch.device("cuda"))
+    pg = tree_map(lambda t: t.cuda(), params)
+    state = TrainState.create(apply_fn=model.apply, params=pg, tx=adamw(lr), rng=rng.PRNGKey(5).to("cuda"))
+    step = dp.make_train_step_dp(mesh_g, num_minibatches=nmb, loss_fn=lm_loss_fn)
+    m_gen, bg = None, batch.to("cuda")
+    losses_gen = []
+    for _ in range(steps):
+        state, m_gen = step(state, None, bg)
+        losses_gen.append(float(m_gen["loss"][0]) / m_gen["loss"][1])
+    with mesh_g:
+        eng = GPT2Engine(cfg, mesh_g, mode="dp", batch_per_rank=batch.inputs.shape[0], seq_len=128, lr=lr,
+                         num_minibatches=nmb, init_params=params, use_graph=False)
+        st = eng.make_state(model, rng.PRNGKey(5))
+        losses_eng = []
+        for _ in range(steps):
+            st, m = eng.train_step(st, None, batch)
+            losses_eng.append(float(m["loss"][0]) / m["loss"][1])
+    torch.cuda.synchronize()
+    assert m["loss"][1] == batch.labels.numel()
+    for a, b in zip(losses_gen, losses_eng):
+        assert abs(a - b) < 3e-2, (losses_gen, losses_eng)
+    assert losses_eng[-1] < losses_eng[0]
+    p_eng = eng.params_tree()
+    for (pa, a), (pb, b) in zip(_leaves_with_path(state.params), _leaves_with_path(p_eng)):
+        assert pa == pb
+        bb = b[: a.shape[0]] if b.shape != a.shape else b
+        assert _mean_close(a, bb, lr, steps), (pa, (a.float().cpu() - bb.float().cpu()).abs().mean())
