@@ -184,4 +184,8 @@ def test_gpt2_engine_matches_generic_path(nmb):
     for (pa, a), (pb, b) in zip(_leaves_with_path(state.params), _leaves_with_path(p_eng)):
         assert pa == pb
         bb = b[: a.shape[0]] if b.shape != a.shape else b
-        assert _mean_close(a, bb, lr, steps), (pa, (a.float().cpu() - bb.float().cpu()).abs().mean())
+        d = (a.float().cpu() - bb.float().cpu()).abs()
+        # Adam turns rounding noise on (near-)zero gradients into +-lr steps; the key bias of
+        # attention has an exactly zero gradient (softmax is shift invariant), so bound biases loosely
+        mean_tol = (0.6 if pa.endswith("bias") else 0.06) * lr * steps
+        assert d.max() <= 2.2 * lr * steps and d.mean() <= mean_tol, (pa, d.max(), d.mean())
