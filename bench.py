@@ -31,6 +31,13 @@ CONFIGS = {
                          classes=10, mode="dp"),
     "mlp_fsdp": dict(model="mlp_784_512_10", per_gpu_batch=16, minibatches=4, hidden=512, inp=784, classes=10,
                      mode="fsdp"),
+    # transformer configurations of BASELINE.json (samples = sequences of 1024 tokens)
+    "gpt2s_dp": dict(model="gpt2_small_124M", gpt="small", per_gpu_batch=8, minibatches=1, seq=1024, mode="dp"),
+    "gpt2s_fsdp": dict(model="gpt2_small_124M", gpt="small", per_gpu_batch=8, minibatches=1, seq=1024, mode="fsdp"),
+    "gpt2m_dp": dict(model="gpt2_medium_355M", gpt="medium", per_gpu_batch=8, minibatches=1, seq=1024, mode="dp"),
+    "gpt2m_2d": dict(model="gpt2_medium_355M", gpt="medium", per_gpu_batch=8, minibatches=1, seq=1024, mode="fsdp",
+                     mesh2d=True),
+    "gpt2_tiny": dict(model="gpt2_tiny", gpt="tiny", per_gpu_batch=4, minibatches=1, seq=128, mode="dp"),
 }
 
 
@@ -138,24 +145,49 @@ def main() -> None:
     assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run"
     c = CONFIGS[args.config]
     cfg = dp_config()
-    cfg.model.hidden_size = c["hidden"]
     B = c["per_gpu_batch"]
-    mesh = Mesh((world,), ("data",))
-    model = Classifier(cfg.model)
+    is_gpt = "gpt" in c
+    if c.get("mesh2d") and world >= 4:
+        mesh = Mesh((2, world // 2), ("data", "fsdp"))
+        shard_axis = "fsdp"
+    else:
+        mesh = Mesh((world,), ("data",))
+        shard_axis = "data"
     key = rng.PRNGKey(cfg.seed)
     model_rng, data_rng, label_rng = rng.split(key, 3)
-    # synthetic data of the reference's shape; a distinct batch shard per rank, fixed across steps
-    # like the reference's single synthetic batch (data_paral.py:113-124)
+    # synthetic data of the named shape; a distinct shard per rank, fixed across steps like the
+    # reference's single synthetic batch (data_paral.py:113-124)
     gx = rng.uniform_generator(rng.fold_in(data_rng, rank))
-    x = torch.randn(B, c["inp"], generator=gx).pin_memory()
-    y = torch.randint(0, c["classes"], (B,), generator=rng.uniform_generator(rng.fold_in(label_rng, rank))).pin_memory()
+    if is_gpt:
+        from jax_distributed_tuts_b200.engine import GPT2Engine
+        from jax_distributed_tuts_b200.models.gpt2 import GPT2, gpt2_config
+        gcfg = gpt2_config(c["gpt"])
+        model = GPT2(gcfg)
+        T = c["seq"]
+        tok = torch.randint(0, gcfg.vocab_size, (B, T + 1), generator=gx)
+        x, y = tok[:, :T].contiguous().pin_memory(), tok[:, 1:].contiguous().pin_memory()
+        h2d_bytes = int(x.numel() * 8 + y.numel() * 8)
+    else:
+        cfg.model.hidden_size = c["hidden"]
+        model = Classifier(cfg.model)
+        x = torch.randn(B, c["inp"], generator=gx).pin_memory()
+        y = torch.randint(0, c["classes"], (B,), generator=rng.uniform_generator(rng.fold_in(label_rng, rank))).pin_memory()
+        h2d_bytes = int(x.numel() * 4 + y.numel() * 8)
     with mesh:
-        init_state = dp.init_dp(model_rng, x[:4], model)
-        eng = MLPEngine(cfg.model, mesh, mode=c["mode"], batch_per_rank=B, lr=cfg.optimizer.learning_rate,
-                        num_minibatches=c["minibatches"], init_params=init_state.params, input_size=c["inp"],
-                        use_graph=not args.no_graph,
-                        min_weight_size=16 if c["mode"] == "fsdp" else 2 ** 18)
-        state = eng.make_state(model, init_state.rng)
+        if is_gpt:
+            params = model.init({"params": model_rng}, x[:1])["params"]      # random init of the named architecture
+            eng = GPT2Engine(gcfg, mesh, mode=c["mode"], batch_per_rank=B, seq_len=T, lr=3e-4,
+                             num_minibatches=c["minibatches"], init_params=params, use_graph=not args.no_graph,
+                             shard_axis=shard_axis, comm_blocks=32)
+            del params
+            state = eng.make_state(model, rng.rebase(model_rng))
+        else:
+            init_state = dp.init_dp(model_rng, x[:4], model)
+            eng = MLPEngine(cfg.model, mesh, mode=c["mode"], batch_per_rank=B, lr=cfg.optimizer.learning_rate,
+                            num_minibatches=c["minibatches"], init_params=init_state.params, input_size=c["inp"],
+                            use_graph=not args.no_graph,
+                            min_weight_size=16 if c["mode"] == "fsdp" else 2 ** 18)
+            state = eng.make_state(model, init_state.rng)
         step = dp.make_train_step_dp(mesh)
         batch = Batch(x, y)
 
@@ -219,7 +251,8 @@ def main() -> None:
             "dtype": "bf16", "data": "synthetic (random-normal inputs, uniform labels, random-init weights)",
             "impl": "ours",
             "config": {"model": c["model"], "global_batch": gb, "per_gpu_batch": B, "minibatches": c["minibatches"],
-                       "seq_len": None, "parallelism": f"{c['mode']}{world}", "optimizer": "adamw",
+                       "seq_len": c.get("seq"), "parallelism": ("dp2xfsdp%d" % (world // 2)) if (c.get("mesh2d") and world >= 4) else f"{c['mode']}{world}",
+                       "optimizer": "adamw",
                        "name": args.config, "l2": "flushed between timed steps (256 MiB write)",
                        "cuda_graph": not args.no_graph, "comm": eng.arena.backend},
             "gpu_launches": int(getattr(eng, "launches_per_step", 0)) * args.steps,
@@ -230,7 +263,13 @@ def main() -> None:
         if e2e_ms is not None:
             out["e2e"] = {"value": gb / (e2e_max / args.steps * 1e-3), "unit": "samples/s",
                           "ms_per_step": e2e_max / args.steps,
-                          "h2d_bytes_per_step": int(x.numel() * 4 + y.numel() * 8), "d2h_bytes_per_step": 4}
+                          "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 4}
+        if is_gpt:
+            toks = gb * c["seq"]
+            out["tokens_per_s"] = toks / (ms_per_step * 1e-3)
+            n_params = sum(int(torch.tensor(sp.shape).prod()) for sp in eng.layout.leaves.values())
+            flops = 6.0 * n_params * toks + 12.0 * gcfg.n_layer * gcfg.d_model * c["seq"] * toks * 0.5
+            out["model_tflops_per_gpu"] = flops / (ms_per_step * 1e-3) / 1e12 / world
         print(json.dumps(out), flush=True)
     if world > 1:
         dist.barrier()
