@@ -114,3 +114,27 @@ def dp_lr_worker(rank, world, steps, lr):
         for _ in range(steps):
             state, metrics = step(state, metrics, local)
     return {"params": state.params, "metrics": metrics}
+
+
+def pp_worker(rank, world, n_stages, steps, microbatches):
+    """GPipe over `n_stages` ranks (x `world // n_stages` data replicas) on a 4-layer tiny GPT-2."""
+    from jax_distributed_tuts_b200.models.gpt2 import GPT2, gpt2_config
+    from jax_distributed_tuts_b200.parallel import pp
+    cfg = gpt2_config("tiny", n_layer=4)
+    n_data = world // n_stages
+    mesh = Mesh((n_data, n_stages), ("data", "pipe"))
+    model = GPT2(cfg)
+    g = torch.Generator().manual_seed(0)
+    tok = torch.randint(0, cfg.vocab_size, (4 * n_data, 129), generator=g)
+    batch = Batch(tok[:, :128].contiguous(), tok[:, 1:].contiguous())
+    with mesh:
+        stage = pp.GPT2Stage(model, mesh.axis_index("pipe"), n_stages)
+        local = dp.shard_batch(batch, "data")
+        state = pp.init_pp(rng.PRNGKey(7), local.inputs, stage, learning_rate=1e-3)
+        step = pp.make_train_step_pp(mesh, stage_model=stage, num_microbatches=microbatches, pipe_axis="pipe",
+                                     data_axis="data" if n_data > 1 else None)
+        metrics = None
+        for _ in range(steps):
+            state, metrics = step(state, metrics, local)
+    return {"params": state.params, "metrics": metrics, "stage": mesh.axis_index("pipe"),
+            "data": mesh.axis_index("data")}

@@ -1,0 +1,66 @@
+"""Pipeline parallelism on the CPU plumbing tier: GPipe over 2 and 4 stages == the unsplit model."""
+import torch
+
+from jax_distributed_tuts_b200.launch import sim_multiCPU_dev
+from jax_distributed_tuts_b200.parallel.pp import split_layers
+
+import _workers as W
+
+
+def test_split_layers():
+    assert [list(r) for r in split_layers(12, 4)] == [[0, 1, 2], [3, 4, 5], [6, 7, 8], [9, 10, 11]]
+    assert [len(r) for r in split_layers(10, 4)] == [3, 3, 2, 2]
+    assert [list(r) for r in split_layers(2, 1)] == [[0, 1]]
+
+
+def _merge(results):
+    """Union of the stages' parameter dicts (data replica 0)."""
+    out = {}
+    for r in results:
+        if r["data"] == 0:
+            for k, v in r["params"].items():
+                out.setdefault(k, v)
+    return out
+
+
+def _close(a, b, lr=1e-3, steps=2, bias=False):
+    d = (a.float() - b.float()).abs()
+    return d.max() <= 2.2 * lr * steps and d.mean() <= (0.6 if bias else 0.06) * lr * steps
+
+
+def _flat(tree, prefix=""):
+    for k, v in tree.items():
+        if isinstance(v, dict):
+            yield from _flat(v, f"{prefix}{k}/")
+        else:
+            yield f"{prefix}{k}", v
+
+
+def test_gpipe_matches_unsplit_model():
+    steps, mb = 2, 2
+    single = sim_multiCPU_dev(W.pp_worker, 1, args=(1, steps, mb))
+    ref = dict(_flat(_merge(single)))
+    for n_stages in (2, 4):
+        res = sim_multiCPU_dev(W.pp_worker, n_stages, args=(n_stages, steps, mb))
+        # every stage reports the same global metrics
+        l0 = res[0]["metrics"]["loss"]
+        assert l0[1] == single[0]["metrics"]["loss"][1] == steps * 4 * 128
+        assert abs(float(l0[0]) - float(single[0]["metrics"]["loss"][0])) < 0.02 * l0[1]
+        for r in res[1:]:
+            assert float(r["metrics"]["loss"][0]) == float(l0[0])
+        # first and last stage hold identical copies of the tied embedding
+        assert torch.equal(res[0]["params"]["wte"], res[-1]["params"]["wte"])
+        got = dict(_flat(_merge(res)))
+        assert set(got) == set(ref)
+        for k in ref:
+            assert _close(got[k], ref[k], bias=k.endswith("bias")), (n_stages, k, (got[k] - ref[k]).abs().mean())
+
+
+def test_gpipe_with_data_axis():
+    res = sim_multiCPU_dev(W.pp_worker, 4, args=(2, 1, 2))      # mesh (data=2, pipe=2)
+    by = {(r["data"], r["stage"]): r for r in res}
+    for stage in (0, 1):   # data replicas of a stage stay identical
+        a, b = dict(_flat(by[(0, stage)]["params"])), dict(_flat(by[(1, stage)]["params"]))
+        for k in a:
+            assert torch.equal(a[k], b[k]), (stage, k)
+    assert by[(0, 0)]["metrics"]["loss"][1] == 2 * 4 * 128
