@@ -94,7 +94,7 @@ __device__ __forceinline__ void adamw1(float& p, float& m, float& v, float g, co
   p = p - hp.lr * ((m * c1) / (sqrtf(v * c2) + hp.eps) + hp.weight_decay * p);
 }
 
-__global__ void __launch_bounds__(512, 1)
+__global__ void __launch_bounds__(256, 1)
 fused_reduce_adamw_kernel(const CommDev c, const b200_seg* __restrict__ segs, int nseg, int broadcast,
                           float* __restrict__ p_local, __nv_bfloat16* __restrict__ bf16_local,
                           float* __restrict__ m, float* __restrict__ v, const b200_adamw_hparams hp,
@@ -121,55 +121,78 @@ fused_reduce_adamw_kernel(const CommDev c, const b200_seg* __restrict__ segs, in
     if (vec) {
       const int rl4 = sg.row_len >> 2;
       const int64_t total4 = static_cast<int64_t>(sg.rows) * rl4;
-      for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total4;
-           i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
-        const int64_t row = i / rl4;
-        const int64_t col = (i - row * rl4) << 2;
-        const int64_t src = sg.src_off + row * sg.src_pitch + col;
-        const int64_t loc = sg.loc_off + row * sg.row_len + col;
-        float4 g;
-        if (c.world == 1) {
-          g = *reinterpret_cast<const float4*>(my_grad + src);
-        } else if (c.mc_grad != nullptr) {
-          g = mc_ld_reduce_f32x4(c.mc_grad + src);
-        } else {
-          g = make_float4(0.f, 0.f, 0.f, 0.f);
+      const int64_t nthreads = static_cast<int64_t>(gridDim.x) * blockDim.x;
+      constexpr int U = 4;   // independent 16-byte vectors per thread per iteration (memory-level parallelism)
+      for (int64_t i0 = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i0 < total4; i0 += nthreads * U) {
+        int64_t src[U], loc[U], dst[U];
+        bool ok[U];
+        float4 g[U], pp[U], mm[U], vv[U];
+        float* p_base = broadcast ? c.param[c.rank] : p_local;
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const int64_t i = i0 + u * nthreads;
+          ok[u] = i < total4;
+          const int64_t ii = ok[u] ? i : 0;
+          const int64_t row = ii / rl4;
+          const int64_t col = (ii - row * rl4) << 2;
+          src[u] = sg.src_off + row * sg.src_pitch + col;
+          loc[u] = sg.loc_off + row * sg.row_len + col;
+          dst[u] = broadcast ? sg.dst_off + row * sg.row_len + col : loc[u];
+        }
+        // ---- loads (all issued before any use) ----
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          if (!ok[u]) continue;
+          if (c.world == 1) g[u] = *reinterpret_cast<const float4*>(my_grad + src[u]);
+          else if (c.mc_grad != nullptr) g[u] = mc_ld_reduce_f32x4(c.mc_grad + src[u]);
+          else g[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+          mm[u] = *reinterpret_cast<float4*>(m + loc[u]);
+          vv[u] = *reinterpret_cast<float4*>(v + loc[u]);
+          pp[u] = *reinterpret_cast<float4*>(p_base + dst[u]);
+        }
+        if (c.world > 1 && c.mc_grad == nullptr) {
 #pragma unroll 1
           for (int k = 0; k < c.world; ++k) {
             // DP slices are disjoint per rank: start at myself to spread the traffic. Replicated
             // FSDP leaves are reduced by every rank: a fixed order keeps the replicas bit-identical.
             int peer = broadcast ? c.rank + k : k;
             if (peer >= c.world) peer -= c.world;
-            float4 t4 = ld_sys_f32x4(c.grad[peer] + src);
-            g.x += t4.x; g.y += t4.y; g.z += t4.z; g.w += t4.w;
+            float4 t4[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u)
+              if (ok[u]) t4[u] = ld_sys_f32x4(c.grad[peer] + src[u]);
+#pragma unroll
+            for (int u = 0; u < U; ++u)
+              if (ok[u]) { g[u].x += t4[u].x; g[u].y += t4[u].y; g[u].z += t4[u].z; g[u].w += t4[u].w; }
           }
         }
-        float4 pp, mm = *reinterpret_cast<float4*>(m + loc), vv = *reinterpret_cast<float4*>(v + loc);
-        const int64_t dst = broadcast ? sg.dst_off + row * sg.row_len + col : loc;
-        float* p_base = broadcast ? c.param[c.rank] : p_local;
-        pp = *reinterpret_cast<float4*>(p_base + dst);
-        adamw1(pp.x, mm.x, vv.x, g.x * hp.grad_scale, hp, c1, c2);
-        adamw1(pp.y, mm.y, vv.y, g.y * hp.grad_scale, hp, c1, c2);
-        adamw1(pp.z, mm.z, vv.z, g.z * hp.grad_scale, hp, c1, c2);
-        adamw1(pp.w, mm.w, vv.w, g.w * hp.grad_scale, hp, c1, c2);
-        *reinterpret_cast<float4*>(m + loc) = mm;
-        *reinterpret_cast<float4*>(v + loc) = vv;
-        __nv_bfloat162 lo = __floats2bfloat162_rn(pp.x, pp.y), hi = __floats2bfloat162_rn(pp.z, pp.w);
-        const uint32_t w0 = *reinterpret_cast<uint32_t*>(&lo), w1 = *reinterpret_cast<uint32_t*>(&hi);
-        if (!broadcast || c.world == 1) {
-          *reinterpret_cast<float4*>(p_base + dst) = pp;
-          __nv_bfloat16* b = broadcast ? c.bf16[c.rank] : bf16_local;
-          if (b != nullptr) *reinterpret_cast<uint2*>(b + dst) = make_uint2(w0, w1);
-        } else if (c.mc_param != nullptr) {
-          mc_st_f32x4(c.mc_param + dst, pp);
-          if (c.mc_bf16 != nullptr) mc_st_b32x2(c.mc_bf16 + dst, w0, w1);
-        } else {
+        // ---- AdamW + publish ----
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          if (!ok[u]) continue;
+          adamw1(pp[u].x, mm[u].x, vv[u].x, g[u].x * hp.grad_scale, hp, c1, c2);
+          adamw1(pp[u].y, mm[u].y, vv[u].y, g[u].y * hp.grad_scale, hp, c1, c2);
+          adamw1(pp[u].z, mm[u].z, vv[u].z, g[u].z * hp.grad_scale, hp, c1, c2);
+          adamw1(pp[u].w, mm[u].w, vv[u].w, g[u].w * hp.grad_scale, hp, c1, c2);
+          *reinterpret_cast<float4*>(m + loc[u]) = mm[u];
+          *reinterpret_cast<float4*>(v + loc[u]) = vv[u];
+          __nv_bfloat162 lo = __floats2bfloat162_rn(pp[u].x, pp[u].y), hi = __floats2bfloat162_rn(pp[u].z, pp[u].w);
+          const uint32_t w0 = *reinterpret_cast<uint32_t*>(&lo), w1 = *reinterpret_cast<uint32_t*>(&hi);
+          if (!broadcast || c.world == 1) {
+            *reinterpret_cast<float4*>(p_base + dst[u]) = pp[u];
+            __nv_bfloat16* b = broadcast ? c.bf16[c.rank] : bf16_local;
+            if (b != nullptr) *reinterpret_cast<uint2*>(b + dst[u]) = make_uint2(w0, w1);
+          } else if (c.mc_param != nullptr) {
+            mc_st_f32x4(c.mc_param + dst[u], pp[u]);
+            if (c.mc_bf16 != nullptr) mc_st_b32x2(c.mc_bf16 + dst[u], w0, w1);
+          } else {
 #pragma unroll 1
-          for (int k = 0; k < c.world; ++k) {
-            int peer = c.rank + k;
-            if (peer >= c.world) peer -= c.world;
-            *reinterpret_cast<float4*>(c.param[peer] + dst) = pp;
-            if (c.bf16[peer] != nullptr) *reinterpret_cast<uint2*>(c.bf16[peer] + dst) = make_uint2(w0, w1);
+            for (int k = 0; k < c.world; ++k) {
+              int peer = c.rank + k;
+              if (peer >= c.world) peer -= c.world;
+              *reinterpret_cast<float4*>(c.param[peer] + dst[u]) = pp[u];
+              if (c.bf16[peer] != nullptr) *reinterpret_cast<uint2*>(c.bf16[peer] + dst[u]) = make_uint2(w0, w1);
+            }
           }
         }
       }
@@ -288,10 +311,11 @@ extern "C" int b200_fused_reduce_adamw(const b200_comm_ctx* ctx, const b200_seg*
     if (broadcast) B200_REQUIRE(d.param[i] != nullptr, "comm: missing parameter buffer of rank %d", i);
   }
   if (!broadcast) B200_REQUIRE(p_local != nullptr, "comm: local mode needs p_local");
-  if (blocks <= 0) blocks = 32;
+  if (blocks <= 0) blocks = 64;
   if (blocks > B200_COMM_MAX_BLOCKS) blocks = B200_COMM_MAX_BLOCKS;
+  if (blocks > num_sms()) blocks = num_sms();   // every block must be resident: they spin on each other across GPUs
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  fused_reduce_adamw_kernel<<<blocks, 512, 0, s>>>(d, segs_dev, nseg, broadcast, p_local,
+  fused_reduce_adamw_kernel<<<blocks, 256, 0, s>>>(d, segs_dev, nseg, broadcast, p_local,
                                                    static_cast<__nv_bfloat16*>(bf16_local), m, v, *hp,
                                                    step_count, step_metrics, metrics_acc, nmetrics);
   count_launch();

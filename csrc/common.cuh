@@ -236,23 +236,23 @@ __host__ __device__ constexpr uint32_t umma_idesc_bf16(int m, int n, int a_mn, i
 }
 
 // ---- small math ----
-__device__ __forceinline__ float silu_f(float x) { return x / (1.0f + __expf(-x)); }
+__device__ __forceinline__ float silu_f(float x) { return __fdividef(x, 1.0f + __expf(-x)); }
 __device__ __forceinline__ float silu_grad_f(float x) {
-  float s = 1.0f / (1.0f + __expf(-x));
+  float s = __fdividef(1.0f, 1.0f + __expf(-x));
   return s * (1.0f + x * (1.0f - s));
 }
 // GPT-2 "gelu_new" (tanh approximation)
 __device__ __forceinline__ float gelu_f(float x) {
   const float k0 = 0.7978845608028654f, k1 = 0.044715f;
   float u = k0 * (x + k1 * x * x * x);
-  float t = 1.0f - 2.0f / (1.0f + __expf(2.0f * u));  // tanh(u)
+  float t = 1.0f - __fdividef(2.0f, 1.0f + __expf(2.0f * u));  // tanh(u)
   return 0.5f * x * (1.0f + t);
 }
 __device__ __forceinline__ float gelu_grad_f(float x) {
   const float k0 = 0.7978845608028654f, k1 = 0.044715f;
   float x2 = x * x;
   float u = k0 * (x + k1 * x * x2);
-  float t = 1.0f - 2.0f / (1.0f + __expf(2.0f * u));
+  float t = 1.0f - __fdividef(2.0f, 1.0f + __expf(2.0f * u));
   float du = k0 * (1.0f + 3.0f * k1 * x2);
   return 0.5f * (1.0f + t) + 0.5f * x * (1.0f - t * t) * du;
 }

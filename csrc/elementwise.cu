@@ -163,8 +163,55 @@ xent_block_bf16_kernel(__nv_bfloat16* __restrict__ logits, int ld, const int64_t
 }
 
 // ------------------------------------------------------------------------------------------
-// column sums (bias gradients): block (32 x 8) walks a 32-column stripe, coalesced along cols.
+// column sums (bias gradients). Vector path (ld % 8 == 0): a thread owns 8 consecutive columns
+// (one 16-byte load per row), 32 threads cover 256 columns, 8 row-lanes per block walk the
+// block's row range; partial sums meet in shared memory and leave with one atomicAdd per column
+// per block. Scalar path for narrow / unaligned matrices (the 10-class head).
 // ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+colsum_bf16_vec_kernel(const __nv_bfloat16* __restrict__ x, int ld, int rows, int cols, float* __restrict__ out,
+                       int row_chunks) {
+  __shared__ float s[8][256 + 8];
+  const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
+  const int col = blockIdx.x * 256 + cx * 8;
+  const int rows_per = (rows + row_chunks - 1) / row_chunks;
+  const int r0 = blockIdx.y * rows_per;
+  const int r1 = min(rows, r0 + rows_per);
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (col < cols) {   // cols % 8 == 0 on this path, so the 8 columns are all valid
+    int r = r0 + ry;
+    for (; r + 24 < r1; r += 32) {   // four independent loads in flight
+      uint4 w[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) w[u] = *reinterpret_cast<const uint4*>(x + static_cast<size_t>(r + u * 8) * ld + col);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        acc[0] += __uint_as_float(w[u].x << 16); acc[1] += __uint_as_float(w[u].x & 0xFFFF0000u);
+        acc[2] += __uint_as_float(w[u].y << 16); acc[3] += __uint_as_float(w[u].y & 0xFFFF0000u);
+        acc[4] += __uint_as_float(w[u].z << 16); acc[5] += __uint_as_float(w[u].z & 0xFFFF0000u);
+        acc[6] += __uint_as_float(w[u].w << 16); acc[7] += __uint_as_float(w[u].w & 0xFFFF0000u);
+      }
+    }
+    for (; r < r1; r += 8) {
+      const uint4 w = *reinterpret_cast<const uint4*>(x + static_cast<size_t>(r) * ld + col);
+      acc[0] += __uint_as_float(w.x << 16); acc[1] += __uint_as_float(w.x & 0xFFFF0000u);
+      acc[2] += __uint_as_float(w.y << 16); acc[3] += __uint_as_float(w.y & 0xFFFF0000u);
+      acc[4] += __uint_as_float(w.z << 16); acc[5] += __uint_as_float(w.z & 0xFFFF0000u);
+      acc[6] += __uint_as_float(w.w << 16); acc[7] += __uint_as_float(w.w & 0xFFFF0000u);
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s[ry][cx * 8 + j] = acc[j];
+  __syncthreads();
+  const int c = threadIdx.x;   // 256 threads = 256 columns
+  if (blockIdx.x * 256 + c < cols) {
+    float t = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t += s[i][c];
+    atomicAdd(&out[blockIdx.x * 256 + c], t);
+  }
+}
+
 __global__ void colsum_bf16_kernel(const __nv_bfloat16* __restrict__ x, int ld, int rows, int cols,
                                    float* __restrict__ out, int accumulate, int row_chunks) {
   __shared__ float s[8][33];
@@ -348,15 +395,22 @@ extern "C" int b200_colsum_bf16(const void* x, int ld, int rows, int cols, float
                                 void* stream) {
   B200_REQUIRE(rows > 0 && cols > 0, "colsum: empty input");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  int col_blocks = (cols + 31) / 32;
-  int row_chunks = 1;
-  // enough blocks to fill the chip when the matrix is tall
-  while (col_blocks * row_chunks < num_sms() * 2 && rows / (row_chunks * 2) >= 64) row_chunks *= 2;
-  if (row_chunks > 1 && !accumulate) {
-    B200_CUDA(cudaMemsetAsync(out, 0, sizeof(float) * cols, s));
+  const bool vec = (ld % 8 == 0) && (cols % 8 == 0) && ((reinterpret_cast<uintptr_t>(x) & 15) == 0) && cols >= 64;
+  if (vec) {
+    int col_blocks = (cols + 255) / 256;
+    int row_chunks = 1;
+    while (col_blocks * row_chunks < num_sms() * 2 && rows / (row_chunks * 2) >= 32) row_chunks *= 2;
+    if (!accumulate) B200_CUDA(cudaMemsetAsync(out, 0, sizeof(float) * cols, s));
+    colsum_bf16_vec_kernel<<<dim3(col_blocks, row_chunks), 256, 0, s>>>(static_cast<const __nv_bfloat16*>(x), ld, rows,
+                                                                      cols, out, row_chunks);
+  } else {
+    int col_blocks = (cols + 31) / 32;
+    int row_chunks = 1;
+    while (col_blocks * row_chunks < num_sms() * 2 && rows / (row_chunks * 2) >= 64) row_chunks *= 2;
+    if (row_chunks > 1 && !accumulate) B200_CUDA(cudaMemsetAsync(out, 0, sizeof(float) * cols, s));
+    colsum_bf16_kernel<<<dim3(col_blocks, row_chunks), dim3(32, 8), 0, s>>>(
+        static_cast<const __nv_bfloat16*>(x), ld, rows, cols, out, accumulate, row_chunks);
   }
-  colsum_bf16_kernel<<<dim3(col_blocks, row_chunks), dim3(32, 8), 0, s>>>(
-      static_cast<const __nv_bfloat16*>(x), ld, rows, cols, out, accumulate, row_chunks);
   count_launch();
   B200_CUDA(cudaGetLastError());
   return 0;

@@ -293,7 +293,25 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
           for (int j = 0; j < 4; ++j)
             if (col + j < tc.n_limit) bias4[j] = __bfloat162float(p.bias[col + j]);
         }
-#pragma unroll 2
+        // Issue every global load this chunk needs (saved pre-activation, residual, accumulator)
+        // before any math, so 8 independent requests per lane are in flight instead of one.
+        uint2 aux8[8], res8[8];
+        float4 acc8[8];
+        const bool need_aux = p.bwd && p.aux != nullptr && full4 && p.vec_aux;
+        const bool need_res = !p.bwd && p.resid != nullptr && full4 && p.vec_res;
+        const bool need_acc = p.d_fp32 && p.accumulate && full4 && p.vec_d;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int row = row_base + i * 4 + lrow;
+          const bool ok = row < p.M && col_ok;
+          aux8[i] = make_uint2(0u, 0u);
+          res8[i] = make_uint2(0u, 0u);
+          acc8[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (ok && need_aux) aux8[i] = *reinterpret_cast<const uint2*>(p.aux + static_cast<size_t>(row) * p.ldaux + col);
+          if (ok && need_res) res8[i] = *reinterpret_cast<const uint2*>(p.resid + static_cast<size_t>(row) * p.ldres + col);
+          if (ok && need_acc) acc8[i] = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.d) + static_cast<size_t>(row) * p.ldd + col);
+        }
+#pragma unroll
         for (int i = 0; i < 8; ++i) {
           const int lr = i * 4 + lrow;          // row within the warp's 32 rows
           const int row = row_base + lr;
@@ -329,8 +347,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
           } else if (p.aux != nullptr) {
             const __nv_bfloat16* ap = p.aux + static_cast<size_t>(row) * p.ldaux + col;
             float x[4];
-            if (full4 && p.vec_aux) {
-              const uint2 w = *reinterpret_cast<const uint2*>(ap);
+            if (need_aux) {
+              const uint2 w = aux8[i];
               x[0] = bf16_bits_to_f(w.x & 0xFFFF); x[1] = bf16_bits_to_f(w.x >> 16);
               x[2] = bf16_bits_to_f(w.y & 0xFFFF); x[3] = bf16_bits_to_f(w.y >> 16);
             } else {
@@ -360,8 +378,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
           }
           if (!p.bwd && p.resid != nullptr) {
             const __nv_bfloat16* rp = p.resid + static_cast<size_t>(row) * p.ldres + col;
-            if (full4 && p.vec_res) {
-              const uint2 w = *reinterpret_cast<const uint2*>(rp);
+            if (need_res) {
+              const uint2 w = res8[i];
               v[0] += bf16_bits_to_f(w.x & 0xFFFF); v[1] += bf16_bits_to_f(w.x >> 16);
               v[2] += bf16_bits_to_f(w.y & 0xFFFF); v[3] += bf16_bits_to_f(w.y >> 16);
             } else {
@@ -376,7 +394,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
             if (full4 && p.vec_d) {
               float4 o = make_float4(v[0], v[1], v[2], v[3]);
               if (p.accumulate) {
-                const float4 c4 = *reinterpret_cast<const float4*>(dp);
+                const float4 c4 = acc8[i];
                 o.x += c4.x; o.y += c4.y; o.z += c4.z; o.w += c4.w;
               }
               *reinterpret_cast<float4*>(dp) = o;

@@ -74,9 +74,11 @@ layernorm_fwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* _
   }
 }
 
-// dx = rstd * (dy*g - mean(dy*g) - xhat * mean(dy*g*xhat)); dgamma += dy*xhat; dbeta += dy.
-// Each block keeps fp32 partial dgamma/dbeta in shared memory over the rows it owns and flushes
-// them with one atomicAdd per column at the end.
+// dx = rstd * (dy*g - mean(dy*g) - xhat * mean(dy*g*xhat)) (+ dresid); dgamma += dy*xhat; dbeta += dy.
+// A lane owns the same columns for every row it visits, so its dgamma/dbeta partial sums stay in
+// registers across rows; they are combined across the block's warps in shared memory once at the
+// end and flushed with one atomicAdd per column per block.
+template <int NCH>   // 16-byte chunks per lane: cols <= NCH * 256
 __global__ void __launch_bounds__(256)
 layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
                      const __nv_bfloat16* __restrict__ gamma, const float* __restrict__ mean,
@@ -91,28 +93,45 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
   const int lane = threadIdx.x & 31;
   const int wpb = blockDim.x >> 5;
   const int nchunk = cols >> 3;
+  float acc_g[NCH][8], acc_b[NCH][8], gam[NCH][8];
+#pragma unroll
+  for (int c = 0; c < NCH; ++c) {
+    const int idx = c * 32 + lane;
+    if (idx < nchunk) unpack8(reinterpret_cast<const uint4*>(gamma)[idx], gam[c]);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { acc_g[c][j] = 0.f; acc_b[c][j] = 0.f; }
+  }
   for (int row = blockIdx.x * wpb + (threadIdx.x >> 5); row < rows; row += gridDim.x * wpb) {
     const uint4* xr = reinterpret_cast<const uint4*>(x + static_cast<size_t>(row) * cols);
     const uint4* dr = reinterpret_cast<const uint4*>(dy + static_cast<size_t>(row) * cols);
     const float mu = mean[row], rs = rstd[row];
-    float xh[LN_MAX_CHUNKS][8], dg[LN_MAX_CHUNKS][8];
+    float xh[NCH][8], dg[NCH][8];
+    uint4 xw[NCH], dw[NCH], rw[NCH];
+#pragma unroll
+    for (int c = 0; c < NCH; ++c) {      // all loads of the row first
+      const int idx = c * 32 + lane;
+      if (idx < nchunk) {
+        xw[c] = xr[idx];
+        dw[c] = dr[idx];
+        if (dresid != nullptr) rw[c] = reinterpret_cast<const uint4*>(dresid + static_cast<size_t>(row) * cols)[idx];
+      }
+    }
     float s1 = 0.f, s2 = 0.f;
 #pragma unroll
-    for (int c = 0; c < LN_MAX_CHUNKS; ++c) {
-      int idx = c * 32 + lane;
+    for (int c = 0; c < NCH; ++c) {
+      const int idx = c * 32 + lane;
       if (idx < nchunk) {
-        float xv[8], dv[8], g[8];
-        unpack8(xr[idx], xv);
-        unpack8(dr[idx], dv);
-        unpack8(reinterpret_cast<const uint4*>(gamma)[idx], g);
+        float xv[8], dv[8];
+        unpack8(xw[c], xv);
+        unpack8(dw[c], dv);
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           xh[c][j] = (xv[j] - mu) * rs;
-          dg[c][j] = dv[j] * g[j];
+          dg[c][j] = dv[j] * gam[c][j];
           s1 += dg[c][j];
           s2 += dg[c][j] * xh[c][j];
-          atomicAdd(&s_dg[idx * 8 + j], dv[j] * xh[c][j]);
-          atomicAdd(&s_db[idx * 8 + j], dv[j]);
+          acc_g[c][j] += dv[j] * xh[c][j];
+          acc_b[c][j] += dv[j];
         }
       }
     }
@@ -120,19 +139,30 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
     s2 = warp_sum(s2) / cols;
     uint4* or_ = reinterpret_cast<uint4*>(dx + static_cast<size_t>(row) * cols);
 #pragma unroll
-    for (int c = 0; c < LN_MAX_CHUNKS; ++c) {
-      int idx = c * 32 + lane;
+    for (int c = 0; c < NCH; ++c) {
+      const int idx = c * 32 + lane;
       if (idx < nchunk) {
         float o[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) o[j] = rs * (dg[c][j] - s1 - xh[c][j] * s2);
         if (dresid != nullptr) {   // gradient arriving through the residual connection
           float rr[8];
-          unpack8(reinterpret_cast<const uint4*>(dresid + static_cast<size_t>(row) * cols)[idx], rr);
+          unpack8(rw[c], rr);
 #pragma unroll
           for (int j = 0; j < 8; ++j) o[j] += rr[j];
         }
         or_[idx] = pack8(o);
+      }
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < NCH; ++c) {
+    const int idx = c * 32 + lane;
+    if (idx < nchunk) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        atomicAdd(&s_dg[idx * 8 + j], acc_g[c][j]);
+        atomicAdd(&s_db[idx * 8 + j], acc_b[c][j]);
       }
     }
   }
@@ -241,12 +271,19 @@ extern "C" int b200_layernorm_bwd(const void* dy, const void* x, const void* gam
                                   int rows, int cols, void* stream) {
   B200_REQUIRE(rows > 0 && cols > 0 && cols % 8 == 0 && cols <= 2048, "layernorm: cols=%d must be a multiple of 8, <= 2048", cols);
   int blocks = (rows + 7) / 8;
-  int cap = num_sms() * 2;
+  int cap = num_sms() * 4;
   if (blocks > cap) blocks = cap;
-  layernorm_bwd_kernel<<<blocks, 256, 2 * cols * sizeof(float), static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(x),
-      static_cast<const __nv_bfloat16*>(gamma), mean, rstd, static_cast<const __nv_bfloat16*>(dresid),
-      static_cast<__nv_bfloat16*>(dx), dgamma, dbeta, rows, cols);
+  auto launch = [&](auto kern) {
+    kern<<<blocks, 256, 2 * cols * sizeof(float), static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(x),
+        static_cast<const __nv_bfloat16*>(gamma), mean, rstd, static_cast<const __nv_bfloat16*>(dresid),
+        static_cast<__nv_bfloat16*>(dx), dgamma, dbeta, rows, cols);
+  };
+  if (cols <= 256) launch(layernorm_bwd_kernel<1>);
+  else if (cols <= 512) launch(layernorm_bwd_kernel<2>);
+  else if (cols <= 768) launch(layernorm_bwd_kernel<3>);
+  else if (cols <= 1024) launch(layernorm_bwd_kernel<4>);
+  else launch(layernorm_bwd_kernel<8>);
   count_launch();
   B200_CUDA(cudaGetLastError());
   return 0;

@@ -16,7 +16,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 7
+#define B200_ABI_VERSION 8
 
 const char* b200_last_error(void);
 int b200_abi_version(void);
@@ -239,7 +239,7 @@ typedef struct b200_comm_ctx {
 } b200_comm_ctx;
 
 #define B200_SIGNAL_WORDS 8192
-#define B200_COMM_MAX_BLOCKS 64
+#define B200_COMM_MAX_BLOCKS 128
 
 /* broadcast = 1 (DP):   p/bf16 written to all ranks at dst_off; m,v local at loc_off.
  * broadcast = 0 (FSDP): p_local/bf16_local/m/v are this rank's shard buffers at loc_off.

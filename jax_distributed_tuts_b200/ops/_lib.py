@@ -10,7 +10,7 @@ from typing import Optional
 
 from . import _build
 
-ABI_VERSION = 7
+ABI_VERSION = 8
 
 _lib: Optional[C.CDLL] = None
 
@@ -78,7 +78,7 @@ class GatherSeg(C.Structure):
 
 
 SIGNAL_WORDS = 8192
-COMM_MAX_BLOCKS = 64
+COMM_MAX_BLOCKS = 128
 
 
 class B200Error(RuntimeError):
