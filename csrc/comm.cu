@@ -120,7 +120,7 @@ fused_reduce_adamw_kernel(const CommDev c, const b200_seg* __restrict__ segs, in
     const bool vec = ((sg.row_len | sg.src_pitch | sg.src_off | sg.dst_off | sg.loc_off) & 3) == 0;
     if (vec) {
       const int rl4 = sg.row_len >> 2;
-      const int64_t total4 = static_cast<int64_t>(sg.rows) * rl4;
+      const int64_t total4 = static_cast<int64_t>(sg.rows) * rl4;   // multi-row segments: < 2^31 (host-checked)
       const int64_t nthreads = static_cast<int64_t>(gridDim.x) * blockDim.x;
       constexpr int U = 4;   // independent 16-byte vectors per thread per iteration (memory-level parallelism)
       for (int64_t i0 = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i0 < total4; i0 += nthreads * U) {
@@ -133,7 +133,9 @@ fused_reduce_adamw_kernel(const CommDev c, const b200_seg* __restrict__ segs, in
           const int64_t i = i0 + u * nthreads;
           ok[u] = i < total4;
           const int64_t ii = ok[u] ? i : 0;
-          const int64_t row = ii / rl4;
+          // rows == 1 (every DP segment, contiguous FSDP shards) needs no division; otherwise the
+          // segment is far below 2^31 vectors and a 32-bit division is enough
+          const int64_t row = sg.rows == 1 ? 0 : static_cast<int64_t>(static_cast<uint32_t>(ii) / static_cast<uint32_t>(rl4));
           const int64_t col = (ii - row * rl4) << 2;
           src[u] = sg.src_off + row * sg.src_pitch + col;
           loc[u] = sg.loc_off + row * sg.row_len + col;

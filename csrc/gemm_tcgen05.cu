@@ -92,6 +92,152 @@ __device__ __forceinline__ TileCoord tile_coord(const GemmDev& p, int tile, int 
 
 __device__ __forceinline__ float bf16_bits_to_f(uint32_t v) { return __uint_as_float(v << 16); }
 
+// Epilogue of one warp for one tile: rows [row_base, row_base+32) x columns [col_base, col_base+BN/2)
+// of the output, accumulator at TMEM address `taddr` (lane quadrant, stage and column half already
+// applied). See the comment at the call site for the data path.
+template <int BN>
+__device__ __forceinline__ void epilogue_tile(const GemmDev& p, int row_base, int col_base, int n_limit, uint32_t taddr,
+                                              float* stage, const uint64_t* seed_tab, uint64_t seed, int lane) {
+  constexpr int CHUNKS = BN / 64;     // 32-column chunks per warp
+  const int lrow = lane >> 3;         // row within a group of 4 rows
+  const int lchunk = lane & 7;        // 16-byte chunk (4 columns) within the 32-column row
+  const bool warp_active = row_base < p.M && col_base < n_limit;
+  uint32_t r[32];
+  if (warp_active) tmem_ld_32x32b_x32(taddr, r);
+#pragma unroll 1
+  for (int c = 0; c < CHUNKS; ++c) {
+    const int col0 = col_base + c * 32;
+    if (!warp_active || col0 >= n_limit) break;  // warp-uniform
+    tmem_ld_wait();
+    // registers (thread = row) -> staging, 16-byte chunks XOR-swizzled by row: conflict-free
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float4 v4 = make_float4(__uint_as_float(r[j * 4 + 0]), __uint_as_float(r[j * 4 + 1]),
+                              __uint_as_float(r[j * 4 + 2]), __uint_as_float(r[j * 4 + 3]));
+      *reinterpret_cast<float4*>(stage + lane * 32 + ((j ^ (lane & 7)) << 2)) = v4;
+    }
+    __syncwarp();
+    // prefetch the next chunk from TMEM while this one is being processed
+    if (c + 1 < CHUNKS && col0 + 32 < n_limit) tmem_ld_32x32b_x32(taddr + (c + 1) * 32, r);
+    const int col = col0 + lchunk * 4;
+    const bool full4 = col + 4 <= n_limit;
+    const bool col_ok = col < n_limit;
+    float bias4[4] = {0.f, 0.f, 0.f, 0.f};
+    if (!p.bwd && p.bias != nullptr && col_ok) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (col + j < n_limit) bias4[j] = __bfloat162float(p.bias[col + j]);
+    }
+#pragma unroll 2
+    for (int i = 0; i < 8; ++i) {
+      const int lr = i * 4 + lrow;          // row within the warp's 32 rows
+      const int row = row_base + lr;
+      if (row_base + i * 4 >= p.M) break;   // warp-uniform: nothing left in this tile
+      if (row >= p.M || !col_ok) continue;
+      const float4 a4 = *reinterpret_cast<const float4*>(stage + lr * 32 + ((lchunk ^ (lr & 7)) << 2));
+      float v[4] = {a4.x * p.alpha, a4.y * p.alpha, a4.z * p.alpha, a4.w * p.alpha};
+      if (!p.bwd) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) v[j] += bias4[j];
+        if (p.pre != nullptr) {
+          __nv_bfloat16* pp = p.pre + static_cast<size_t>(row) * p.ldpre + col;
+          __nv_bfloat162 t0 = __floats2bfloat162_rn(v[0], v[1]), t1 = __floats2bfloat162_rn(v[2], v[3]);
+          if (full4 && p.vec_pre) {
+            *reinterpret_cast<uint2*>(pp) = make_uint2(*reinterpret_cast<uint32_t*>(&t0), *reinterpret_cast<uint32_t*>(&t1));
+          } else {
+            __nv_bfloat16 tv[4] = {t0.x, t0.y, t1.x, t1.y};
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              if (col + j < n_limit) pp[j] = tv[j];
+          }
+          // the activation sees the value as it was stored (bf16), like the backward will
+          v[0] = __bfloat162float(t0.x); v[1] = __bfloat162float(t0.y);
+          v[2] = __bfloat162float(t1.x); v[3] = __bfloat162float(t1.y);
+        }
+        if (p.act == B200_ACT_SILU) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) v[j] = silu_f(v[j]);
+        } else if (p.act == B200_ACT_GELU) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) v[j] = gelu_f(v[j]);
+        }
+      } else if (p.aux != nullptr) {
+        const __nv_bfloat16* ap = p.aux + static_cast<size_t>(row) * p.ldaux + col;
+        float x[4];
+        if (full4 && p.vec_aux) {
+          const uint2 w = *reinterpret_cast<const uint2*>(ap);
+          x[0] = bf16_bits_to_f(w.x & 0xFFFF); x[1] = bf16_bits_to_f(w.x >> 16);
+          x[2] = bf16_bits_to_f(w.y & 0xFFFF); x[3] = bf16_bits_to_f(w.y >> 16);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) x[j] = (col + j < n_limit) ? __bfloat162float(ap[j]) : 0.0f;
+        }
+        if (p.act == B200_ACT_SILU) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) v[j] *= silu_grad_f(x[j]);
+        } else if (p.act == B200_ACT_GELU) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) v[j] *= gelu_grad_f(x[j]);
+        }
+      }
+      if (p.drop_key != nullptr) {
+        int drow = row;
+        uint64_t sd = seed;
+        if (p.drop_nsalt > 0) {
+          int blk = row / p.drop_rows_per_salt;
+          drow = row - blk * p.drop_rows_per_salt;
+          sd = seed_tab[blk < p.drop_nsalt ? blk : p.drop_nsalt - 1];
+        }
+        const uint32_t keep = dropout_keep4(sd, static_cast<uint32_t>(drow), static_cast<uint32_t>(col) >> 2,
+                                            p.drop_thresh16);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) v[j] = ((keep >> j) & 1u) ? v[j] * p.drop_scale : 0.0f;
+      }
+      if (!p.bwd && p.resid != nullptr) {
+        const __nv_bfloat16* rp = p.resid + static_cast<size_t>(row) * p.ldres + col;
+        if (full4 && p.vec_res) {
+          const uint2 w = *reinterpret_cast<const uint2*>(rp);
+          v[0] += bf16_bits_to_f(w.x & 0xFFFF); v[1] += bf16_bits_to_f(w.x >> 16);
+          v[2] += bf16_bits_to_f(w.y & 0xFFFF); v[3] += bf16_bits_to_f(w.y >> 16);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            if (col + j < n_limit) v[j] += __bfloat162float(rp[j]);
+        }
+      }
+      // ---- store ----
+      if (p.d_fp32) {
+        float* dp = reinterpret_cast<float*>(p.d) + static_cast<size_t>(row) * p.ldd + col;
+        if (full4 && p.vec_d) {
+          float4 o = make_float4(v[0], v[1], v[2], v[3]);
+          if (p.accumulate) {
+            const float4 c4 = *reinterpret_cast<const float4*>(dp);
+            o.x += c4.x; o.y += c4.y; o.z += c4.z; o.w += c4.w;
+          }
+          *reinterpret_cast<float4*>(dp) = o;
+        } else {
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            if (col + j < n_limit) dp[j] = p.accumulate ? dp[j] + v[j] : v[j];
+        }
+      } else {
+        __nv_bfloat16* dp = reinterpret_cast<__nv_bfloat16*>(p.d) + static_cast<size_t>(row) * p.ldd + col;
+        __nv_bfloat162 t0 = __floats2bfloat162_rn(v[0], v[1]), t1 = __floats2bfloat162_rn(v[2], v[3]);
+        if (full4 && p.vec_d) {
+          *reinterpret_cast<uint2*>(dp) = make_uint2(*reinterpret_cast<uint32_t*>(&t0), *reinterpret_cast<uint32_t*>(&t1));
+        } else {
+          __nv_bfloat16 tv[4] = {t0.x, t0.y, t1.x, t1.y};
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            if (col + j < n_limit) dp[j] = tv[j];
+        }
+      }
+    }
+    __syncwarp();   // staging is reused by the next chunk
+  }
+  if (warp_active) tmem_ld_wait();
+}
+
 template <int BN, int A_MN, int B_MN>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ TmapSet tma_b,
@@ -245,8 +391,6 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
     const int quad = warp & 3;          // TMEM lane quadrant this warp may read
     const int half = ew >> 2;           // which half of the tile's columns
     float* stage = reinterpret_cast<float*>(smem + STAGES * Cfg::STAGE_BYTES + Cfg::BAR_BYTES) + ew * (32 * 32);
-    const int lrow = lane >> 3;         // row within a group of 4 rows
-    const int lchunk = lane & 7;        // 16-byte chunk (4 columns) within the 32-column row
     uint64_t seed = 0;
     uint64_t* seed_tab = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE_BYTES + Cfg::BAR_BYTES + 8 * 32 * 32 * 4) + ew * 16;
     if (p.drop_key != nullptr) {
@@ -255,7 +399,6 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
       if (lane < p.drop_nsalt) seed_tab[lane] = mix64(key ^ p.drop_salts[lane]);   // one RNG stream per minibatch
       __syncwarp();
     }
-    constexpr int CHUNKS = BN / 64;     // 32-column chunks per warp
     int local = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
       const int as = local & 1;
@@ -263,162 +406,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
       TileCoord tc = tile_coord(p, tile, m_tiles, BN);
       mbar_wait(&tmem_full[as], aphase);
       tc_fence_after();
-      const int row_base = tc.m0 + quad * 32;
-      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + as * BN + half * (BN / 2);
-      const int col_base = tc.n0 + half * (BN / 2);
-      const bool warp_active = row_base < p.M && col_base < tc.n_limit;
-      uint32_t r[32];
-      if (warp_active) tmem_ld_32x32b_x32(taddr, r);
-#pragma unroll 1
-      for (int c = 0; c < CHUNKS; ++c) {
-        const int col0 = col_base + c * 32;
-        if (!warp_active || col0 >= tc.n_limit) break;  // warp-uniform
-        tmem_ld_wait();
-        // registers (thread = row) -> staging, 16-byte chunks XOR-swizzled by row: conflict-free
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          float4 v4 = make_float4(__uint_as_float(r[j * 4 + 0]), __uint_as_float(r[j * 4 + 1]),
-                                  __uint_as_float(r[j * 4 + 2]), __uint_as_float(r[j * 4 + 3]));
-          *reinterpret_cast<float4*>(stage + lane * 32 + ((j ^ (lane & 7)) << 2)) = v4;
-        }
-        __syncwarp();
-        // prefetch the next chunk from TMEM while this one is being processed
-        if (c + 1 < CHUNKS && col0 + 32 < tc.n_limit) tmem_ld_32x32b_x32(taddr + (c + 1) * 32, r);
-        const int col = col0 + lchunk * 4;
-        const bool full4 = col + 4 <= tc.n_limit;
-        const bool col_ok = col < tc.n_limit;
-        float bias4[4] = {0.f, 0.f, 0.f, 0.f};
-        if (!p.bwd && p.bias != nullptr && col_ok) {
-#pragma unroll
-          for (int j = 0; j < 4; ++j)
-            if (col + j < tc.n_limit) bias4[j] = __bfloat162float(p.bias[col + j]);
-        }
-        // Issue every global load this chunk needs (saved pre-activation, residual, accumulator)
-        // before any math, so 8 independent requests per lane are in flight instead of one.
-        uint2 aux8[8], res8[8];
-        float4 acc8[8];
-        const bool need_aux = p.bwd && p.aux != nullptr && full4 && p.vec_aux;
-        const bool need_res = !p.bwd && p.resid != nullptr && full4 && p.vec_res;
-        const bool need_acc = p.d_fp32 && p.accumulate && full4 && p.vec_d;
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int row = row_base + i * 4 + lrow;
-          const bool ok = row < p.M && col_ok;
-          aux8[i] = make_uint2(0u, 0u);
-          res8[i] = make_uint2(0u, 0u);
-          acc8[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (ok && need_aux) aux8[i] = *reinterpret_cast<const uint2*>(p.aux + static_cast<size_t>(row) * p.ldaux + col);
-          if (ok && need_res) res8[i] = *reinterpret_cast<const uint2*>(p.resid + static_cast<size_t>(row) * p.ldres + col);
-          if (ok && need_acc) acc8[i] = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.d) + static_cast<size_t>(row) * p.ldd + col);
-        }
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int lr = i * 4 + lrow;          // row within the warp's 32 rows
-          const int row = row_base + lr;
-          if (row_base + i * 4 >= p.M) break;   // warp-uniform: nothing left in this tile
-          if (row >= p.M || !col_ok) continue;
-          const float4 a4 = *reinterpret_cast<const float4*>(stage + lr * 32 + ((lchunk ^ (lr & 7)) << 2));
-          float v[4] = {a4.x * p.alpha, a4.y * p.alpha, a4.z * p.alpha, a4.w * p.alpha};
-          if (!p.bwd) {
-#pragma unroll
-            for (int j = 0; j < 4; ++j) v[j] += bias4[j];
-            if (p.pre != nullptr) {
-              __nv_bfloat16* pp = p.pre + static_cast<size_t>(row) * p.ldpre + col;
-              __nv_bfloat162 t0 = __floats2bfloat162_rn(v[0], v[1]), t1 = __floats2bfloat162_rn(v[2], v[3]);
-              if (full4 && p.vec_pre) {
-                *reinterpret_cast<uint2*>(pp) = make_uint2(*reinterpret_cast<uint32_t*>(&t0), *reinterpret_cast<uint32_t*>(&t1));
-              } else {
-                __nv_bfloat16 tv[4] = {t0.x, t0.y, t1.x, t1.y};
-#pragma unroll
-                for (int j = 0; j < 4; ++j)
-                  if (col + j < tc.n_limit) pp[j] = tv[j];
-              }
-              // the activation sees the value as it was stored (bf16), like the backward will
-              v[0] = __bfloat162float(t0.x); v[1] = __bfloat162float(t0.y);
-              v[2] = __bfloat162float(t1.x); v[3] = __bfloat162float(t1.y);
-            }
-            if (p.act == B200_ACT_SILU) {
-#pragma unroll
-              for (int j = 0; j < 4; ++j) v[j] = silu_f(v[j]);
-            } else if (p.act == B200_ACT_GELU) {
-#pragma unroll
-              for (int j = 0; j < 4; ++j) v[j] = gelu_f(v[j]);
-            }
-          } else if (p.aux != nullptr) {
-            const __nv_bfloat16* ap = p.aux + static_cast<size_t>(row) * p.ldaux + col;
-            float x[4];
-            if (need_aux) {
-              const uint2 w = aux8[i];
-              x[0] = bf16_bits_to_f(w.x & 0xFFFF); x[1] = bf16_bits_to_f(w.x >> 16);
-              x[2] = bf16_bits_to_f(w.y & 0xFFFF); x[3] = bf16_bits_to_f(w.y >> 16);
-            } else {
-#pragma unroll
-              for (int j = 0; j < 4; ++j) x[j] = (col + j < tc.n_limit) ? __bfloat162float(ap[j]) : 0.0f;
-            }
-            if (p.act == B200_ACT_SILU) {
-#pragma unroll
-              for (int j = 0; j < 4; ++j) v[j] *= silu_grad_f(x[j]);
-            } else if (p.act == B200_ACT_GELU) {
-#pragma unroll
-              for (int j = 0; j < 4; ++j) v[j] *= gelu_grad_f(x[j]);
-            }
-          }
-          if (p.drop_key != nullptr) {
-            int drow = row;
-            uint64_t sd = seed;
-            if (p.drop_nsalt > 0) {
-              int blk = row / p.drop_rows_per_salt;
-              drow = row - blk * p.drop_rows_per_salt;
-              sd = seed_tab[blk < p.drop_nsalt ? blk : p.drop_nsalt - 1];
-            }
-            const uint32_t keep = dropout_keep4(sd, static_cast<uint32_t>(drow), static_cast<uint32_t>(col) >> 2,
-                                                p.drop_thresh16);
-#pragma unroll
-            for (int j = 0; j < 4; ++j) v[j] = ((keep >> j) & 1u) ? v[j] * p.drop_scale : 0.0f;
-          }
-          if (!p.bwd && p.resid != nullptr) {
-            const __nv_bfloat16* rp = p.resid + static_cast<size_t>(row) * p.ldres + col;
-            if (need_res) {
-              const uint2 w = res8[i];
-              v[0] += bf16_bits_to_f(w.x & 0xFFFF); v[1] += bf16_bits_to_f(w.x >> 16);
-              v[2] += bf16_bits_to_f(w.y & 0xFFFF); v[3] += bf16_bits_to_f(w.y >> 16);
-            } else {
-#pragma unroll
-              for (int j = 0; j < 4; ++j)
-                if (col + j < tc.n_limit) v[j] += __bfloat162float(rp[j]);
-            }
-          }
-          // ---- store ----
-          if (p.d_fp32) {
-            float* dp = reinterpret_cast<float*>(p.d) + static_cast<size_t>(row) * p.ldd + col;
-            if (full4 && p.vec_d) {
-              float4 o = make_float4(v[0], v[1], v[2], v[3]);
-              if (p.accumulate) {
-                const float4 c4 = acc8[i];
-                o.x += c4.x; o.y += c4.y; o.z += c4.z; o.w += c4.w;
-              }
-              *reinterpret_cast<float4*>(dp) = o;
-            } else {
-#pragma unroll
-              for (int j = 0; j < 4; ++j)
-                if (col + j < tc.n_limit) dp[j] = p.accumulate ? dp[j] + v[j] : v[j];
-            }
-          } else {
-            __nv_bfloat16* dp = reinterpret_cast<__nv_bfloat16*>(p.d) + static_cast<size_t>(row) * p.ldd + col;
-            __nv_bfloat162 t0 = __floats2bfloat162_rn(v[0], v[1]), t1 = __floats2bfloat162_rn(v[2], v[3]);
-            if (full4 && p.vec_d) {
-              *reinterpret_cast<uint2*>(dp) = make_uint2(*reinterpret_cast<uint32_t*>(&t0), *reinterpret_cast<uint32_t*>(&t1));
-            } else {
-              __nv_bfloat16 tv[4] = {t0.x, t0.y, t1.x, t1.y};
-#pragma unroll
-              for (int j = 0; j < 4; ++j)
-                if (col + j < tc.n_limit) dp[j] = tv[j];
-            }
-          }
-        }
-        __syncwarp();   // staging is reused by the next chunk
-      }
-      if (warp_active) tmem_ld_wait();
+      epilogue_tile<BN>(p, tc.m0 + quad * 32, tc.n0 + half * (BN / 2), tc.n_limit,
+                        tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + as * BN + half * (BN / 2), stage, seed_tab,
+                        seed, lane);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tmem_empty[as]);
@@ -430,6 +420,238 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
+  }
+}
+
+// =============================================================================================
+// CTA-pair variant (cta_group::2): a cluster of two CTAs on the two SMs of a TPC computes one
+// 256 x BN tile. Each CTA loads its own 128 rows of A and its own half (BN/2 columns) of B; the
+// leader CTA issues tcgen05.mma with M = 256 and the hardware reads both halves of B from the two
+// CTAs' shared memories. Per flop each SM pulls 1/3 fewer operand bytes from L2 than with a
+// single-CTA 128 x BN tile, which is what the K ~ 768 GEMMs of the transformer are bound by.
+// Barriers: TMA of both CTAs completes on the leader's full barrier; MMA completion is multicast
+// to the empty / accumulator-full barriers of both CTAs; epilogue warps of both CTAs arrive on
+// the leader's accumulator-empty barrier.
+// =============================================================================================
+template <int BN>
+struct PairCfg {
+  static constexpr int BNH = BN / 2;                 // B columns held by each CTA
+  static constexpr int A_BYTES = BM * BK * 2;
+  static constexpr int B_BYTES = BNH * BK * 2;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int STAGES = 6;
+  static constexpr uint32_t TMEM_COLS = (2 * BN <= 256) ? 256 : 512;
+  static constexpr int BAR_BYTES = 256;
+  static constexpr int EPI_STAGE_BYTES = 8 * 32 * 32 * 4 + 8 * 16 * 8;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + BAR_BYTES + EPI_STAGE_BYTES + 1024;
+};
+
+template <int BN, int A_MN, int B_MN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
+gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ TmapSet tma_b,
+                         const GemmDev p) {
+  using Cfg = PairCfg<BN>;
+  constexpr int STAGES = Cfg::STAGES;
+  constexpr int BNH = Cfg::BNH;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE_BYTES);   // used in the leader
+  uint64_t* empty_bar = full_bar + STAGES;                                              // both CTAs
+  uint64_t* tmem_full = empty_bar + STAGES;                                             // both CTAs
+  uint64_t* tmem_empty = tmem_full + 2;                                                 // used in the leader
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+  const int cluster_id = blockIdx.x >> 1;
+  const int num_clusters = gridDim.x >> 1;
+
+  constexpr int BM2 = 2 * BM;
+  const int m_tiles = (p.M + BM2 - 1) / BM2;
+  int n_tiles;
+  if (p.shard_mode == 2)
+    n_tiles = ((p.shard_len + BN - 1) / BN) * p.nsrc;
+  else
+    n_tiles = (p.N + BN - 1) / BN;
+  const int num_tiles = m_tiles * n_tiles;
+  int kps = 0, nk;
+  if (p.shard_mode == 1) {
+    kps = (p.shard_len + ((p.shard_len & 7) ? 7 : 0) + BK - 1) / BK;
+    nk = kps * p.nsrc;
+  } else {
+    nk = (p.K + BK - 1) / BK;
+  }
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tma_a);
+    for (int s = 0; s < p.nsrc; ++s) tma_prefetch_desc(&tma_b.m[s]);
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&tmem_full[s], 1);
+      mbar_init(&tmem_empty[s], 16);   // 8 epilogue warps in each CTA of the pair
+    }
+    mbar_fence_init();
+  }
+  if (warp == 1) tmem_alloc_pair<Cfg::TMEM_COLS>(tmem_ptr);
+  tc_fence_before();
+  cluster_sync_all();                  // barriers of both CTAs initialised before any remote arrive
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  // tile -> coordinates (same order as the single-CTA kernel, M tiles of 256 rows)
+  auto coord = [&](int tile) {
+    TileCoord t;
+    int mt = tile % m_tiles;
+    int nt = tile / m_tiles;
+    t.m0 = mt * BM2;
+    if (p.shard_mode == 2) {
+      int tps = (p.shard_len + BN - 1) / BN;
+      int ntl = tps * p.nsrc;
+      nt = (nt + p.rot * tps) % ntl;
+      int src = nt / tps, loc = nt % tps;
+      t.b_src = src;
+      t.b_n = loc * BN;
+      t.n0 = src * p.shard_len + loc * BN;
+      int lim = (src + 1) * p.shard_len;
+      t.n_limit = lim < p.N ? lim : p.N;
+    } else {
+      t.b_src = 0;
+      t.b_n = nt * BN;
+      t.n0 = nt * BN;
+      t.n_limit = p.N;
+    }
+    return t;
+  };
+
+  if (warp == 0) {
+    // ===================== TMA producer (both CTAs) =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+        TileCoord tc = coord(tile);
+        const int my_m0 = tc.m0 + static_cast<int>(rank) * BM;
+        const int my_bn = tc.b_n + static_cast<int>(rank) * BNH;
+        for (int it = 0; it < nk; ++it) {
+          int a_k, b_k, b_src;
+          if (p.shard_mode == 1) {
+            int s = it / kps, kb = it - s * kps;
+            b_src = p.rot + s;
+            if (b_src >= p.nsrc) b_src -= p.nsrc;
+            const int base = b_src * p.shard_len;
+            const int shift = base & 7;
+            a_k = base - shift + kb * BK;
+            b_k = kb * BK - shift;
+          } else {
+            a_k = b_k = it * BK;
+            b_src = tc.b_src;
+          }
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * Cfg::STAGE_BYTES;
+          uint8_t* sb = sa + Cfg::A_BYTES;
+          const uint32_t full_leader = mapa_cluster(smem_u32(&full_bar[stage]), 0);
+          if (leader) mbar_expect_tx(&full_bar[stage], 2 * Cfg::STAGE_BYTES);   // bytes of both CTAs
+          if (A_MN == 0) {
+            tma_load_2d_pair(sa, &tma_a, full_leader, a_k, my_m0);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BM / 64; ++j)
+              tma_load_2d_pair(sa + j * (64 * BK * 2), &tma_a, full_leader, my_m0 + j * 64, a_k);
+          }
+          const CUtensorMap* bm = &tma_b.m[b_src];
+          if (B_MN == 0) {
+            tma_load_2d_pair(sb, bm, full_leader, b_k, my_bn);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BNH / 64; ++j)
+              tma_load_2d_pair(sb + j * (64 * BK * 2), bm, full_leader, my_bn + j * 64, b_k);
+          }
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (leader CTA only) =====================
+    if (leader) {
+      constexpr uint32_t idesc = umma_idesc_bf16(BM2, BN, A_MN, B_MN);
+      constexpr uint32_t A_LBO = A_MN ? BK * 128 : 16, A_SBO = 1024, A_KSTEP = A_MN ? 2048 : 32;
+      constexpr uint32_t B_LBO = B_MN ? BK * 128 : 16, B_SBO = 1024, B_KSTEP = B_MN ? 2048 : 32;
+      int stage = 0;
+      uint32_t phase = 0;
+      int local = 0;
+      for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, ++local) {
+        const int as = local & 1;
+        const uint32_t aphase = (local >> 1) & 1;
+        mbar_wait(&tmem_empty[as], aphase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + as * BN;
+        for (int it = 0; it < nk; ++it) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          if (lane == 0) {
+            const uint32_t sa = smem_u32(smem + stage * Cfg::STAGE_BYTES);
+            const uint32_t sb = sa + Cfg::A_BYTES;
+#pragma unroll
+            for (int k = 0; k < BK / UMMA_K; ++k) {
+              uint64_t da = umma_smem_desc(sa + k * A_KSTEP, A_LBO, A_SBO);
+              uint64_t db = umma_smem_desc(sb + k * B_KSTEP, B_LBO, B_SBO);
+              umma_bf16_pair(d_tmem, da, db, idesc, (it | k) ? 1u : 0u);
+            }
+            umma_commit_pair(&empty_bar[stage]);
+            if (it == nk - 1) umma_commit_pair(&tmem_full[as]);
+          }
+          __syncwarp();
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else {
+    // ===================== epilogue (warps 2..9 of both CTAs) =====================
+    const int ew = warp - 2;
+    const int quad = warp & 3;
+    const int half = ew >> 2;
+    float* stage = reinterpret_cast<float*>(smem + STAGES * Cfg::STAGE_BYTES + Cfg::BAR_BYTES) + ew * (32 * 32);
+    uint64_t seed = 0;
+    uint64_t* seed_tab = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE_BYTES + Cfg::BAR_BYTES + 8 * 32 * 32 * 4) + ew * 16;
+    if (p.drop_key != nullptr) {
+      const uint64_t key = *p.drop_key;
+      seed = mix64(key ^ p.drop_salt);
+      if (lane < p.drop_nsalt) seed_tab[lane] = mix64(key ^ p.drop_salts[lane]);
+      __syncwarp();
+    }
+    int local = 0;
+    for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, ++local) {
+      const int as = local & 1;
+      const uint32_t aphase = (local >> 1) & 1;
+      TileCoord tc = coord(tile);
+      mbar_wait(&tmem_full[as], aphase);
+      tc_fence_after();
+      epilogue_tile<BN>(p, tc.m0 + static_cast<int>(rank) * BM + quad * 32, tc.n0 + half * (BN / 2), tc.n_limit,
+                        tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + as * BN + half * (BN / 2), stage, seed_tab,
+                        seed, lane);
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(mapa_cluster(smem_u32(&tmem_empty[as]), 0));
+    }
+  }
+
+  tc_fence_before();
+  cluster_sync_all();                  // neither CTA may exit (or free TMEM) while the other still uses it
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc_pair<Cfg::TMEM_COLS>(tmem_base);
   }
 }
 
@@ -475,6 +697,52 @@ static int launch_gemm(const b200_gemm_args& a, const GemmDev& dev, cudaStream_t
   count_launch();
   B200_CUDA(cudaGetLastError());
   return 0;
+}
+
+template <int BN, int A_MN, int B_MN>
+static int launch_gemm_pair(const b200_gemm_args& a, const GemmDev& dev, cudaStream_t stream) {
+  using Cfg = PairCfg<BN>;
+  CUtensorMap ta;
+  TmapSet tb;
+  memset(&tb, 0, sizeof(tb));
+  int rc;
+  if (A_MN == 0)
+    rc = make_tmap_2d(&ta, a.a, 2, (uint64_t)a.k, (uint64_t)a.m, (uint64_t)a.lda * 2, BK, BM, 128);
+  else
+    rc = make_tmap_2d(&ta, a.a, 2, (uint64_t)a.m, (uint64_t)a.k, (uint64_t)a.lda * 2, 64, BK, 128);
+  if (rc) return rc;
+  uint64_t bn = a.n, bk = a.k;
+  if (a.b_shard_mode == 1) bk = a.b_shard_len;
+  if (a.b_shard_mode == 2) bn = a.b_shard_len;
+  for (int s = 0; s < dev.nsrc; ++s) {
+    if (B_MN == 0)
+      rc = make_tmap_2d(&tb.m[s], a.b_src[s], 2, bk, bn, (uint64_t)a.ldb * 2, BK, Cfg::BNH, 128);
+    else
+      rc = make_tmap_2d(&tb.m[s], a.b_src[s], 2, bn, bk, (uint64_t)a.ldb * 2, 64, BK, 128);
+    if (rc) return rc;
+  }
+  auto kern = gemm_tcgen05_pair_kernel<BN, A_MN, B_MN>;
+  static bool attr_done = false;
+  if (!attr_done) {
+    B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+    attr_done = true;
+  }
+  int m_tiles = (a.m + 2 * BM - 1) / (2 * BM);
+  int n_tiles = (a.b_shard_mode == 2) ? ((a.b_shard_len + BN - 1) / BN) * dev.nsrc : (a.n + BN - 1) / BN;
+  long long tiles = (long long)m_tiles * n_tiles;
+  int clusters = (int)(tiles < num_sms() / 2 ? tiles : num_sms() / 2);
+  kern<<<clusters * 2, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(ta, tb, dev);
+  count_launch();
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
+
+template <int BN>
+static int dispatch_major_pair(const b200_gemm_args& a, const GemmDev& dev, cudaStream_t s) {
+  if (a.a_mn == 0 && a.b_mn == 0) return launch_gemm_pair<BN, 0, 0>(a, dev, s);
+  if (a.a_mn == 0 && a.b_mn == 1) return launch_gemm_pair<BN, 0, 1>(a, dev, s);
+  if (a.a_mn == 1 && a.b_mn == 0) return launch_gemm_pair<BN, 1, 0>(a, dev, s);
+  return launch_gemm_pair<BN, 1, 1>(a, dev, s);
 }
 
 template <int BN>
@@ -558,6 +826,14 @@ extern "C" int b200_gemm_bf16(const b200_gemm_args* args, void* stream) {
     }
   }
   cudaStream_t s = static_cast<cudaStream_t>(stream);
+  // CTA pairs (256-row tiles) once the problem has at least two row tiles; pair_mode: 0 = auto,
+  // 1 = never, 2 = always (when the tile shape allows it)
+  const bool pair_ok = bn >= 128;
+  const bool use_pair = pair_ok && (a.pair_mode == 2 || (a.pair_mode == 0 && a.m > BM));
+  if (use_pair) {
+    if (bn == 128) return dispatch_major_pair<128>(a, dev, s);
+    return dispatch_major_pair<256>(a, dev, s);
+  }
   switch (bn) {
     case 64: return dispatch_major<64>(a, dev, s);
     case 128: return dispatch_major<128>(a, dev, s);

@@ -16,7 +16,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 8
+#define B200_ABI_VERSION 9
 
 const char* b200_last_error(void);
 int b200_abi_version(void);
@@ -84,6 +84,9 @@ typedef struct b200_gemm_args {
    * drop_nsalt = 0 uses drop_salt for all rows. */
   int32_t drop_nsalt, drop_rows_per_salt;
   uint64_t drop_salts[16];
+  /* 0 = choose, 1 = single-CTA 128-row tiles, 2 = CTA pairs (cta_group::2, 256-row tiles: the two
+   * SMs of a TPC share the B operand, one third less L2->SM traffic per flop) */
+  int32_t pair_mode;
 } b200_gemm_args;
 
 int b200_gemm_bf16(const b200_gemm_args* args, void* stream);

@@ -10,7 +10,7 @@ from typing import Optional
 
 from . import _build
 
-ABI_VERSION = 8
+ABI_VERSION = 9
 
 _lib: Optional[C.CDLL] = None
 
@@ -43,6 +43,7 @@ class GemmArgs(C.Structure):
         ("block_n", C.c_int32),
         ("drop_nsalt", C.c_int32), ("drop_rows_per_salt", C.c_int32),
         ("drop_salts", C.c_uint64 * 16),
+        ("pair_mode", C.c_int32),
     ]
 
 

@@ -56,6 +56,7 @@ def gemm(
     b_shape: Optional[tuple[int, int]] = None,
     ldb: Optional[int] = None,
     block_n: int = 0,
+    pair_mode: int = 0,
 ) -> torch.Tensor:
     """``out (+)= epilogue(A @ B)`` on tcgen05 (see ``include/b200dist.h`` for the layouts).
 
@@ -117,6 +118,7 @@ def gemm(
             for i, sv in enumerate(drop_salts):
                 args.drop_salts[i] = sv & 0xFFFFFFFFFFFFFFFF
     args.block_n = block_n
+    args.pair_mode = pair_mode
     _lib.check(_lib.lib().b200_gemm_bf16(C.byref(args), _stream()))
     return out
 

@@ -16,7 +16,7 @@ import time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 GROUPS = ["gemm_kmajor", "gemm_mnmajor", "gemm_epilogue", "gemm_sharded", "elementwise", "transformer",
-          "attention", "gemm_perf"]
+          "attention", "gemm_perf", "gemm_epi_perf"]
 
 
 def _rel_err(got, ref):
@@ -67,6 +67,11 @@ def group_gemm_kmajor():
         K.gemm(a, b, out, block_n=bn)
         ref = a.float() @ b.float().t()
         ok &= _report(f"TN fp32 out m={m} n={n} k={k} bn={bn}", _rel_err(out, ref), 2e-3)
+        if bn != 64 and n > 64:
+            for pm in (1, 2):
+                out.fill_(float("nan"))
+                K.gemm(a, b, out, block_n=bn, pair_mode=pm)
+                ok &= _report(f"   pair_mode={pm}", _rel_err(out, ref), 2e-3)
         if not ok and m * n <= 128 * 256:
             bad = ((out - ref).abs() > 1e-2 * ref.abs().max()).nonzero()
             print("   first bad idx:", bad[:8].tolist(), "n_bad", bad.shape[0])
@@ -372,8 +377,9 @@ def group_gemm_perf():
             t1 = _time(fn); t2 = _time(tfn)
             print(f"  ({m},{n},{k}) {name}: {t1:8.3f} {fl / t1 / 1e9:8.1f} | {t2:8.3f} {fl / t2 / 1e9:8.1f}", flush=True)
         for bn in (128, 256):
-            t1 = _time(lambda: K.gemm(a, bt, out, block_n=bn))
-            print(f"     TN block_n={bn}: {t1:8.3f} ms {fl / t1 / 1e9:8.1f} TFLOP/s", flush=True)
+            for pm, nm in ((1, "1-CTA"), (2, "pair ")):
+                t1 = _time(lambda: K.gemm(a, bt, out, block_n=bn, pair_mode=pm))
+                print(f"     TN block_n={bn} {nm}: {t1:8.3f} ms {fl / t1 / 1e9:8.1f} TFLOP/s", flush=True)
     # wgrad layout
     m, n, k = 768, 3072, 8192
     at = torch.randn(k, m, device="cuda", dtype=torch.bfloat16)
@@ -383,6 +389,39 @@ def group_gemm_perf():
     t2 = _time(lambda: torch.matmul(at.t(), b))
     fl = 2.0 * m * n * k
     print(f"  wgrad ({m},{n},{k}): {t1:8.3f} ms {fl / t1 / 1e9:8.1f} TFLOP/s | torch {t2:8.3f} ms {fl / t2 / 1e9:8.1f}")
+    return True
+
+
+def group_gemm_epi_perf():
+    """Cost of each epilogue feature on a GPT-2-shaped GEMM (M=8192, N=3072, K=768)."""
+    import torch
+    from jax_distributed_tuts_b200.ops import kernels as K
+    m, n, k = 8192, 3072, 768
+    a = torch.randn(m, k, device="cuda", dtype=torch.bfloat16)
+    bt = torch.randn(n, k, device="cuda", dtype=torch.bfloat16)
+    out = torch.empty(m, n, device="cuda", dtype=torch.bfloat16)
+    out32 = torch.zeros(m, n, device="cuda", dtype=torch.float32)
+    pre = torch.randn(m, n, device="cuda", dtype=torch.bfloat16)
+    res = torch.randn(m, n, device="cuda", dtype=torch.bfloat16)
+    bias = torch.randn(n, device="cuda", dtype=torch.bfloat16)
+    fl = 2.0 * m * n * k
+    cases = {
+        "plain bf16 out": lambda: K.gemm(a, bt, out),
+        "plain fp32 out": lambda: K.gemm(a, bt, out32),
+        "fp32 accumulate": lambda: K.gemm(a, bt, out32, accumulate=True),
+        "+bias": lambda: K.gemm(a, bt, out, bias=bias),
+        "+bias+gelu": lambda: K.gemm(a, bt, out, bias=bias, act="gelu"),
+        "+bias+gelu+save pre": lambda: K.gemm(a, bt, out, bias=bias, act="gelu", pre=pre),
+        "+bias+residual": lambda: K.gemm(a, bt, out, bias=bias, resid=res),
+        "bwd aux (no act)": lambda: K.gemm(a, bt, out, bwd=True, aux=pre),
+        "bwd aux gelu'": lambda: K.gemm(a, bt, out, bwd=True, aux=pre, act="gelu"),
+        "bwd aux silu'": lambda: K.gemm(a, bt, out, bwd=True, aux=pre, act="silu"),
+    }
+    for name, fn in cases.items():
+        for bn in (128, 256):
+            import functools
+        t = _time(fn)
+        print(f"  {name:24s} {t * 1e3:8.1f} us  {fl / t / 1e9:7.1f} TFLOP/s", flush=True)
     return True
 
 
