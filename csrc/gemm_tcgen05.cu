@@ -48,7 +48,13 @@ struct GemmDev {
   uint32_t drop_thresh16;
   float drop_scale;
   int vec_d, vec_pre, vec_aux, vec_res;  // 16-byte vector access allowed
+  int epi_kind;                          // EPI_*: compile-time specialised epilogue, or EPI_GENERIC
 };
+
+// Specialised epilogues (fully vectorised, no run-time feature tests in the inner loop). Anything
+// else - dropout, SiLU, odd alignments, partial 4-column groups - takes EPI_GENERIC.
+enum { EPI_GENERIC = 0, EPI_PLAIN = 1, EPI_PLAIN_F32 = 2, EPI_BIAS = 3, EPI_BIAS_RESID = 4, EPI_BIAS_GELU_PRE = 5,
+       EPI_BWD_GELU = 6 };
 
 template <int BN>
 struct GemmCfg {
@@ -91,6 +97,89 @@ __device__ __forceinline__ TileCoord tile_coord(const GemmDev& p, int tile, int 
 }
 
 __device__ __forceinline__ float bf16_bits_to_f(uint32_t v) { return __uint_as_float(v << 16); }
+
+template <int BN, int KIND>
+__device__ __forceinline__ void epilogue_tile_fast(const GemmDev& p, int row_base, int col_base, int n_limit, uint32_t taddr,
+                                                   float* stage, int lane) {
+  constexpr int CHUNKS = BN / 64;
+  constexpr bool HAS_BIAS = KIND == EPI_BIAS || KIND == EPI_BIAS_RESID || KIND == EPI_BIAS_GELU_PRE;
+  const int lrow = lane >> 3, lchunk = lane & 7;
+  if (row_base >= p.M || col_base >= n_limit) return;   // warp-uniform
+  const int rows_left = p.M - row_base;
+  const float alpha = p.alpha;
+  uint32_t r[32];
+  tmem_ld_32x32b_x32(taddr, r);
+#pragma unroll 1
+  for (int c = 0; c < CHUNKS; ++c) {
+    const int col0 = col_base + c * 32;
+    if (col0 >= n_limit) break;
+    tmem_ld_wait();
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float4 v4 = make_float4(__uint_as_float(r[j * 4 + 0]), __uint_as_float(r[j * 4 + 1]),
+                              __uint_as_float(r[j * 4 + 2]), __uint_as_float(r[j * 4 + 3]));
+      *reinterpret_cast<float4*>(stage + lane * 32 + ((j ^ (lane & 7)) << 2)) = v4;
+    }
+    __syncwarp();
+    if (c + 1 < CHUNKS && col0 + 32 < n_limit) tmem_ld_32x32b_x32(taddr + (c + 1) * 32, r);
+    const int col = col0 + lchunk * 4;
+    const bool col_ok = col < n_limit;      // n_limit is a multiple of 4 on this path
+    float b0 = 0.f, b1 = 0.f, b2 = 0.f, b3 = 0.f;
+    if (HAS_BIAS && col_ok) {
+      const uint2 bw = *reinterpret_cast<const uint2*>(p.bias + col);
+      b0 = bf16_bits_to_f(bw.x & 0xFFFF); b1 = bf16_bits_to_f(bw.x >> 16);
+      b2 = bf16_bits_to_f(bw.y & 0xFFFF); b3 = bf16_bits_to_f(bw.y >> 16);
+    }
+    const size_t row0 = static_cast<size_t>(row_base + lrow);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int lr = i * 4 + lrow;
+      if (i * 4 >= rows_left) break;        // warp-uniform
+      if (lr < rows_left && col_ok) {
+        const size_t row = row0 + i * 4;
+        const float4 a4 = *reinterpret_cast<const float4*>(stage + lr * 32 + ((lchunk ^ (lr & 7)) << 2));
+        float v0 = a4.x * alpha + b0, v1 = a4.y * alpha + b1, v2 = a4.z * alpha + b2, v3 = a4.w * alpha + b3;
+        if (KIND == EPI_BIAS_GELU_PRE) {
+          __nv_bfloat162 t0 = __floats2bfloat162_rn(v0, v1), t1 = __floats2bfloat162_rn(v2, v3);
+          *reinterpret_cast<uint2*>(p.pre + row * p.ldpre + col) =
+              make_uint2(*reinterpret_cast<uint32_t*>(&t0), *reinterpret_cast<uint32_t*>(&t1));
+          v0 = gelu_f(__bfloat162float(t0.x)); v1 = gelu_f(__bfloat162float(t0.y));
+          v2 = gelu_f(__bfloat162float(t1.x)); v3 = gelu_f(__bfloat162float(t1.y));
+        }
+        if (KIND == EPI_BWD_GELU) {
+          const uint2 w = *reinterpret_cast<const uint2*>(p.aux + row * p.ldaux + col);
+          v0 *= gelu_grad_f(bf16_bits_to_f(w.x & 0xFFFF)); v1 *= gelu_grad_f(bf16_bits_to_f(w.x >> 16));
+          v2 *= gelu_grad_f(bf16_bits_to_f(w.y & 0xFFFF)); v3 *= gelu_grad_f(bf16_bits_to_f(w.y >> 16));
+        }
+        if (KIND == EPI_BIAS_RESID) {
+          const uint2 w = *reinterpret_cast<const uint2*>(p.resid + row * p.ldres + col);
+          v0 += bf16_bits_to_f(w.x & 0xFFFF); v1 += bf16_bits_to_f(w.x >> 16);
+          v2 += bf16_bits_to_f(w.y & 0xFFFF); v3 += bf16_bits_to_f(w.y >> 16);
+        }
+        if (KIND == EPI_PLAIN_F32) {
+          float* dp = reinterpret_cast<float*>(p.d) + row * p.ldd + col;
+          float4 o = make_float4(v0, v1, v2, v3);
+          if (p.accumulate) {
+            const float4 c4 = *reinterpret_cast<const float4*>(dp);
+            o.x += c4.x; o.y += c4.y; o.z += c4.z; o.w += c4.w;
+          }
+          *reinterpret_cast<float4*>(dp) = o;
+        } else {
+          __nv_bfloat162 t0 = __floats2bfloat162_rn(v0, v1), t1 = __floats2bfloat162_rn(v2, v3);
+          *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.d) + row * p.ldd + col) =
+              make_uint2(*reinterpret_cast<uint32_t*>(&t0), *reinterpret_cast<uint32_t*>(&t1));
+        }
+      }
+    }
+    __syncwarp();
+  }
+  tmem_ld_wait();
+}
+
+// Dispatch once per tile on the epilogue kind (uniform across the kernel).
+template <int BN>
+__device__ __forceinline__ void epilogue_dispatch(const GemmDev& p, int row_base, int col_base, int n_limit, uint32_t taddr,
+                                                  float* stage, const uint64_t* seed_tab, uint64_t seed, int lane);
 
 // Epilogue of one warp for one tile: rows [row_base, row_base+32) x columns [col_base, col_base+BN/2)
 // of the output, accumulator at TMEM address `taddr` (lane quadrant, stage and column half already
@@ -236,6 +325,20 @@ __device__ __forceinline__ void epilogue_tile(const GemmDev& p, int row_base, in
     __syncwarp();   // staging is reused by the next chunk
   }
   if (warp_active) tmem_ld_wait();
+}
+
+template <int BN>
+__device__ __forceinline__ void epilogue_dispatch(const GemmDev& p, int row_base, int col_base, int n_limit, uint32_t taddr,
+                                                  float* stage, const uint64_t* seed_tab, uint64_t seed, int lane) {
+  switch (p.epi_kind) {
+    case EPI_PLAIN: epilogue_tile_fast<BN, EPI_PLAIN>(p, row_base, col_base, n_limit, taddr, stage, lane); break;
+    case EPI_PLAIN_F32: epilogue_tile_fast<BN, EPI_PLAIN_F32>(p, row_base, col_base, n_limit, taddr, stage, lane); break;
+    case EPI_BIAS: epilogue_tile_fast<BN, EPI_BIAS>(p, row_base, col_base, n_limit, taddr, stage, lane); break;
+    case EPI_BIAS_RESID: epilogue_tile_fast<BN, EPI_BIAS_RESID>(p, row_base, col_base, n_limit, taddr, stage, lane); break;
+    case EPI_BIAS_GELU_PRE: epilogue_tile_fast<BN, EPI_BIAS_GELU_PRE>(p, row_base, col_base, n_limit, taddr, stage, lane); break;
+    case EPI_BWD_GELU: epilogue_tile_fast<BN, EPI_BWD_GELU>(p, row_base, col_base, n_limit, taddr, stage, lane); break;
+    default: epilogue_tile<BN>(p, row_base, col_base, n_limit, taddr, stage, seed_tab, seed, lane); break;
+  }
 }
 
 template <int BN, int A_MN, int B_MN>
@@ -406,7 +509,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
       TileCoord tc = tile_coord(p, tile, m_tiles, BN);
       mbar_wait(&tmem_full[as], aphase);
       tc_fence_after();
-      epilogue_tile<BN>(p, tc.m0 + quad * 32, tc.n0 + half * (BN / 2), tc.n_limit,
+      epilogue_dispatch<BN>(p, tc.m0 + quad * 32, tc.n0 + half * (BN / 2), tc.n_limit,
                         tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + as * BN + half * (BN / 2), stage, seed_tab,
                         seed, lane);
       tc_fence_before();
@@ -638,7 +741,7 @@ gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
       TileCoord tc = coord(tile);
       mbar_wait(&tmem_full[as], aphase);
       tc_fence_after();
-      epilogue_tile<BN>(p, tc.m0 + static_cast<int>(rank) * BM + quad * 32, tc.n0 + half * (BN / 2), tc.n_limit,
+      epilogue_dispatch<BN>(p, tc.m0 + static_cast<int>(rank) * BM + quad * 32, tc.n0 + half * (BN / 2), tc.n_limit,
                         tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + as * BN + half * (BN / 2), stage, seed_tab,
                         seed, lane);
       tc_fence_before();
@@ -808,6 +911,27 @@ extern "C" int b200_gemm_bf16(const b200_gemm_args* args, void* stream) {
   dev.vec_aux = a.aux && aligned16(a.aux) && (a.ldaux % 4 == 0) && cols_ok;
   dev.vec_res = a.resid && aligned16(a.resid) && (a.ldres % 4 == 0) && cols_ok;
 
+  {
+    const bool n4 = (a.n % 4 == 0) && cols_ok;
+    const bool no_drop = dev.drop_key == nullptr;
+    const bool bias_ok = a.bias == nullptr || (reinterpret_cast<uintptr_t>(a.bias) & 7) == 0;
+    int kind = EPI_GENERIC;
+    if (n4 && no_drop && dev.vec_d && bias_ok) {
+      if (a.bwd) {
+        if (a.aux == nullptr && a.act == B200_ACT_NONE) kind = a.d_fp32 ? EPI_PLAIN_F32 : EPI_PLAIN;
+        else if (a.aux != nullptr && dev.vec_aux && a.act == B200_ACT_GELU && !a.d_fp32) kind = EPI_BWD_GELU;
+      } else if (a.bias == nullptr && a.pre == nullptr && a.resid == nullptr && a.act == B200_ACT_NONE) {
+        kind = a.d_fp32 ? EPI_PLAIN_F32 : EPI_PLAIN;
+      } else if (!a.d_fp32 && a.bias != nullptr && a.act == B200_ACT_NONE && a.pre == nullptr) {
+        if (a.resid == nullptr) kind = EPI_BIAS;
+        else if (dev.vec_res) kind = EPI_BIAS_RESID;
+      } else if (!a.d_fp32 && a.bias != nullptr && a.act == B200_ACT_GELU && a.pre != nullptr && dev.vec_pre &&
+                 a.resid == nullptr) {
+        kind = EPI_BIAS_GELU_PRE;
+      }
+    }
+    dev.epi_kind = kind;
+  }
   int bn = a.block_n;
   if (bn == 0) {
     int n_eff = a.b_shard_mode == 2 ? a.b_shard_len : a.n;
