@@ -49,6 +49,7 @@ struct GemmDev {
   float drop_scale;
   int vec_d, vec_pre, vec_aux, vec_res;  // 16-byte vector access allowed
   int epi_kind;                          // EPI_*: compile-time specialised epilogue, or EPI_GENERIC
+  int k_splits, atomic_out;              // split-K: tile index also selects a K range; partials are red.add-ed
 };
 
 // Specialised epilogues (fully vectorised, no run-time feature tests in the inner loop). Anything
@@ -131,6 +132,28 @@ __device__ __forceinline__ void epilogue_tile_fast(const GemmDev& p, int row_bas
       b2 = bf16_bits_to_f(bw.y & 0xFFFF); b3 = bf16_bits_to_f(bw.y >> 16);
     }
     const size_t row0 = static_cast<size_t>(row_base + lrow);
+    // kinds that read global memory in the epilogue: issue all eight loads of this chunk first (the
+    // output stores below could alias them as far as the compiler knows, so it would not)
+    constexpr bool LOADS8 = KIND == EPI_BWD_GELU || KIND == EPI_BIAS_RESID;
+    uint2 ld8[LOADS8 ? 8 : 1];
+    float4 acc8[KIND == EPI_PLAIN_F32 ? 8 : 1];
+    if (LOADS8) {
+      const __nv_bfloat16* src = KIND == EPI_BWD_GELU ? p.aux : p.resid;
+      const int lds = KIND == EPI_BWD_GELU ? p.ldaux : p.ldres;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        ld8[i] = make_uint2(0u, 0u);
+        if (i * 4 + lrow < rows_left && col_ok) ld8[i] = *reinterpret_cast<const uint2*>(src + (row0 + i * 4) * lds + col);
+      }
+    }
+    if (KIND == EPI_PLAIN_F32 && p.accumulate && !p.atomic_out) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        acc8[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (i * 4 + lrow < rows_left && col_ok)
+          acc8[i] = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.d) + (row0 + i * 4) * p.ldd + col);
+      }
+    }
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       const int lr = i * 4 + lrow;
@@ -147,23 +170,27 @@ __device__ __forceinline__ void epilogue_tile_fast(const GemmDev& p, int row_bas
           v2 = gelu_f(__bfloat162float(t1.x)); v3 = gelu_f(__bfloat162float(t1.y));
         }
         if (KIND == EPI_BWD_GELU) {
-          const uint2 w = *reinterpret_cast<const uint2*>(p.aux + row * p.ldaux + col);
+          const uint2 w = ld8[LOADS8 ? i : 0];
           v0 *= gelu_grad_f(bf16_bits_to_f(w.x & 0xFFFF)); v1 *= gelu_grad_f(bf16_bits_to_f(w.x >> 16));
           v2 *= gelu_grad_f(bf16_bits_to_f(w.y & 0xFFFF)); v3 *= gelu_grad_f(bf16_bits_to_f(w.y >> 16));
         }
         if (KIND == EPI_BIAS_RESID) {
-          const uint2 w = *reinterpret_cast<const uint2*>(p.resid + row * p.ldres + col);
+          const uint2 w = ld8[LOADS8 ? i : 0];
           v0 += bf16_bits_to_f(w.x & 0xFFFF); v1 += bf16_bits_to_f(w.x >> 16);
           v2 += bf16_bits_to_f(w.y & 0xFFFF); v3 += bf16_bits_to_f(w.y >> 16);
         }
         if (KIND == EPI_PLAIN_F32) {
           float* dp = reinterpret_cast<float*>(p.d) + row * p.ldd + col;
-          float4 o = make_float4(v0, v1, v2, v3);
-          if (p.accumulate) {
-            const float4 c4 = *reinterpret_cast<const float4*>(dp);
-            o.x += c4.x; o.y += c4.y; o.z += c4.z; o.w += c4.w;
+          if (p.atomic_out) {   // split-K partial sums meet in memory
+            asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(dp), "f"(v0), "f"(v1), "f"(v2), "f"(v3) : "memory");
+          } else {
+            float4 o = make_float4(v0, v1, v2, v3);
+            if (p.accumulate) {
+              const float4 c4 = acc8[KIND == EPI_PLAIN_F32 ? i : 0];
+              o.x += c4.x; o.y += c4.y; o.z += c4.z; o.w += c4.w;
+            }
+            *reinterpret_cast<float4*>(dp) = o;
           }
-          *reinterpret_cast<float4*>(dp) = o;
         } else {
           __nv_bfloat162 t0 = __floats2bfloat162_rn(v0, v1), t1 = __floats2bfloat162_rn(v2, v3);
           *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.d) + row * p.ldd + col) =
@@ -365,7 +392,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
     n_tiles = ((p.shard_len + BN - 1) / BN) * p.nsrc;
   else
     n_tiles = (p.N + BN - 1) / BN;
-  const int num_tiles = m_tiles * n_tiles;
+  const int num_tiles = m_tiles * n_tiles * p.k_splits;
   int kps = 0, nk;
   if (p.shard_mode == 1) {
     // TMA needs the innermost coordinate 16-byte aligned. A shard that starts at an A column that
@@ -377,6 +404,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
   } else {
     nk = (p.K + BK - 1) / BK;
   }
+  // split-K (never combined with K-sharded B): split s of a tile covers k blocks [s*nk_split, ...)
+  const int nk_total = nk;
+  const int nk_split = (nk_total + p.k_splits - 1) / p.k_splits;
+  const int mn_tiles = m_tiles * n_tiles;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tma_a);
@@ -403,8 +434,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        TileCoord tc = tile_coord(p, tile, m_tiles, BN);
-        for (int it = 0; it < nk; ++it) {
+        const int split = tile / mn_tiles;
+        TileCoord tc = tile_coord(p, tile - split * mn_tiles, m_tiles, BN);
+        const int it_end = min(nk_total, (split + 1) * nk_split);
+        for (int it = split * nk_split; it < it_end; ++it) {
           int a_k, b_k, b_src;
           if (p.shard_mode == 1) {
             int s = it / kps, kb = it - s * kps;
@@ -461,7 +494,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
       mbar_wait(&tmem_empty[as], aphase ^ 1);
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + as * BN;
-      for (int it = 0; it < nk; ++it) {
+      const int split = tile / mn_tiles;
+      const int it_begin = split * nk_split, it_end = min(nk_total, (split + 1) * nk_split);
+      for (int it = it_begin; it < it_end; ++it) {
         mbar_wait(&full_bar[stage], phase);
         tc_fence_after();
         if (lane == 0) {
@@ -471,10 +506,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
           for (int k = 0; k < BK / UMMA_K; ++k) {
             uint64_t da = umma_smem_desc(sa + k * A_KSTEP, A_LBO, A_SBO);
             uint64_t db = umma_smem_desc(sb + k * B_KSTEP, B_LBO, B_SBO);
-            umma_bf16(d_tmem, da, db, idesc, (it | k) ? 1u : 0u);
+            umma_bf16(d_tmem, da, db, idesc, ((it - it_begin) | k) ? 1u : 0u);
           }
           umma_commit(&empty_bar[stage]);
-          if (it == nk - 1) umma_commit(&tmem_full[as]);
+          if (it == it_end - 1) umma_commit(&tmem_full[as]);
         }
         __syncwarp();
         if (++stage == STAGES) {
@@ -506,7 +541,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
       const int as = local & 1;
       const uint32_t aphase = (local >> 1) & 1;
-      TileCoord tc = tile_coord(p, tile, m_tiles, BN);
+      TileCoord tc = tile_coord(p, tile % mn_tiles, m_tiles, BN);
       mbar_wait(&tmem_full[as], aphase);
       tc_fence_after();
       epilogue_dispatch<BN>(p, tc.m0 + quad * 32, tc.n0 + half * (BN / 2), tc.n_limit,
@@ -579,7 +614,8 @@ gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
     n_tiles = ((p.shard_len + BN - 1) / BN) * p.nsrc;
   else
     n_tiles = (p.N + BN - 1) / BN;
-  const int num_tiles = m_tiles * n_tiles;
+  const int mn_tiles = m_tiles * n_tiles;
+  const int num_tiles = mn_tiles * p.k_splits;
   int kps = 0, nk;
   if (p.shard_mode == 1) {
     kps = (p.shard_len + ((p.shard_len & 7) ? 7 : 0) + BK - 1) / BK;
@@ -587,6 +623,8 @@ gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
   } else {
     nk = (p.K + BK - 1) / BK;
   }
+  const int nk_total = nk;
+  const int nk_split = (nk_total + p.k_splits - 1) / p.k_splits;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tma_a);
@@ -638,10 +676,12 @@ gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
-        TileCoord tc = coord(tile);
+        const int split = tile / mn_tiles;
+        TileCoord tc = coord(tile - split * mn_tiles);
         const int my_m0 = tc.m0 + static_cast<int>(rank) * BM;
         const int my_bn = tc.b_n + static_cast<int>(rank) * BNH;
-        for (int it = 0; it < nk; ++it) {
+        const int it_end = min(nk_total, (split + 1) * nk_split);
+        for (int it = split * nk_split; it < it_end; ++it) {
           int a_k, b_k, b_src;
           if (p.shard_mode == 1) {
             int s = it / kps, kb = it - s * kps;
@@ -697,7 +737,9 @@ gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
         mbar_wait(&tmem_empty[as], aphase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + as * BN;
-        for (int it = 0; it < nk; ++it) {
+        const int split = tile / mn_tiles;
+        const int it_begin = split * nk_split, it_end = min(nk_total, (split + 1) * nk_split);
+        for (int it = it_begin; it < it_end; ++it) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
           if (lane == 0) {
@@ -707,10 +749,10 @@ gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
             for (int k = 0; k < BK / UMMA_K; ++k) {
               uint64_t da = umma_smem_desc(sa + k * A_KSTEP, A_LBO, A_SBO);
               uint64_t db = umma_smem_desc(sb + k * B_KSTEP, B_LBO, B_SBO);
-              umma_bf16_pair(d_tmem, da, db, idesc, (it | k) ? 1u : 0u);
+              umma_bf16_pair(d_tmem, da, db, idesc, ((it - it_begin) | k) ? 1u : 0u);
             }
             umma_commit_pair(&empty_bar[stage]);
-            if (it == nk - 1) umma_commit_pair(&tmem_full[as]);
+            if (it == it_end - 1) umma_commit_pair(&tmem_full[as]);
           }
           __syncwarp();
           if (++stage == STAGES) {
@@ -738,7 +780,7 @@ gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
     for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, ++local) {
       const int as = local & 1;
       const uint32_t aphase = (local >> 1) & 1;
-      TileCoord tc = coord(tile);
+      TileCoord tc = coord(tile % mn_tiles);
       mbar_wait(&tmem_full[as], aphase);
       tc_fence_after();
       epilogue_dispatch<BN>(p, tc.m0 + static_cast<int>(rank) * BM + quad * 32, tc.n0 + half * (BN / 2), tc.n_limit,
@@ -794,7 +836,7 @@ static int launch_gemm(const b200_gemm_args& a, const GemmDev& dev, cudaStream_t
   int m_tiles = (a.m + BM - 1) / BM;
   int n_tiles = (a.b_shard_mode == 2) ? ((a.b_shard_len + BN - 1) / BN) * dev.nsrc
                                       : (a.n + BN - 1) / BN;
-  long long tiles = (long long)m_tiles * n_tiles;
+  long long tiles = (long long)m_tiles * n_tiles * dev.k_splits;
   int grid = (int)(tiles < num_sms() ? tiles : num_sms());
   kern<<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(ta, tb, dev);
   count_launch();
@@ -832,7 +874,7 @@ static int launch_gemm_pair(const b200_gemm_args& a, const GemmDev& dev, cudaStr
   }
   int m_tiles = (a.m + 2 * BM - 1) / (2 * BM);
   int n_tiles = (a.b_shard_mode == 2) ? ((a.b_shard_len + BN - 1) / BN) * dev.nsrc : (a.n + BN - 1) / BN;
-  long long tiles = (long long)m_tiles * n_tiles;
+  long long tiles = (long long)m_tiles * n_tiles * dev.k_splits;
   int clusters = (int)(tiles < num_sms() / 2 ? tiles : num_sms() / 2);
   kern<<<clusters * 2, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(ta, tb, dev);
   count_launch();
@@ -954,6 +996,36 @@ extern "C" int b200_gemm_bf16(const b200_gemm_args* args, void* stream) {
   // 1 = never, 2 = always (when the tile shape allows it)
   const bool pair_ok = bn >= 128;
   const bool use_pair = pair_ok && (a.pair_mode == 2 || (a.pair_mode == 0 && a.m > BM));
+  // split-K for fp32 outputs whose M x N grid cannot fill the chip (weight gradients: small M x N,
+  // K = tokens). Partial products are added in memory with red.global.add, after a memset when the
+  // call does not accumulate.
+  dev.k_splits = 1;
+  dev.atomic_out = 0;
+  if (dev.epi_kind == EPI_PLAIN_F32 && a.b_shard_mode != 1 && a.split_k != 1) {
+    const long long row_tile = use_pair ? 2 * BM : BM;
+    const long long mn = ((a.m + row_tile - 1) / row_tile) * (((a.b_shard_mode == 2 ? a.b_shard_len : a.n) + bn - 1) / bn) *
+                         (a.b_shard_mode == 2 ? nsrc : 1);
+    const long long slots = use_pair ? num_sms() / 2 : num_sms();
+    const int nkb = (a.k + BK - 1) / BK;
+    int splits = a.split_k > 1 ? a.split_k : (int)(slots / mn);
+    if (splits > nkb / 4) splits = nkb / 4;          // keep at least 4 k-blocks per split
+    if (splits > 16) splits = 16;
+    if (splits >= 2) {
+      int per = (nkb + splits - 1) / splits;
+      splits = (nkb + per - 1) / per;                // no empty split
+      if (splits >= 2) {
+        dev.k_splits = splits;
+        dev.atomic_out = 1;
+        if (!a.accumulate) {
+          if (a.ldd == a.n) {
+            B200_CUDA(cudaMemsetAsync(a.d, 0, sizeof(float) * (size_t)a.m * a.n, s));
+          } else {
+            B200_CUDA(cudaMemset2DAsync(a.d, sizeof(float) * (size_t)a.ldd, 0, sizeof(float) * (size_t)a.n, a.m, s));
+          }
+        }
+      }
+    }
+  }
   if (use_pair) {
     if (bn == 128) return dispatch_major_pair<128>(a, dev, s);
     return dispatch_major_pair<256>(a, dev, s);

@@ -16,7 +16,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 9
+#define B200_ABI_VERSION 10
 
 const char* b200_last_error(void);
 int b200_abi_version(void);
@@ -87,6 +87,9 @@ typedef struct b200_gemm_args {
   /* 0 = choose, 1 = single-CTA 128-row tiles, 2 = CTA pairs (cta_group::2, 256-row tiles: the two
    * SMs of a TPC share the B operand, one third less L2->SM traffic per flop) */
   int32_t pair_mode;
+  /* split-K for fp32 outputs: 0 = choose (when the M x N tile grid cannot fill the chip),
+   * 1 = never, n > 1 = that many K ranges. Partials are summed with red.global.add. */
+  int32_t split_k;
 } b200_gemm_args;
 
 int b200_gemm_bf16(const b200_gemm_args* args, void* stream);

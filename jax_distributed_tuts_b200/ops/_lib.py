@@ -10,7 +10,7 @@ from typing import Optional
 
 from . import _build
 
-ABI_VERSION = 9
+ABI_VERSION = 10
 
 _lib: Optional[C.CDLL] = None
 
@@ -44,6 +44,7 @@ class GemmArgs(C.Structure):
         ("drop_nsalt", C.c_int32), ("drop_rows_per_salt", C.c_int32),
         ("drop_salts", C.c_uint64 * 16),
         ("pair_mode", C.c_int32),
+        ("split_k", C.c_int32),
     ]
 
 

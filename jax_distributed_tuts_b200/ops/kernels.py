@@ -57,6 +57,7 @@ def gemm(
     ldb: Optional[int] = None,
     block_n: int = 0,
     pair_mode: int = 0,
+    split_k: int = 0,
 ) -> torch.Tensor:
     """``out (+)= epilogue(A @ B)`` on tcgen05 (see ``include/b200dist.h`` for the layouts).
 
@@ -119,6 +120,7 @@ def gemm(
                 args.drop_salts[i] = sv & 0xFFFFFFFFFFFFFFFF
     args.block_n = block_n
     args.pair_mode = pair_mode
+    args.split_k = split_k
     _lib.check(_lib.lib().b200_gemm_bf16(C.byref(args), _stream()))
     return out
 

@@ -112,6 +112,18 @@ def group_gemm_mnmajor():
         out.fill_(float("nan"))
         K.gemm(at, b, out, a_mn=True, b_mn=True)
         ok &= _report(f"both MN-major (wgrad) m={m} n={n} k={k}", _rel_err(out, ref), 2e-3)
+    # split-K (small M x N grid, long K): automatic and forced, with and without accumulation
+    m, n, k = 768, 1024, 4096
+    at = torch.randn(k, m, device="cuda", dtype=torch.bfloat16)
+    b = torch.randn(k, n, device="cuda", dtype=torch.bfloat16)
+    ref = at.float().t() @ b.float()
+    for sk in (0, 1, 3, 8):
+        for pm in (1, 2):
+            acc = torch.full((m, n), float("nan"), device="cuda")
+            K.gemm(at, b, acc, a_mn=True, b_mn=True, split_k=sk, pair_mode=pm)
+            ok &= _report(f"wgrad split_k={sk} pair_mode={pm}", _rel_err(acc, ref), 2e-3)
+            K.gemm(at, b, acc, a_mn=True, b_mn=True, split_k=sk, pair_mode=pm, accumulate=True)
+            ok &= _report(f"wgrad split_k={sk} pair_mode={pm} accumulate", _rel_err(acc, 2 * ref), 2e-3)
     # padded pitch (N=10 stored with ld 16)
     x = torch.randn(64, 512, device="cuda", dtype=torch.bfloat16)
     wbuf = torch.zeros(512, 16, device="cuda", dtype=torch.bfloat16)
