@@ -170,7 +170,7 @@ xent_block_bf16_kernel(__nv_bfloat16* __restrict__ logits, int ld, const int64_t
 // ------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 colsum_bf16_vec_kernel(const __nv_bfloat16* __restrict__ x, int ld, int rows, int cols, float* __restrict__ out,
-                       int row_chunks) {
+                       int row_chunks, int direct) {
   __shared__ float s[8][256 + 8];
   const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
   const int col = blockIdx.x * 256 + cx * 8;
@@ -208,7 +208,8 @@ colsum_bf16_vec_kernel(const __nv_bfloat16* __restrict__ x, int ld, int rows, in
     float t = 0.f;
 #pragma unroll
     for (int i = 0; i < 8; ++i) t += s[i][c];
-    atomicAdd(&out[blockIdx.x * 256 + c], t);
+    if (direct) out[blockIdx.x * 256 + c] = t;      // one block per column stripe, no accumulation
+    else atomicAdd(&out[blockIdx.x * 256 + c], t);
   }
 }
 
@@ -400,9 +401,10 @@ extern "C" int b200_colsum_bf16(const void* x, int ld, int rows, int cols, float
     int col_blocks = (cols + 255) / 256;
     int row_chunks = 1;
     while (col_blocks * row_chunks < num_sms() * 2 && rows / (row_chunks * 2) >= 32) row_chunks *= 2;
-    if (!accumulate) B200_CUDA(cudaMemsetAsync(out, 0, sizeof(float) * cols, s));
+    const int direct = (row_chunks == 1 && !accumulate) ? 1 : 0;
+    if (!accumulate && !direct) B200_CUDA(cudaMemsetAsync(out, 0, sizeof(float) * cols, s));
     colsum_bf16_vec_kernel<<<dim3(col_blocks, row_chunks), 256, 0, s>>>(static_cast<const __nv_bfloat16*>(x), ld, rows,
-                                                                      cols, out, row_chunks);
+                                                                      cols, out, row_chunks, direct);
   } else {
     int col_blocks = (cols + 31) / 32;
     int row_chunks = 1;

@@ -980,15 +980,18 @@ extern "C" int b200_gemm_bf16(const b200_gemm_args* args, void* stream) {
     if (n_eff <= 64) bn = 64;
     else if (n_eff <= 128) bn = 128;
     else {
-      // cost ~ waves * tile width; 128-wide tiles pay ~15% more shared-memory traffic per flop
+      // 128-wide tiles move twice the operand bytes per flop from L2 (measured: 30-50% slower on
+      // every transformer shape), so they only win when 256-wide tiles would leave most of the
+      // chip idle and the output cannot be split along K.
       long long m_tiles = (a.m + BM - 1) / BM;
       long long reps = a.b_shard_mode == 2 ? nsrc : 1;
       long long t256 = m_tiles * ((n_eff + 255) / 256) * reps;
       long long t128 = m_tiles * ((n_eff + 127) / 128) * reps;
       long long sms = num_sms();
-      double c256 = (double)((t256 + sms - 1) / sms) * 256.0;
-      double c128 = (double)((t128 + sms - 1) / sms) * 128.0 * 1.15;
-      bn = c256 <= c128 ? 256 : 128;
+      const bool splittable = dev.epi_kind == EPI_PLAIN_F32 && a.b_shard_mode != 1 && a.split_k != 1;
+      double e256 = (double)t256 / (double)(((t256 + sms - 1) / sms) * sms);
+      double e128 = (double)t128 / (double)(((t128 + sms - 1) / sms) * sms);
+      bn = (splittable || e256 * 1.5 >= e128) ? 256 : 128;
     }
   }
   cudaStream_t s = static_cast<cudaStream_t>(stream);
