@@ -178,7 +178,7 @@ def main() -> None:
             params = model.init({"params": model_rng}, x[:1])["params"]      # random init of the named architecture
             eng = GPT2Engine(gcfg, mesh, mode=c["mode"], batch_per_rank=B, seq_len=T, lr=3e-4,
                              num_minibatches=c["minibatches"], init_params=params, use_graph=not args.no_graph,
-                             shard_axis=shard_axis, comm_blocks=32)
+                             shard_axis=shard_axis, comm_blocks=128)
             del params
             state = eng.make_state(model, rng.rebase(model_rng))
         else:

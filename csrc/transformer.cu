@@ -79,7 +79,7 @@ layernorm_fwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* _
 // registers across rows; they are combined across the block's warps in shared memory once at the
 // end and flushed with one atomicAdd per column per block.
 template <int NCH>   // 16-byte chunks per lane: cols <= NCH * 256
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 2)
 layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
                      const __nv_bfloat16* __restrict__ gamma, const float* __restrict__ mean,
                      const float* __restrict__ rstd, const __nv_bfloat16* __restrict__ dresid,
@@ -93,11 +93,9 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
   const int lane = threadIdx.x & 31;
   const int wpb = blockDim.x >> 5;
   const int nchunk = cols >> 3;
-  float acc_g[NCH][8], acc_b[NCH][8], gam[NCH][8];
+  float acc_g[NCH][8], acc_b[NCH][8];
 #pragma unroll
   for (int c = 0; c < NCH; ++c) {
-    const int idx = c * 32 + lane;
-    if (idx < nchunk) unpack8(reinterpret_cast<const uint4*>(gamma)[idx], gam[c]);
 #pragma unroll
     for (int j = 0; j < 8; ++j) { acc_g[c][j] = 0.f; acc_b[c][j] = 0.f; }
   }
@@ -105,10 +103,9 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
     const uint4* xr = reinterpret_cast<const uint4*>(x + static_cast<size_t>(row) * cols);
     const uint4* dr = reinterpret_cast<const uint4*>(dy + static_cast<size_t>(row) * cols);
     const float mu = mean[row], rs = rstd[row];
-    float xh[NCH][8], dg[NCH][8];
-    uint4 xw[NCH], dw[NCH], rw[NCH];
+    uint4 xw[NCH], dw[NCH], rw[NCH];       // the row stays in registers as packed bf16
 #pragma unroll
-    for (int c = 0; c < NCH; ++c) {      // all loads of the row first
+    for (int c = 0; c < NCH; ++c) {        // all loads of the row first
       const int idx = c * 32 + lane;
       if (idx < nchunk) {
         xw[c] = xr[idx];
@@ -121,16 +118,16 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
     for (int c = 0; c < NCH; ++c) {
       const int idx = c * 32 + lane;
       if (idx < nchunk) {
-        float xv[8], dv[8];
+        float xv[8], dv[8], g[8];
         unpack8(xw[c], xv);
         unpack8(dw[c], dv);
+        unpack8(reinterpret_cast<const uint4*>(gamma)[idx], g);   // L1-resident
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-          xh[c][j] = (xv[j] - mu) * rs;
-          dg[c][j] = dv[j] * gam[c][j];
-          s1 += dg[c][j];
-          s2 += dg[c][j] * xh[c][j];
-          acc_g[c][j] += dv[j] * xh[c][j];
+          const float xh = (xv[j] - mu) * rs, dg = dv[j] * g[j];
+          s1 += dg;
+          s2 += dg * xh;
+          acc_g[c][j] += dv[j] * xh;
           acc_b[c][j] += dv[j];
         }
       }
@@ -142,9 +139,12 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
     for (int c = 0; c < NCH; ++c) {
       const int idx = c * 32 + lane;
       if (idx < nchunk) {
-        float o[8];
+        float xv[8], dv[8], g[8], o[8];
+        unpack8(xw[c], xv);
+        unpack8(dw[c], dv);
+        unpack8(reinterpret_cast<const uint4*>(gamma)[idx], g);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) o[j] = rs * (dg[c][j] - s1 - xh[c][j] * s2);
+        for (int j = 0; j < 8; ++j) o[j] = rs * (dv[j] * g[j] - s1 - (xv[j] - mu) * rs * s2);
         if (dresid != nullptr) {   // gradient arriving through the residual connection
           float rr[8];
           unpack8(rw[c], rr);
@@ -271,7 +271,7 @@ extern "C" int b200_layernorm_bwd(const void* dy, const void* x, const void* gam
                                   int rows, int cols, void* stream) {
   B200_REQUIRE(rows > 0 && cols > 0 && cols % 8 == 0 && cols <= 2048, "layernorm: cols=%d must be a multiple of 8, <= 2048", cols);
   int blocks = (rows + 7) / 8;
-  int cap = num_sms() * 4;
+  int cap = num_sms() * 2;
   if (blocks > cap) blocks = cap;
   auto launch = [&](auto kern) {
     kern<<<blocks, 256, 2 * cols * sizeof(float), static_cast<cudaStream_t>(stream)>>>(

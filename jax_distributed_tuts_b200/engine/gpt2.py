@@ -43,6 +43,7 @@ def _layer_leaves(i: int, c: int, bucket: int):
 class GPT2Engine(FusedEngine):
     def __init__(self, config, mesh: Mesh, *, mode: str = "dp", batch_per_rank: int, seq_len: Optional[int] = None,
                  lr: float = 3e-4, num_minibatches: int = 1, init_params: Optional[Dict] = None, **kw):
+        kw.setdefault("comm_blocks", 128)   # hundreds of MB per bucket: keep many bytes in flight
         super().__init__(mesh, mode=mode, lr=lr, num_minibatches=num_minibatches,
                          data_axis_name=config.get("data_axis_name", "data"), **kw)
         self.cfg = config
