@@ -240,27 +240,51 @@ fused_reduce_adamw_kernel(const CommDev c, const b200_seg* __restrict__ segs, in
   cross_rank_barrier(c, 1);
 }
 
-// All-gather of small tensors by peer loads: dst[seg.dst_off + p*nbytes ...] = peer_p[seg.src_off ...].
-// Used for sharded biases (a few hundred bytes per rank): no stand-alone collective launch, no
-// staging copy. The shards must already be published (the optimizer kernel's end barrier).
+// All-gather by peer loads: for every segment and every rank p, `rows` rows of `row_bytes` bytes are
+// copied from peer p (contiguous rows at src_off, pitch src_pitch) to
+// dst + dst_off + p*peer_stride (+ r*dst_pitch per row). Row shards use rows = 1; column shards
+// interleave the peers' column blocks into the full rows. No collective launch, no staging copy.
+// The shards must already be published (the optimizer kernel's end barrier).
 struct PeerPtrs { const uint8_t* p[MAX_WORLD]; };
-__global__ void peer_gather_kernel(const PeerPtrs peers, int world, const b200_gather_seg* __restrict__ segs,
-                                   int nseg, uint8_t* __restrict__ dst) {
+__global__ void __launch_bounds__(256)
+peer_gather_kernel(const PeerPtrs peers, int world, const b200_gather_seg* __restrict__ segs, int nseg,
+                   uint8_t* __restrict__ dst) {
+  const int64_t nthreads = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  const int64_t tid = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   for (int s = 0; s < nseg; ++s) {
     const b200_gather_seg sg = segs[s];
-    const bool vec = ((sg.src_off | sg.dst_off | sg.nbytes) & 15) == 0;
+    const bool vec = ((sg.src_off | sg.dst_off | sg.row_bytes | sg.src_pitch | sg.dst_pitch | sg.peer_stride) & 15) == 0;
     for (int p = blockIdx.y; p < world; p += gridDim.y) {
       const uint8_t* src = peers.p[p] + sg.src_off;
-      uint8_t* d = dst + sg.dst_off + static_cast<int64_t>(p) * sg.nbytes;
+      uint8_t* d = dst + sg.dst_off + static_cast<int64_t>(p) * sg.peer_stride;
       if (vec) {
-        const int64_t n16 = sg.nbytes >> 4;
-        for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n16;
-             i += static_cast<int64_t>(gridDim.x) * blockDim.x)
-          reinterpret_cast<uint4*>(d)[i] = reinterpret_cast<const uint4*>(src)[i];
+        const int64_t rb16 = sg.row_bytes >> 4;
+        const int64_t n16 = rb16 * sg.rows;
+        constexpr int U = 4;
+        for (int64_t i0 = tid; i0 < n16; i0 += nthreads * U) {
+          uint4 v[U];
+          int64_t doff[U];
+          bool ok[U];
+#pragma unroll
+          for (int u = 0; u < U; ++u) {
+            const int64_t i = i0 + u * nthreads;
+            ok[u] = i < n16;
+            const int64_t ii = ok[u] ? i : 0;
+            const int64_t r = sg.rows == 1 ? 0 : static_cast<int64_t>(static_cast<uint32_t>(ii) / static_cast<uint32_t>(rb16));
+            const int64_t c = ii - r * rb16;
+            doff[u] = r * sg.dst_pitch + (c << 4);
+            if (ok[u]) v[u] = *reinterpret_cast<const uint4*>(src + r * sg.src_pitch + (c << 4));
+          }
+#pragma unroll
+          for (int u = 0; u < U; ++u)
+            if (ok[u]) *reinterpret_cast<uint4*>(d + doff[u]) = v[u];
+        }
       } else {
-        for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < sg.nbytes;
-             i += static_cast<int64_t>(gridDim.x) * blockDim.x)
-          d[i] = src[i];
+        const int64_t n = sg.row_bytes * sg.rows;
+        for (int64_t i = tid; i < n; i += nthreads) {
+          const int64_t r = i / sg.row_bytes, c = i - r * sg.row_bytes;
+          d[r * sg.dst_pitch + c] = src[r * sg.src_pitch + c];
+        }
       }
     }
   }
@@ -349,6 +373,7 @@ extern "C" int b200_peer_gather(void* const* peer_base, int world, const b200_ga
     pp.p[i] = static_cast<const uint8_t*>(peer_base[i]);
   }
   if (blocks <= 0) blocks = 4;
+  if (blocks * world > 4 * num_sms()) blocks = 4 * num_sms() / world;
   peer_gather_kernel<<<dim3(blocks, world), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       pp, world, segs_dev, nseg, static_cast<uint8_t*>(dst));
   count_launch();

@@ -16,7 +16,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 10
+#define B200_ABI_VERSION 11
 
 const char* b200_last_error(void);
 int b200_abi_version(void);
@@ -256,12 +256,16 @@ int b200_fused_reduce_adamw(const b200_comm_ctx* ctx, const b200_seg* segs_dev, 
                             const b200_adamw_hparams* hp, int32_t* step_count, int bump_step,
                             const float* step_metrics, float* metrics_acc, int nmetrics,
                             int blocks, void* stream);
-/* All-gather of small tensors through peer loads (no collective launch): for every segment and
- * every rank p, dst[dst_off + p*nbytes, +nbytes) = peer_base[p][src_off, +nbytes).
- * The FSDP engine uses it for sharded biases; the big weights are never gathered (the GEMM's
- * TMA producer reads the shards in place). Reference: all_gather at param_sharding.py:140. */
+/* All-gather through peer loads (no collective launch): for every segment and every rank p, `rows`
+ * rows of `row_bytes` bytes are read from peer_base[p] + src_off (row pitch src_pitch) and written
+ * to dst + dst_off + p*peer_stride (row pitch dst_pitch). Row shards: rows = 1 and peer_stride =
+ * row_bytes; column shards: peer_stride = row_bytes and dst_pitch = the full row. The FSDP engines
+ * use it for sharded biases and, when the consuming GEMM has many row tiles, to assemble a layer's
+ * weights once per use, prefetched one layer ahead (peer memory is not cached in the local L2, so
+ * the in-GEMM gather would otherwise re-pull each weight tile for every row tile).
+ * Reference: all_gather at param_sharding.py:140. */
 typedef struct b200_gather_seg {
-  int64_t src_off, dst_off, nbytes;
+  int64_t src_off, dst_off, row_bytes, rows, src_pitch, dst_pitch, peer_stride;
 } b200_gather_seg;
 int b200_peer_gather(void* const* peer_base, int world, const b200_gather_seg* segs_dev, int nseg,
                      void* dst, int blocks, void* stream);

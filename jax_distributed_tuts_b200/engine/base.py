@@ -170,7 +170,7 @@ class FusedEngine:
     def __init__(self, mesh: Mesh, *, mode: str = "dp", lr: float, b1: float = 0.9, b2: float = 0.999,
                  eps: float = 1e-8, weight_decay: float = 1e-4, num_minibatches: int = 4,
                  data_axis_name: str = "data", shard_axis: Optional[str] = None, min_weight_size: int = 2 ** 18,
-                 use_graph: bool = True, comm_blocks: int = 16, overlap: bool = True):
+                 use_graph: bool = True, comm_blocks: int = 16, overlap: bool = True, fsdp_weights: str = "fused"):
         if not torch.cuda.is_available():
             raise RuntimeError("the fused engine needs a CUDA device; use the generic tier on CPU")
         _lib.lib()  # fail loudly if the kernel library is missing
@@ -189,6 +189,12 @@ class FusedEngine:
         self.use_graph = use_graph
         self.comm_blocks = comm_blocks
         self.overlap = overlap and self.world > 1
+        # FSDP weight access: "fused" = the GEMM's TMA producer reads the peer shards in place (best
+        # when the GEMM has few row tiles: every tile of the weight crosses NVLink once per row tile);
+        # "gather" = a layer's shards are assembled into a local buffer by peer loads once per use,
+        # prefetched on the side stream, and the GEMMs run on local (L2-cached) memory.
+        assert fsdp_weights in ("fused", "gather")
+        self.fsdp_weights = fsdp_weights if (mode == "fsdp" and self.S > 1) else "fused"
         self.graph: Optional[torch.cuda.CUDAGraph] = None
         self._last_metrics = None
         self._counts = [0, 0]
@@ -222,6 +228,10 @@ class FusedEngine:
             self.v = torch.zeros(self.local_total, dtype=torch.float32, device=d)
             self.pb = self.arena.tensor("bf16", torch.bfloat16, self.local_total)
             self._setup_bias_gather()
+            if self.fsdp_weights == "gather":
+                self.gather_stream = torch.cuda.Stream()
+                self._lru = 0
+                self._setup_bucket_gather()
         self.ctx = self._make_ctx(self.arena, "grad", "param" if self.mode == "dp" else None, "bf16", "signal")
         self._build_segments()
 
@@ -236,10 +246,15 @@ class FusedEngine:
             dim = None
             if numel > self.min_weight_size:
                 dim = choose_shard_dim(sp.shape, (None,) * len(sp.shape), self.S)
+                dim = self._override_shard_dim(path, sp.shape, dim)
             self.shard_dim[path] = dim
             self.loc_off[path] = loc
             loc = _round_up(loc + self._local_numel(path), 64)
         self.local_total = _round_up(loc, 64)
+
+    def _override_shard_dim(self, path: str, shape, dim):
+        """Hook for leaves with access patterns the generic rule does not know about."""
+        return dim
 
     def _local_shape2d(self, path: str) -> Tuple[int, int, int]:
         """(rows, cols, ld) of this rank's slice of a leaf in padded 2-D form."""
@@ -270,7 +285,7 @@ class FusedEngine:
         for path, sp in self.layout.leaves.items():
             if len(sp.shape) == 1 and self.shard_dim[path] is not None:
                 per = sp.cols // self.S
-                segs.append(GatherSeg(self.loc_off[path] * 2, off, per * 2))
+                segs.append(GatherSeg(self.loc_off[path] * 2, off, per * 2, 1, per * 2, per * 2, per * 2))
                 spans[path] = (off // 2, sp.cols)
                 off = _round_up(off + sp.cols * 2, 64)
         self._bias_nseg = len(segs)
@@ -282,6 +297,81 @@ class FusedEngine:
                 arr[i] = self.arena.peer_ptrs[r] + self.arena.offsets["bf16"]
             self._bias_peers = arr
             self.bias_full = {k: self._bias_buf[o: o + n_] for k, (o, n_) in spans.items()}
+
+    def _setup_bucket_gather(self) -> None:
+        """"gather" mode: per bucket, segment tables that assemble every sharded 2-D leaf of the bucket
+        into one of two rotating local buffers laid out like the DP working copy."""
+        from ..ops._lib import GatherSeg
+        self._gbuf_segs: Dict[int, Tuple[torch.Tensor, int]] = {}
+        per_bucket: Dict[int, list] = {}
+        size = 0
+        for (b0, b1) in self.layout.bucket_ranges:
+            size = max(size, b1 - b0)
+        for path, sp in self.layout.leaves.items():
+            dim = self.shard_dim[path]
+            if dim is None or len(sp.shape) == 1:
+                continue
+            r, c, ld = self._local_shape2d(path)
+            base = self.layout.bucket_ranges[sp.bucket][0]
+            dst = (sp.offset - base) * 2
+            if c != sp.cols:     # column shards: peers' column blocks interleave into the full rows
+                seg = GatherSeg(self.loc_off[path] * 2, dst, c * 2, sp.rows, ld * 2, sp.ld * 2, c * 2)
+            else:                # row shards: contiguous blocks
+                seg = GatherSeg(self.loc_off[path] * 2, dst, r * sp.ld * 2, 1, r * sp.ld * 2, r * sp.ld * 2, r * sp.ld * 2)
+            per_bucket.setdefault(sp.bucket, []).append(seg)
+        for b, segs in per_bucket.items():
+            self._gbuf_segs[b] = (self._segs_to_device(segs), len(segs))
+        self._gbufs = [torch.zeros(size, dtype=torch.bfloat16, device=self.device) for _ in range(2)]
+        self._gbuf_bucket = [None, None]
+        self._gbuf_events = [None, None]
+        arr = (C.c_void_p * self.S)()
+        for i, r_ in enumerate(self.shard_peer_ranks):
+            arr[i] = self.arena.peer_ptrs[r_] + self.arena.offsets["bf16"]
+        self._gather_peers = arr
+
+    def prefetch_bucket(self, b: int, keep: Optional[int] = None) -> None:
+        """Starts assembling bucket ``b``'s weights on the gather stream (no-op unless in gather
+        mode). ``keep`` names the bucket the caller is about to use: its buffer is not recycled."""
+        if self.fsdp_weights != "gather" or b not in self._gbuf_segs or b in self._gbuf_bucket:
+            return
+        if None in self._gbuf_bucket:
+            slot = self._gbuf_bucket.index(None)
+        else:
+            cands = [i for i in (0, 1) if self._gbuf_bucket[i] != keep]
+            slot = self._lru if self._lru in cands else cands[0]
+        main = torch.cuda.current_stream()
+        self.gather_stream.wait_stream(main)      # every reader of the recycled buffer is already queued on main
+        segs, nseg = self._gbuf_segs[b]
+        with torch.cuda.stream(self.gather_stream):
+            _lib.check(_lib.lib().b200_peer_gather(C.cast(self._gather_peers, C.POINTER(C.c_void_p)), self.S,
+                                                    segs.data_ptr(), nseg, self._gbufs[slot].data_ptr(), 32,
+                                                    self.gather_stream.cuda_stream))
+            ev = torch.cuda.Event()
+            ev.record(self.gather_stream)
+        self._gbuf_bucket[slot] = b
+        self._gbuf_events[slot] = ev
+        self._lru = 1 - slot
+
+    def _gathered(self, path: str) -> torch.Tensor:
+        sp = self.layout.leaves[path]
+        b = sp.bucket
+        if b not in self._gbuf_bucket:
+            self.prefetch_bucket(b, keep=b)
+        slot = self._gbuf_bucket.index(b)
+        ev = self._gbuf_events[slot]
+        if ev is not None:
+            torch.cuda.current_stream().wait_event(ev)
+            self._gbuf_events[slot] = None
+        base = self.layout.bucket_ranges[b][0]
+        o = sp.offset - base
+        return self._gbufs[slot][o: o + sp.rows * sp.ld].view(sp.rows, sp.ld)[:, : sp.cols]
+
+    def release_gathered(self) -> None:
+        """Forget which buckets the rotating buffers hold (call at step boundaries: the shards change)."""
+        if self.fsdp_weights == "gather":
+            self._gbuf_bucket = [None, None]
+            self._gbuf_events = [None, None]
+            self._lru = 0
 
     def _gather_small(self) -> None:
         if self.mode != "fsdp" or not self._bias_nseg:
@@ -457,6 +547,8 @@ class FusedEngine:
             return self.layout.view2d(self.pb, path), {}, None
         if self.shard_dim[path] is None or self.S == 1:
             return self._local_view(self.pb, path), {}, None
+        if self.fsdp_weights == "gather":
+            return self._gathered(path), {}, None
         r, c, ld = self._local_shape2d(path)
         srcs = [self.arena.peer_ptrs[g] + self.arena.offsets["bf16"] + self.loc_off[path] * 2
                 for g in self.shard_peer_ranks]

@@ -63,9 +63,6 @@ class GPT2Engine(FusedEngine):
             leaves += _layer_leaves(i, c, 1 + j)
         leaves += [("wte", (self.Vp, c), L + 1), ("wpe", (config.n_ctx, c), L + 1)]
         self._setup_buffers(FlatLayout(leaves, self.world))
-        if self.mode == "fsdp":
-            for path in ("wte", "wpe"):
-                assert self.shard_dim[path] in (None, 0), f"{path} must be row-sharded or replicated"
         d, M = self.device, self.M
         bf, f32 = torch.bfloat16, torch.float32
         self.tokens = torch.zeros(self.B, self.T, dtype=torch.int64, device=d)
@@ -87,6 +84,14 @@ class GPT2Engine(FusedEngine):
         self.rng_base = None
         if init_params is not None:
             self.load_params(init_params)
+
+    def _override_shard_dim(self, path: str, shape, dim):
+        # Embedding tables are consumed by row lookups: shard them on rows (or not at all). The
+        # reference's rule picks rows anyway whenever the table is taller than wide, which holds for
+        # every real configuration (50304 x C, 1024 x C).
+        if path in ("wte", "wpe"):
+            return 0 if shape[0] % self.S == 0 else None
+        return dim
 
     # ------------------------------------------------------------------ parameters ------------
     @staticmethod
@@ -147,13 +152,17 @@ class GPT2Engine(FusedEngine):
                 self._sync_bucket(b, last=False)
         self._sync_bucket(self.L + 1, last=True)
         K.rng_split_(self.rng_base, None, _rng.salt_word(next_rng), 0)
+        self.release_gathered()
 
     def _forward(self, tok: torch.Tensor) -> None:
         c = self.C
         self._embed(tok)
         x = self.x0
+        bucket_of = lambda layer: 1 + (self.L - 1 - layer)
+        self.prefetch_bucket(bucket_of(0))
         for i in range(self.L):
             p, A = f"h_{i}/", self.acts[i]
+            self.prefetch_bucket(bucket_of(i + 1) if i + 1 < self.L else self.L + 1, keep=bucket_of(i))   # next layer / the tied head
             K.layernorm_fwd(x, self.vec(p + "ln_1/scale"), self.vec(p + "ln_1/bias"), A["a"], A["mean1"], A["rstd1"])
             self.gemm_w(A["a"], p + "attn/c_attn/kernel", A["qkv"], bias=self.vec(p + "attn/c_attn/bias"))
             K.attention_fwd(A["qkv"], A["att"], A["lse"], self.mbB, self.T, self.Hh)
@@ -175,6 +184,7 @@ class GPT2Engine(FusedEngine):
         logits = self.logits[:, : self.V]
         K.softmax_xent_bf16_(logits, tgt.reshape(-1), grad_scale=1.0 / M, metrics=self.step_metrics)
         dlog = self.logits                                   # now the gradient (pad columns stay zero)
+        self.prefetch_bucket(1, keep=self.L + 1)             # top layer's weights while the head runs
         K.gemm(dlog, self.xf, g2("wte"), a_mn=True, b_mn=True, accumulate=acc)      # dwte = dlogits^T xf
         self.gemm_w(dlog, "wte", self.dm)                                            # dxf = dlogits wte
         dx, spare = self.dxa, self.dxb
@@ -187,6 +197,8 @@ class GPT2Engine(FusedEngine):
             self._sync_bucket_async(0)
         for j, i in enumerate(range(self.L - 1, -1, -1)):
             p, A = f"h_{i}/", self.acts[i]
+            if i > 0:
+                self.prefetch_bucket(1 + j + 1, keep=1 + j)  # the layer below, needed next
             # x2 = x1 + gelu(m2 Wfc + bfc) Wproj + bproj
             K.gemm(A["hact"], dx, g2(p + "mlp/c_proj/kernel"), a_mn=True, b_mn=True, accumulate=acc)
             K.colsum(dx, g1(p + "mlp/c_proj/bias"), accumulate=acc)

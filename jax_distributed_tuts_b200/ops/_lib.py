@@ -10,7 +10,7 @@ from typing import Optional
 
 from . import _build
 
-ABI_VERSION = 10
+ABI_VERSION = 11
 
 _lib: Optional[C.CDLL] = None
 
@@ -76,7 +76,8 @@ class Seg(C.Structure):
 
 
 class GatherSeg(C.Structure):
-    _fields_ = [("src_off", C.c_int64), ("dst_off", C.c_int64), ("nbytes", C.c_int64)]
+    _fields_ = [("src_off", C.c_int64), ("dst_off", C.c_int64), ("row_bytes", C.c_int64), ("rows", C.c_int64),
+                ("src_pitch", C.c_int64), ("dst_pitch", C.c_int64), ("peer_stride", C.c_int64)]
 
 
 SIGNAL_WORDS = 8192

@@ -51,10 +51,12 @@ def main():
             gen_losses.append(float(m["loss"][0]) / m["loss"][1])
         log("generic NCCL DP losses", [f"{x:.4f}" for x in gen_losses])
         ref = dict(tree_leaves_with_path(st.params))
-        for name, mode, mws in (("dp", "dp", 2 ** 18), ("fsdp", "fsdp", 2 ** 12)):
+        for name, mode, mws, fw in (("dp", "dp", 2 ** 18, "fused"), ("fsdp/fused", "fsdp", 2 ** 12, "fused"),
+                                    ("fsdp/gather", "fsdp", 2 ** 12, "gather")):
             try:
                 eng = GPT2Engine(cfg, mesh, mode=mode, batch_per_rank=per, seq_len=T, lr=lr, num_minibatches=1,
-                                 init_params=params, use_graph=True, min_weight_size=mws, comm_blocks=32)
+                                 init_params=params, use_graph=True, min_weight_size=mws, comm_blocks=32,
+                                 fsdp_weights=fw)
                 s2 = eng.make_state(model, rng.PRNGKey(5))
                 losses = []
                 for _ in range(steps):
@@ -94,10 +96,10 @@ def main():
         sparams = smodel.init({"params": rng.PRNGKey(1)}, gb.inputs[:1])["params"]
         stok = torch.randint(0, scfg.vocab_size, (8, 1025), generator=torch.Generator().manual_seed(rank))
         sb = Batch(stok[:, :1024].contiguous().pin_memory(), stok[:, 1:].contiguous().pin_memory())
-        for name, mode in (("dp", "dp"), ("fsdp", "fsdp")):
+        for name, mode, fw in (("dp", "dp", "fused"), ("fsdp/fused", "fsdp", "fused"), ("fsdp/gather", "fsdp", "gather")):
             try:
                 eng = GPT2Engine(scfg, mesh, mode=mode, batch_per_rank=8, seq_len=1024, lr=3e-4, init_params=sparams,
-                                 use_graph=True)
+                                 use_graph=True, fsdp_weights=fw)
                 s3 = eng.make_state(smodel, rng.PRNGKey(2))
                 for _ in range(4):
                     s3, m3 = eng.train_step(s3, None, sb)
