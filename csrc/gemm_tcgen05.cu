@@ -991,14 +991,18 @@ extern "C" int b200_gemm_bf16(const b200_gemm_args* args, void* stream) {
       const bool splittable = dev.epi_kind == EPI_PLAIN_F32 && a.b_shard_mode != 1 && a.split_k != 1;
       double e256 = (double)t256 / (double)(((t256 + sms - 1) / sms) * sms);
       double e128 = (double)t128 / (double)(((t128 + sms - 1) / sms) * sms);
-      bn = (splittable || e256 * 1.5 >= e128) ? 256 : 128;
+      // a problem that fits in one wave even with 128-wide tiles is latency-bound: more, smaller CTAs
+      if (t128 <= sms) bn = 128;
+      else bn = (splittable || e256 * 1.5 >= e128) ? 256 : 128;
     }
   }
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   // CTA pairs (256-row tiles) once the problem has at least two row tiles; pair_mode: 0 = auto,
   // 1 = never, 2 = always (when the tile shape allows it)
   const bool pair_ok = bn >= 128;
-  const bool use_pair = pair_ok && (a.pair_mode == 2 || (a.pair_mode == 0 && a.m > BM));
+  // (auto: only for problems large enough to amortise the cluster launch and the pair barriers)
+  const bool big = (long long)a.m * a.n * a.k >= (1LL << 27);
+  const bool use_pair = pair_ok && (a.pair_mode == 2 || (a.pair_mode == 0 && a.m > BM && big));
   // split-K for fp32 outputs whose M x N grid cannot fill the chip (weight gradients: small M x N,
   // K = tokens). Partial products are added in memory with red.global.add, after a memset when the
   // call does not accumulate.

@@ -193,7 +193,7 @@ class FusedEngine:
         # when the GEMM has few row tiles: every tile of the weight crosses NVLink once per row tile);
         # "gather" = a layer's shards are assembled into a local buffer by peer loads once per use,
         # prefetched on the side stream, and the GEMMs run on local (L2-cached) memory.
-        assert fsdp_weights in ("fused", "gather")
+        assert fsdp_weights in ("fused", "gather"), "engines resolve 'auto' before calling the base class"
         self.fsdp_weights = fsdp_weights if (mode == "fsdp" and self.S > 1) else "fused"
         self.graph: Optional[torch.cuda.CUDAGraph] = None
         self._last_metrics = None

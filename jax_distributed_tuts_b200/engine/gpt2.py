@@ -44,6 +44,9 @@ class GPT2Engine(FusedEngine):
     def __init__(self, config, mesh: Mesh, *, mode: str = "dp", batch_per_rank: int, seq_len: Optional[int] = None,
                  lr: float = 3e-4, num_minibatches: int = 1, init_params: Optional[Dict] = None, **kw):
         kw.setdefault("comm_blocks", 128)   # hundreds of MB per bucket: keep many bytes in flight
+        tokens = (batch_per_rank // num_minibatches) * (seq_len or config.n_ctx)
+        if kw.get("fsdp_weights", "auto") == "auto":   # many row tiles per GEMM: gather once per layer
+            kw["fsdp_weights"] = "gather" if tokens > 1024 else "fused"
         super().__init__(mesh, mode=mode, lr=lr, num_minibatches=num_minibatches,
                          data_axis_name=config.get("data_axis_name", "data"), **kw)
         self.cfg = config

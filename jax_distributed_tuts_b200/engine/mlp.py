@@ -42,6 +42,8 @@ class MLPEngine(FusedEngine):
     def __init__(self, config, mesh: Mesh, *, mode: str = "dp", batch_per_rank: int, lr: float,
                  num_minibatches: int = 4, min_weight_size: int = 2 ** 18, init_params: Optional[Dict] = None,
                  input_size: int = 784, fuse_minibatches: bool = True, **kw):
+        if kw.get("fsdp_weights", "auto") == "auto":   # few row tiles per GEMM: read the peers' shards from inside the GEMM
+            kw["fsdp_weights"] = "fused" if batch_per_rank <= 1024 else "gather"
         super().__init__(mesh, mode=mode, lr=lr, num_minibatches=num_minibatches,
                          data_axis_name=config.get("data_axis_name", "data"), min_weight_size=min_weight_size, **kw)
         self.cfg = config
@@ -117,6 +119,7 @@ class MLPEngine(FusedEngine):
         self._sync_bucket(1, last=True)
         # state.rng <- rebase(next_rng): the salt folds into the device-resident key in place
         K.rng_split_(self.rng_base, None, _rng.salt_word(next_rng), 0)
+        self.release_gathered()
 
     def _fwd_bwd(self, xs, lab, salts, rows_per_salt: int, *, accumulate: bool, last: bool) -> None:
         """Forward + backward of one row block (a minibatch, or all minibatches at once)."""
