@@ -138,3 +138,26 @@ def pp_worker(rank, world, n_stages, steps, microbatches):
             state, metrics = step(state, metrics, local)
     return {"params": state.params, "metrics": metrics, "stage": mesh.axis_index("pipe"),
             "data": mesh.axis_index("data")}
+
+
+def fsdp_ckpt_worker(rank, world, path):
+    from jax_distributed_tuts_b200 import checkpoint as ckpt
+    cfg = fsdp_config()
+    cfg.model.dropout_rate = 0.0
+    mesh = Mesh((world,), ("data",))
+    wrap = lambda m: fsdp.shard_module_params(m, axis_name="data", min_weight_size=16)
+    model = Classifier(cfg.model, dense_wrapper=wrap)
+    model_rng, batch = make_batch(cfg)
+    with mesh:
+        state = fsdp.init_model(model_rng, batch.inputs, model, learning_rate=1e-3)
+        step = fsdp.make_train_step_fsdp(mesh, num_minibatches=2)
+        state, _ = step(state, None, dp.shard_batch(batch))
+        ckpt.save_checkpoint(path, state, mesh=mesh)
+        import torch.distributed as dist
+        dist.barrier()
+        loaded = ckpt.load_checkpoint(path)
+        restored = ckpt.restore_params(state.params, loaded["params"], mesh=mesh)
+        k0, k1 = state.params["input_dense"]["kernel"], restored["input_dense"]["kernel"]
+        same = torch.equal(k0.value, k1.value) and k1.names == k0.names
+        same &= torch.equal(state.params["output_dense"]["bias"], restored["output_dense"]["bias"])
+    return {"reload_equal": bool(same), "local_shape": tuple(k1.value.shape)}
