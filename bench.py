@@ -116,7 +116,9 @@ def main() -> None:
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=10)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "baseline"],
+                    help="ours = fused engines; baseline = stock PyTorch+NCCL+cuBLAS reconstruction (baseline/); "
+                         "reference = the unmodified reference (not installable here)")
     ap.add_argument("--config", default="mlp_dp", choices=sorted(CONFIGS))
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -174,22 +176,61 @@ def main() -> None:
         y = torch.randint(0, c["classes"], (B,), generator=rng.uniform_generator(rng.fold_in(label_rng, rank))).pin_memory()
         h2d_bytes = int(x.numel() * 4 + y.numel() * 8)
     with mesh:
-        if is_gpt:
-            params = model.init({"params": model_rng}, x[:1])["params"]      # random init of the named architecture
-            eng = GPT2Engine(gcfg, mesh, mode=c["mode"], batch_per_rank=B, seq_len=T, lr=3e-4,
-                             num_minibatches=c["minibatches"], init_params=params, use_graph=not args.no_graph,
-                             shard_axis=shard_axis, comm_blocks=128)
-            del params
-            state = eng.make_state(model, rng.rebase(model_rng))
+        if args.impl == "baseline":
+            from baseline.torch_nccl import GPT2 as TGPT2, MLP as TMLP, BaselineTrainer
+            torch.manual_seed(cfg.seed)
+            if is_gpt:
+                tm = TGPT2(gcfg.n_layer, gcfg.n_head, gcfg.d_model, 50304, gcfg.n_ctx).to(device)
+                lr0 = 3e-4
+            else:
+                tm = TMLP(c["inp"], c["hidden"], c["classes"], 0.1).to(device)
+                lr0 = cfg.optimizer.learning_rate
+            tm.train()
+            trainer = BaselineTrainer(tm, mode=c["mode"], lr=lr0, minibatches=c["minibatches"], world=world, rank=rank)
+            xd, yd = torch.empty_like(x, device=device), torch.empty_like(y, device=device)
+            last = {}
+
+            def load_batch():
+                xd.copy_(x, non_blocking=True)
+                yd.copy_(y, non_blocking=True)
+
+            def run_step():
+                last["loss"] = trainer.step(xd, yd)
+
+            def api_step():
+                load_batch()
+                run_step()
+                return last["loss"].item()
+
+            backend, launches_per_step = "nccl" if world > 1 else "local", 0
         else:
-            init_state = dp.init_dp(model_rng, x[:4], model)
-            eng = MLPEngine(cfg.model, mesh, mode=c["mode"], batch_per_rank=B, lr=cfg.optimizer.learning_rate,
-                            num_minibatches=c["minibatches"], init_params=init_state.params, input_size=c["inp"],
-                            use_graph=not args.no_graph,
-                            min_weight_size=16 if c["mode"] == "fsdp" else 2 ** 18)
-            state = eng.make_state(model, init_state.rng)
-        step = dp.make_train_step_dp(mesh)
-        batch = Batch(x, y)
+            if is_gpt:
+                params = model.init({"params": model_rng}, x[:1])["params"]      # random init of the named architecture
+                eng = GPT2Engine(gcfg, mesh, mode=c["mode"], batch_per_rank=B, seq_len=T, lr=3e-4,
+                                 num_minibatches=c["minibatches"], init_params=params, use_graph=not args.no_graph,
+                                 shard_axis=shard_axis)
+                del params
+                state0 = eng.make_state(model, rng.rebase(model_rng))
+            else:
+                init_state = dp.init_dp(model_rng, x[:4], model)
+                eng = MLPEngine(cfg.model, mesh, mode=c["mode"], batch_per_rank=B, lr=cfg.optimizer.learning_rate,
+                                num_minibatches=c["minibatches"], init_params=init_state.params, input_size=c["inp"],
+                                use_graph=not args.no_graph,
+                                min_weight_size=16 if c["mode"] == "fsdp" else 2 ** 18)
+                state0 = eng.make_state(model, init_state.rng)
+            pub_step = dp.make_train_step_dp(mesh)      # the public entry point: step(state, metrics, batch)
+            batch = Batch(x, y)
+            holder = {"state": state0, "metrics": None}
+
+            def load_batch():
+                eng._load_batch(batch)
+
+            def run_step():
+                eng._run_step()
+
+            def api_step():
+                holder["state"], holder["metrics"] = pub_step(holder["state"], None, batch)
+                return holder["metrics"]["loss"][0].item()
 
         def sync():
             torch.cuda.synchronize()
@@ -198,9 +239,8 @@ def main() -> None:
                 torch.cuda.synchronize()
 
         # ---- warm-up (untimed): includes the eager step and the graph capture ----
-        metrics = None
         for _ in range(args.warmup):
-            state, metrics = step(state, metrics, batch)
+            api_step()
         sync()
         flush = torch.empty(256 << 20, dtype=torch.uint8, device=device)  # > 126 MB L2
 
@@ -211,9 +251,9 @@ def main() -> None:
         for _ in range(args.steps):
             flush.zero_()
             s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            eng._load_batch(batch)      # H2D of the step's inputs is outside the events (kernel-only number)
+            load_batch()                # H2D of the step's inputs is outside the events (kernel-only number)
             s.record()
-            eng._run_step()
+            run_step()
             e.record()
             evs.append((s, e))
         sync()
@@ -221,14 +261,12 @@ def main() -> None:
         clocks = sampler.stop() if sampler else None
 
         # ---- end-to-end region: public API, pinned H2D every step, loss read back every step ----
-        e2e_ms = None
+        e2e_ms, loss_val = None, None
         if not args.no_e2e:
-            metrics = None
             sync()
             t0 = time.perf_counter()
             for _ in range(args.steps):
-                state, metrics = step(state, None, batch)
-                _ = metrics["loss"][0].item()
+                loss_val = api_step()
             sync()
             e2e_ms = (time.perf_counter() - t0) * 1e3
 
@@ -236,7 +274,12 @@ def main() -> None:
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dev_ms, e2e_max = t[0].item(), t[1].item()
-        final_loss = metrics["loss"][0].item() / metrics["loss"][1] if metrics else None
+        if args.impl == "baseline":
+            final_loss = loss_val
+        else:
+            rows = eng._rows_per_step()
+            final_loss = (loss_val / rows) if loss_val is not None else None
+            backend, launches_per_step = eng.arena.backend, int(getattr(eng, "launches_per_step", 0))
 
     if rank == 0:
         gb = B * world
@@ -249,14 +292,14 @@ def main() -> None:
             "ms_per_step": ms_per_step,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "bf16", "data": "synthetic (random-normal inputs, uniform labels, random-init weights)",
-            "impl": "ours",
+            "impl": args.impl,
             "config": {"model": c["model"], "global_batch": gb, "per_gpu_batch": B, "minibatches": c["minibatches"],
                        "seq_len": c.get("seq"), "parallelism": ("dp2xfsdp%d" % (world // 2)) if (c.get("mesh2d") and world >= 4) else f"{c['mode']}{world}",
                        "optimizer": "adamw",
                        "name": args.config, "l2": "flushed between timed steps (256 MiB write)",
-                       "cuda_graph": not args.no_graph, "comm": eng.arena.backend},
-            "gpu_launches": int(getattr(eng, "launches_per_step", 0)) * args.steps,
-            "launches_per_step": int(getattr(eng, "launches_per_step", 0)),
+                       "cuda_graph": (not args.no_graph) and args.impl == "ours", "comm": backend},
+            "gpu_launches": launches_per_step * args.steps,
+            "launches_per_step": launches_per_step,
             "clocks": clocks,
             "final_loss": final_loss,
         }
@@ -267,7 +310,7 @@ def main() -> None:
         if is_gpt:
             toks = gb * c["seq"]
             out["tokens_per_s"] = toks / (ms_per_step * 1e-3)
-            n_params = sum(int(torch.tensor(sp.shape).prod()) for sp in eng.layout.leaves.values())
+            n_params = 124.4e6 if c["gpt"] == "small" else 354.8e6 if c["gpt"] == "medium" else 1e6
             flops = 6.0 * n_params * toks + 12.0 * gcfg.n_layer * gcfg.d_model * c["seq"] * toks * 0.5
             out["model_tflops_per_gpu"] = flops / (ms_per_step * 1e-3) / 1e12 / world
         print(json.dumps(out), flush=True)

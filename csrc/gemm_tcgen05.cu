@@ -988,12 +988,14 @@ extern "C" int b200_gemm_bf16(const b200_gemm_args* args, void* stream) {
       long long t256 = m_tiles * ((n_eff + 255) / 256) * reps;
       long long t128 = m_tiles * ((n_eff + 127) / 128) * reps;
       long long sms = num_sms();
-      const bool splittable = dev.epi_kind == EPI_PLAIN_F32 && a.b_shard_mode != 1 && a.split_k != 1;
+      const bool splittable = dev.epi_kind == EPI_PLAIN_F32 && a.b_shard_mode != 1 && a.split_k != 1 &&
+                              (a.k + BK - 1) / BK >= 8;   // enough K blocks to split
       double e256 = (double)t256 / (double)(((t256 + sms - 1) / sms) * sms);
       double e128 = (double)t128 / (double)(((t128 + sms - 1) / sms) * sms);
       // a problem that fits in one wave even with 128-wide tiles is latency-bound: more, smaller CTAs
-      if (t128 <= sms) bn = 128;
-      else bn = (splittable || e256 * 1.5 >= e128) ? 256 : 128;
+      if (splittable) bn = 256;            // split-K fills the chip; wide tiles halve L2 traffic
+      else if (t128 <= sms) bn = 128;
+      else bn = (e256 * 1.5 >= e128) ? 256 : 128;
     }
   }
   cudaStream_t s = static_cast<cudaStream_t>(stream);
