@@ -31,7 +31,7 @@ def log(*a):
 def main():
     rank, world, device = init_from_env()
     ok_all = True
-    cfg = gpt2_config("tiny", n_layer=2, d_model=256, n_head=4, vocab_size=1024)
+    cfg = gpt2_config("tiny", n_layer=2, d_model=256, n_head=4, vocab_size=1024, n_ctx=256)
     model = GPT2(cfg)
     per, T, steps, lr = 4, 128, 3, 1e-3
     g = torch.Generator().manual_seed(0)
