@@ -95,6 +95,7 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* 
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
+  pdl_sync();
   const uint32_t tmem_s = tmem_base;          // 128 columns
   const uint32_t tmem_o = tmem_base + 128;    // 64 columns
 
@@ -244,6 +245,7 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* 
 __global__ void attention_bwd_prep_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ d_o,
                                           float* __restrict__ delta, float* __restrict__ dq_accum, int batch, int seq,
                                           int heads) {
+  pdl_sync();
   const int lane = threadIdx.x & 31;
   const int64_t rows = static_cast<int64_t>(batch) * seq * heads;
   for (int64_t row = static_cast<int64_t>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5); row < rows;
@@ -266,6 +268,7 @@ __global__ void attention_bwd_prep_kernel(const __nv_bfloat16* __restrict__ o, c
 // dq bf16 <- dq_accum fp32, written into dqkv[..., 0, h, :]
 __global__ void attention_bwd_post_kernel(const float* __restrict__ dq_accum, __nv_bfloat16* __restrict__ dqkv,
                                           int64_t rows_bt, int heads) {
+  pdl_sync();
   const int64_t total = rows_bt * heads * (HD / 2);
   const int C = heads * HD;
   for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
@@ -326,6 +329,7 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_co
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
+  pdl_sync();
   const uint32_t tm_s = tmem_base, tm_dp = tmem_base + 128, tm_dv = tmem_base + 256, tm_dk = tmem_base + 320,
                  tm_dq = tmem_base + 384;
 
@@ -502,9 +506,8 @@ extern "C" int b200_attention_fwd(const void* qkv, void* out, float* lse, int ba
   }
   const float scale_log2 = 1.4426950408889634f / 8.0f;   // log2(e) / sqrt(64)
   dim3 grid(seq / BQ, heads, batch);
-  attention_fwd_kernel<<<grid, ATT_THREADS, AttnFwdSmem::BYTES, static_cast<cudaStream_t>(stream)>>>(
-      tm, static_cast<__nv_bfloat16*>(out), lse, seq, heads, scale_log2);
-  count_launch();
+  B200_CUDA(launch_k(attention_fwd_kernel, dim3(grid), dim3(ATT_THREADS), AttnFwdSmem::BYTES, static_cast<cudaStream_t>(stream), 
+      tm, static_cast<__nv_bfloat16*>(out), lse, seq, heads, scale_log2));
   B200_CUDA(cudaGetLastError());
   return 0;
 }
@@ -536,21 +539,18 @@ extern "C" int b200_attention_bwd(const void* qkv, const void* out, const void* 
   }
   int pblocks = (int)((rows + 7) / 8);
   if (pblocks > num_sms() * 16) pblocks = num_sms() * 16;
-  attention_bwd_prep_kernel<<<pblocks, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(out),
+  B200_CUDA(launch_k(attention_bwd_prep_kernel, dim3(pblocks), dim3(256), 0, s, static_cast<const __nv_bfloat16*>(out),
                                                     static_cast<const __nv_bfloat16*>(dout), delta, dq_accum, batch, seq,
-                                                    heads);
-  count_launch();
+                                                    heads));
   const float scale = 0.125f, scale_log2 = 1.4426950408889634f / 8.0f;
   dim3 grid(seq / BKV, heads, batch);
-  attention_bwd_kernel<<<grid, ATT_THREADS, AttnBwdSmem::BYTES, s>>>(tm_qkv, tm_do, lse, delta, dq_accum,
+  B200_CUDA(launch_k(attention_bwd_kernel, dim3(grid), dim3(ATT_THREADS), AttnBwdSmem::BYTES, s, tm_qkv, tm_do, lse, delta, dq_accum,
                                                                     static_cast<__nv_bfloat16*>(dqkv), seq, heads, scale,
-                                                                    scale_log2);
-  count_launch();
+                                                                    scale_log2));
   int64_t total = (int64_t)batch * seq * C / 2;
   int qblocks = (int)((total + 255) / 256);
   if (qblocks > num_sms() * 16) qblocks = num_sms() * 16;
-  attention_bwd_post_kernel<<<qblocks, 256, 0, s>>>(dq_accum, static_cast<__nv_bfloat16*>(dqkv), (int64_t)batch * seq, heads);
-  count_launch();
+  B200_CUDA(launch_k(attention_bwd_post_kernel, dim3(qblocks), dim3(256), 0, s, dq_accum, static_cast<__nv_bfloat16*>(dqkv), (int64_t)batch * seq, heads));
   B200_CUDA(cudaGetLastError());
   return 0;
 }

@@ -100,6 +100,7 @@ fused_reduce_adamw_kernel(const CommDev c, const b200_seg* __restrict__ segs, in
                           float* __restrict__ m, float* __restrict__ v, const b200_adamw_hparams hp,
                           const int32_t* __restrict__ step_count, const float* __restrict__ step_metrics,
                           float* __restrict__ metrics_acc, int nmetrics) {
+  pdl_sync();
   // metrics: every rank drops its partial sums into every peer's signal buffer before the barrier
   if (blockIdx.x == 0 && step_metrics != nullptr && c.world > 1) {
     for (int i = threadIdx.x; i < c.world * nmetrics; i += blockDim.x) {
@@ -249,6 +250,7 @@ struct PeerPtrs { const uint8_t* p[MAX_WORLD]; };
 __global__ void __launch_bounds__(256)
 peer_gather_kernel(const PeerPtrs peers, int world, const b200_gather_seg* __restrict__ segs, int nseg,
                    uint8_t* __restrict__ dst) {
+  pdl_sync();
   const int64_t nthreads = static_cast<int64_t>(gridDim.x) * blockDim.x;
   const int64_t tid = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   for (int s = 0; s < nseg; ++s) {
@@ -291,11 +293,13 @@ peer_gather_kernel(const PeerPtrs peers, int world, const b200_gather_seg* __res
 }
 
 __global__ void signal_barrier_kernel(const CommDev c) {
+  pdl_sync();
   cross_rank_barrier(c, 0);
   cross_rank_barrier(c, 1);
 }
 
-__global__ void bump_step_kernel2(int32_t* step) { *step += 1; }
+__global__ void bump_step_kernel2(int32_t* step) {
+  pdl_sync(); *step += 1; }
 
 static int fill_ctx(const b200_comm_ctx* ctx, CommDev* d) {
   B200_REQUIRE(ctx->world >= 1 && ctx->world <= MAX_WORLD, "comm: world size %d not in [1,%d]", ctx->world, MAX_WORLD);
@@ -341,13 +345,11 @@ extern "C" int b200_fused_reduce_adamw(const b200_comm_ctx* ctx, const b200_seg*
   if (blocks > B200_COMM_MAX_BLOCKS) blocks = B200_COMM_MAX_BLOCKS;
   if (blocks > num_sms()) blocks = num_sms();   // every block must be resident: they spin on each other across GPUs
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  fused_reduce_adamw_kernel<<<blocks, 256, 0, s>>>(d, segs_dev, nseg, broadcast, p_local,
+  B200_CUDA(launch_k(fused_reduce_adamw_kernel, dim3(blocks), dim3(256), 0, s, d, segs_dev, nseg, broadcast, p_local,
                                                    static_cast<__nv_bfloat16*>(bf16_local), m, v, *hp,
-                                                   step_count, step_metrics, metrics_acc, nmetrics);
-  count_launch();
+                                                   step_count, step_metrics, metrics_acc, nmetrics));
   if (bump_step) {
-    bump_step_kernel2<<<1, 1, 0, s>>>(step_count);
-    count_launch();
+    B200_CUDA(launch_k(bump_step_kernel2, dim3(1), dim3(1), 0, s, step_count));
   }
   B200_CUDA(cudaGetLastError());
   return 0;
@@ -357,8 +359,7 @@ extern "C" int b200_signal_barrier(const b200_comm_ctx* ctx, void* stream) {
   CommDev d;
   int rc = fill_ctx(ctx, &d);
   if (rc) return rc;
-  signal_barrier_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(d);
-  count_launch();
+  B200_CUDA(launch_k(signal_barrier_kernel, dim3(1), dim3(32), 0, static_cast<cudaStream_t>(stream), d));
   B200_CUDA(cudaGetLastError());
   return 0;
 }
@@ -374,9 +375,8 @@ extern "C" int b200_peer_gather(void* const* peer_base, int world, const b200_ga
   }
   if (blocks <= 0) blocks = 4;
   if (blocks * world > 4 * num_sms()) blocks = 4 * num_sms() / world;
-  peer_gather_kernel<<<dim3(blocks, world), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      pp, world, segs_dev, nseg, static_cast<uint8_t*>(dst));
-  count_launch();
+  B200_CUDA(launch_k(peer_gather_kernel, dim3(blocks, world), dim3(256), 0, static_cast<cudaStream_t>(stream), 
+      pp, world, segs_dev, nseg, static_cast<uint8_t*>(dst)));
   B200_CUDA(cudaGetLastError());
   return 0;
 }

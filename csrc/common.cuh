@@ -36,6 +36,13 @@ int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
 // to report "gpu_launches".
 void count_launch(int n = 1);
 
+// Programmatic dependent launch: every kernel of the library is launched with
+// cudaLaunchAttributeProgrammaticStreamSerialization, signals `launch_dependents` at its start and
+// executes `griddepcontrol.wait` before it touches global memory, so the next kernel's CTA
+// scheduling and prologue (barrier init, TMEM allocation, descriptor prefetch) overlap the
+// previous kernel's tail. B200DIST_NO_PDL=1 falls back to ordinary stream ordering.
+bool pdl_enabled();
+
 // Tensor-map creation (cuTensorMapEncodeTiled resolved with cudaGetDriverEntryPoint).
 // 2-D bf16/fp32 tensor, dims/box in elements, inner dimension first.
 int make_tmap_2d(CUtensorMap* out, const void* base, int elem_bytes, uint64_t inner, uint64_t outer,
@@ -47,6 +54,31 @@ int num_sms();
 // Device helpers
 // ---------------------------------------------------------------------------------------
 #ifdef __CUDACC__
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                            Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  const bool pdl = pdl_enabled();
+  cfg.attrs = pdl ? at : nullptr;
+  cfg.numAttrs = pdl ? 1 : 0;
+  count_launch();
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
+// Let the next kernel in the stream start its prologue, then wait until everything this kernel
+// depends on (all earlier kernels in the stream) has completed and is visible.
+__device__ __forceinline__ void pdl_sync() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));

@@ -16,6 +16,7 @@ namespace b200 {
 __global__ void xent_warp_kernel(const float* __restrict__ logits, int ld, const int64_t* __restrict__ labels,
                                  int rows, int classes, float grad_scale, __nv_bfloat16* __restrict__ dlogits,
                                  int ldd, float* __restrict__ metrics, float* __restrict__ row_loss) {
+  pdl_sync();
   const int warps_per_block = blockDim.x >> 5;
   const int lane = threadIdx.x & 31;
   float loss_acc = 0.f, correct_acc = 0.f;
@@ -73,6 +74,7 @@ __global__ void __launch_bounds__(512)
 xent_block_bf16_kernel(__nv_bfloat16* __restrict__ logits, int ld, const int64_t* __restrict__ labels,
                        int rows, int classes, float grad_scale, float* __restrict__ metrics,
                        float* __restrict__ row_loss) {
+  pdl_sync();
   __shared__ float s_m[16], s_s[16];
   __shared__ int s_a[16];
   __shared__ float s_bcast[2];
@@ -171,6 +173,7 @@ xent_block_bf16_kernel(__nv_bfloat16* __restrict__ logits, int ld, const int64_t
 __global__ void __launch_bounds__(256)
 colsum_bf16_vec_kernel(const __nv_bfloat16* __restrict__ x, int ld, int rows, int cols, float* __restrict__ out,
                        int row_chunks, int direct) {
+  pdl_sync();
   __shared__ float s[8][256 + 8];
   const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
   const int col = blockIdx.x * 256 + cx * 8;
@@ -215,6 +218,7 @@ colsum_bf16_vec_kernel(const __nv_bfloat16* __restrict__ x, int ld, int rows, in
 
 __global__ void colsum_bf16_kernel(const __nv_bfloat16* __restrict__ x, int ld, int rows, int cols,
                                    float* __restrict__ out, int accumulate, int row_chunks) {
+  pdl_sync();
   __shared__ float s[8][33];
   const int col = blockIdx.x * 32 + threadIdx.x;
   const int chunk = blockIdx.y;
@@ -253,6 +257,7 @@ __device__ __forceinline__ void adamw_elem(float& p, float& m, float& v, float g
 __global__ void adamw_kernel(float* __restrict__ p, float* __restrict__ m, float* __restrict__ v,
                              float* __restrict__ g, __nv_bfloat16* __restrict__ pb, int64_t n,
                              b200_adamw_hparams hp, const int32_t* __restrict__ step_count, int zero_grad) {
+  pdl_sync();
   const float t = static_cast<float>(*step_count + 1);
   const float c1 = 1.0f / (1.0f - __powf(hp.beta1, t));
   const float c2 = 1.0f / (1.0f - __powf(hp.beta2, t));
@@ -290,9 +295,11 @@ __global__ void adamw_kernel(float* __restrict__ p, float* __restrict__ m, float
   }
 }
 
-__global__ void bump_step_kernel(int32_t* step) { *step += 1; }
+__global__ void bump_step_kernel(int32_t* step) {
+  pdl_sync(); *step += 1; }
 
 __global__ void cast_f32_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int64_t n) {
+  pdl_sync();
   const int64_t n4 = n >> 2;
   const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
   for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n4; i += stride) {
@@ -308,18 +315,21 @@ __global__ void cast_f32_bf16_kernel(const float* __restrict__ src, __nv_bfloat1
 }
 
 __global__ void cast_bf16_f32_kernel(const __nv_bfloat16* __restrict__ src, float* __restrict__ dst, int64_t n) {
+  pdl_sync();
   const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
   for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride)
     dst[i] = __bfloat162float(src[i]);
 }
 
 __global__ void scale_f32_kernel(float* __restrict__ x, int64_t n, float s) {
+  pdl_sync();
   const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
   for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride)
     x[i] = s == 0.f ? 0.f : x[i] * s;
 }
 
 __global__ void rng_split_kernel(uint64_t* key, uint64_t* out_step, uint64_t salt_next, uint64_t salt_step) {
+  pdl_sync();
   uint64_t k = *key;
   if (out_step != nullptr) *out_step = mix64(k ^ salt_step);
   *key = mix64(k ^ salt_next);
@@ -330,6 +340,7 @@ __global__ void act_dropout_kernel(const __nv_bfloat16* __restrict__ x, const __
                                    __nv_bfloat16* __restrict__ out, int64_t rows, int cols, int ld, int act,
                                    const uint64_t* __restrict__ key, uint64_t salt, uint32_t thresh16, float scale,
                                    int bwd) {
+  pdl_sync();
   uint64_t seed = 0;
   if (key != nullptr) seed = mix64(*key ^ salt);
   const int64_t total = rows * cols;
@@ -372,10 +383,9 @@ extern "C" int b200_softmax_xent(const float* logits, int ld_logits, const int64
   int blocks = (rows + 3) / 4;
   int cap = num_sms() * 16;
   if (blocks > cap) blocks = cap;
-  xent_warp_kernel<<<blocks, threads, 0, static_cast<cudaStream_t>(stream)>>>(
+  B200_CUDA(launch_k(xent_warp_kernel, dim3(blocks), dim3(threads), 0, static_cast<cudaStream_t>(stream), 
       logits, ld_logits, labels, rows, classes, grad_scale, static_cast<__nv_bfloat16*>(dlogits),
-      ld_dlogits, metrics, row_loss);
-  count_launch();
+      ld_dlogits, metrics, row_loss));
   B200_CUDA(cudaGetLastError());
   return 0;
 }
@@ -385,9 +395,8 @@ extern "C" int b200_softmax_xent_bf16_inplace(void* logits_bf16, int ld, const i
                                               void* stream) {
   B200_REQUIRE(rows > 0 && classes > 0, "xent: empty input");
   int blocks = rows < num_sms() * 4 ? rows : num_sms() * 4;
-  xent_block_bf16_kernel<<<blocks, 512, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<__nv_bfloat16*>(logits_bf16), ld, labels, rows, classes, grad_scale, metrics, row_loss);
-  count_launch();
+  B200_CUDA(launch_k(xent_block_bf16_kernel, dim3(blocks), dim3(512), 0, static_cast<cudaStream_t>(stream), 
+      static_cast<__nv_bfloat16*>(logits_bf16), ld, labels, rows, classes, grad_scale, metrics, row_loss));
   B200_CUDA(cudaGetLastError());
   return 0;
 }
@@ -403,17 +412,16 @@ extern "C" int b200_colsum_bf16(const void* x, int ld, int rows, int cols, float
     while (col_blocks * row_chunks < num_sms() * 2 && rows / (row_chunks * 2) >= 32) row_chunks *= 2;
     const int direct = (row_chunks == 1 && !accumulate) ? 1 : 0;
     if (!accumulate && !direct) B200_CUDA(cudaMemsetAsync(out, 0, sizeof(float) * cols, s));
-    colsum_bf16_vec_kernel<<<dim3(col_blocks, row_chunks), 256, 0, s>>>(static_cast<const __nv_bfloat16*>(x), ld, rows,
-                                                                      cols, out, row_chunks, direct);
+    B200_CUDA(launch_k(colsum_bf16_vec_kernel, dim3(col_blocks, row_chunks), dim3(256), 0, s, static_cast<const __nv_bfloat16*>(x), ld, rows,
+                                                                      cols, out, row_chunks, direct));
   } else {
     int col_blocks = (cols + 31) / 32;
     int row_chunks = 1;
     while (col_blocks * row_chunks < num_sms() * 2 && rows / (row_chunks * 2) >= 64) row_chunks *= 2;
     if (row_chunks > 1 && !accumulate) B200_CUDA(cudaMemsetAsync(out, 0, sizeof(float) * cols, s));
-    colsum_bf16_kernel<<<dim3(col_blocks, row_chunks), dim3(32, 8), 0, s>>>(
-        static_cast<const __nv_bfloat16*>(x), ld, rows, cols, out, accumulate, row_chunks);
+    B200_CUDA(launch_k(colsum_bf16_kernel, dim3(col_blocks, row_chunks), dim3(32, 8), 0, s, 
+        static_cast<const __nv_bfloat16*>(x), ld, rows, cols, out, accumulate, row_chunks));
   }
-  count_launch();
   B200_CUDA(cudaGetLastError());
   return 0;
 }
@@ -428,13 +436,11 @@ extern "C" int b200_adamw(float* p, float* m, float* v, const float* g, void* p_
   B200_REQUIRE(p_bf16 == nullptr || (reinterpret_cast<uintptr_t>(p_bf16) & 7) == 0,
                "adamw: bf16 copy must be 8-byte aligned");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  adamw_kernel<<<stream_grid(n / 4 + 1, 256), 256, 0, s>>>(p, m, v, const_cast<float*>(g),
+  B200_CUDA(launch_k(adamw_kernel, dim3(stream_grid(n / 4 + 1, 256)), dim3(256), 0, s, p, m, v, const_cast<float*>(g),
                                                           static_cast<__nv_bfloat16*>(p_bf16), n, *hp,
-                                                          step_count, zero_grad);
-  count_launch();
+                                                          step_count, zero_grad));
   if (bump_step) {
-    bump_step_kernel<<<1, 1, 0, s>>>(step_count);
-    count_launch();
+    B200_CUDA(launch_k(bump_step_kernel, dim3(1), dim3(1), 0, s, step_count));
   }
   B200_CUDA(cudaGetLastError());
   return 0;
@@ -444,34 +450,30 @@ extern "C" int b200_cast_f32_bf16(const float* src, void* dst, int64_t n, void* 
   B200_REQUIRE(n > 0, "cast: empty buffer");
   B200_REQUIRE((reinterpret_cast<uintptr_t>(src) & 15) == 0 && (reinterpret_cast<uintptr_t>(dst) & 7) == 0,
                "cast: misaligned buffers");
-  cast_f32_bf16_kernel<<<stream_grid(n / 4 + 1, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      src, static_cast<__nv_bfloat16*>(dst), n);
-  count_launch();
+  B200_CUDA(launch_k(cast_f32_bf16_kernel, dim3(stream_grid(n / 4 + 1, 256)), dim3(256), 0, static_cast<cudaStream_t>(stream), 
+      src, static_cast<__nv_bfloat16*>(dst), n));
   B200_CUDA(cudaGetLastError());
   return 0;
 }
 
 extern "C" int b200_cast_bf16_f32(const void* src, float* dst, int64_t n, void* stream) {
   B200_REQUIRE(n > 0, "cast: empty buffer");
-  cast_bf16_f32_kernel<<<stream_grid(n, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const __nv_bfloat16*>(src), dst, n);
-  count_launch();
+  B200_CUDA(launch_k(cast_bf16_f32_kernel, dim3(stream_grid(n, 256)), dim3(256), 0, static_cast<cudaStream_t>(stream), 
+      static_cast<const __nv_bfloat16*>(src), dst, n));
   B200_CUDA(cudaGetLastError());
   return 0;
 }
 
 extern "C" int b200_scale_f32(float* x, int64_t n, float scale, void* stream) {
   B200_REQUIRE(n > 0, "scale: empty buffer");
-  scale_f32_kernel<<<stream_grid(n, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, n, scale);
-  count_launch();
+  B200_CUDA(launch_k(scale_f32_kernel, dim3(stream_grid(n, 256)), dim3(256), 0, static_cast<cudaStream_t>(stream), x, n, scale));
   B200_CUDA(cudaGetLastError());
   return 0;
 }
 
 extern "C" int b200_rng_split(uint64_t* key, uint64_t* out_step, uint64_t salt_next, uint64_t salt_step,
                               void* stream) {
-  rng_split_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(key, out_step, salt_next, salt_step);
-  count_launch();
+  B200_CUDA(launch_k(rng_split_kernel, dim3(1), dim3(1), 0, static_cast<cudaStream_t>(stream), key, out_step, salt_next, salt_step));
   B200_CUDA(cudaGetLastError());
   return 0;
 }
@@ -481,11 +483,10 @@ static int act_dropout_launch(const void* x, const void* dy, void* out, int64_t 
   B200_REQUIRE(rows > 0 && cols > 0, "act_dropout: empty input");
   float keep = 1.0f - rate;
   const uint64_t* k = rate > 0.f ? key : nullptr;
-  act_dropout_kernel<<<stream_grid(rows * cols, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+  B200_CUDA(launch_k(act_dropout_kernel, dim3(stream_grid(rows * cols, 256)), dim3(256), 0, static_cast<cudaStream_t>(stream), 
       static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(dy),
       static_cast<__nv_bfloat16*>(out), rows, cols, ld, act, k, salt,
-      static_cast<uint32_t>(keep * 65536.0f + 0.5f), keep > 0.f ? 1.0f / keep : 0.f, bwd);
-  count_launch();
+      static_cast<uint32_t>(keep * 65536.0f + 0.5f), keep > 0.f ? 1.0f / keep : 0.f, bwd));
   B200_CUDA(cudaGetLastError());
   return 0;
 }

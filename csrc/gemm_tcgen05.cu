@@ -427,6 +427,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
+  pdl_sync();   // everything above overlapped the previous kernel's tail; global memory is touched below
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -644,6 +645,7 @@ gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
   cluster_sync_all();                  // barriers of both CTAs initialised before any remote arrive
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
+  pdl_sync();
 
   // tile -> coordinates (same order as the single-CTA kernel, M tiles of 256 rows)
   auto coord = [&](int tile) {
@@ -838,8 +840,7 @@ static int launch_gemm(const b200_gemm_args& a, const GemmDev& dev, cudaStream_t
                                       : (a.n + BN - 1) / BN;
   long long tiles = (long long)m_tiles * n_tiles * dev.k_splits;
   int grid = (int)(tiles < num_sms() ? tiles : num_sms());
-  kern<<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(ta, tb, dev);
-  count_launch();
+  B200_CUDA(launch_k(kern, dim3(grid), dim3(GEMM_THREADS), Cfg::SMEM_BYTES, stream, ta, tb, dev));
   B200_CUDA(cudaGetLastError());
   return 0;
 }
@@ -876,8 +877,7 @@ static int launch_gemm_pair(const b200_gemm_args& a, const GemmDev& dev, cudaStr
   int n_tiles = (a.b_shard_mode == 2) ? ((a.b_shard_len + BN - 1) / BN) * dev.nsrc : (a.n + BN - 1) / BN;
   long long tiles = (long long)m_tiles * n_tiles * dev.k_splits;
   int clusters = (int)(tiles < num_sms() / 2 ? tiles : num_sms() / 2);
-  kern<<<clusters * 2, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(ta, tb, dev);
-  count_launch();
+  B200_CUDA(launch_k(kern, dim3(clusters * 2), dim3(GEMM_THREADS), Cfg::SMEM_BYTES, stream, ta, tb, dev));
   B200_CUDA(cudaGetLastError());
   return 0;
 }

@@ -28,6 +28,7 @@ __global__ void __launch_bounds__(128)
 layernorm_fwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ gamma,
                      const __nv_bfloat16* __restrict__ beta, __nv_bfloat16* __restrict__ y,
                      float* __restrict__ mean, float* __restrict__ rstd, int rows, int cols, float eps) {
+  pdl_sync();
   const int lane = threadIdx.x & 31;
   const int wpb = blockDim.x >> 5;
   const int nchunk = cols >> 3;
@@ -85,6 +86,7 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
                      const float* __restrict__ rstd, const __nv_bfloat16* __restrict__ dresid,
                      __nv_bfloat16* __restrict__ dx, float* __restrict__ dgamma,
                      float* __restrict__ dbeta, int rows, int cols) {
+  pdl_sync();
   extern __shared__ float sm[];
   float* s_dg = sm;
   float* s_db = sm + cols;
@@ -177,6 +179,7 @@ __global__ void __launch_bounds__(128)
 embedding_fwd_kernel(const int64_t* __restrict__ tokens, const __nv_bfloat16* __restrict__ wte,
                      const __nv_bfloat16* __restrict__ wpe, __nv_bfloat16* __restrict__ out, int rows, int seq,
                      int dim) {
+  pdl_sync();
   const int lane = threadIdx.x & 31;
   const int wpb = blockDim.x >> 5;
   const int nchunk = dim >> 3;
@@ -203,6 +206,7 @@ __global__ void __launch_bounds__(128)
 embedding_fwd_sharded_kernel(const int64_t* __restrict__ tokens, const TablePeers wte, int64_t wte_rows,
                              const TablePeers wpe, int64_t wpe_rows, __nv_bfloat16* __restrict__ out, int rows,
                              int seq, int dim) {
+  pdl_sync();
   const int lane = threadIdx.x & 31;
   const int wpb = blockDim.x >> 5;
   const int nchunk = dim >> 3;
@@ -227,6 +231,7 @@ embedding_fwd_sharded_kernel(const int64_t* __restrict__ tokens, const TablePeer
 __global__ void __launch_bounds__(128)
 embedding_bwd_kernel(const int64_t* __restrict__ tokens, const __nv_bfloat16* __restrict__ dout,
                      float* __restrict__ dwte, float* __restrict__ dwpe, int rows, int seq, int dim) {
+  pdl_sync();
   const int lane = threadIdx.x & 31;
   const int wpb = blockDim.x >> 5;
   const int nchunk = dim >> 3;
@@ -258,10 +263,9 @@ extern "C" int b200_layernorm_fwd(const void* x, const void* gamma, const void* 
   int blocks = (rows + 3) / 4;
   int cap = num_sms() * 16;
   if (blocks > cap) blocks = cap;
-  layernorm_fwd_kernel<<<blocks, 128, 0, static_cast<cudaStream_t>(stream)>>>(
+  B200_CUDA(launch_k(layernorm_fwd_kernel, dim3(blocks), dim3(128), 0, static_cast<cudaStream_t>(stream), 
       static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(gamma),
-      static_cast<const __nv_bfloat16*>(beta), static_cast<__nv_bfloat16*>(y), mean, rstd, rows, cols, eps);
-  count_launch();
+      static_cast<const __nv_bfloat16*>(beta), static_cast<__nv_bfloat16*>(y), mean, rstd, rows, cols, eps));
   B200_CUDA(cudaGetLastError());
   return 0;
 }
@@ -273,18 +277,20 @@ extern "C" int b200_layernorm_bwd(const void* dy, const void* x, const void* gam
   int blocks = (rows + 7) / 8;
   int cap = num_sms() * 2;
   if (blocks > cap) blocks = cap;
-  auto launch = [&](auto kern) {
-    kern<<<blocks, 256, 2 * cols * sizeof(float), static_cast<cudaStream_t>(stream)>>>(
+  auto launch = [&](auto kern) -> int {
+    B200_CUDA(launch_k(kern, dim3(blocks), dim3(256), 2 * cols * sizeof(float), static_cast<cudaStream_t>(stream), 
         static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(x),
         static_cast<const __nv_bfloat16*>(gamma), mean, rstd, static_cast<const __nv_bfloat16*>(dresid),
-        static_cast<__nv_bfloat16*>(dx), dgamma, dbeta, rows, cols);
+        static_cast<__nv_bfloat16*>(dx), dgamma, dbeta, rows, cols));
+    return 0;
   };
-  if (cols <= 256) launch(layernorm_bwd_kernel<1>);
-  else if (cols <= 512) launch(layernorm_bwd_kernel<2>);
-  else if (cols <= 768) launch(layernorm_bwd_kernel<3>);
-  else if (cols <= 1024) launch(layernorm_bwd_kernel<4>);
-  else launch(layernorm_bwd_kernel<8>);
-  count_launch();
+  int rc;
+  if (cols <= 256) rc = launch(layernorm_bwd_kernel<1>);
+  else if (cols <= 512) rc = launch(layernorm_bwd_kernel<2>);
+  else if (cols <= 768) rc = launch(layernorm_bwd_kernel<3>);
+  else if (cols <= 1024) rc = launch(layernorm_bwd_kernel<4>);
+  else rc = launch(layernorm_bwd_kernel<8>);
+  if (rc) return rc;
   B200_CUDA(cudaGetLastError());
   return 0;
 }
@@ -296,10 +302,9 @@ extern "C" int b200_embedding_fwd(const int64_t* tokens, const void* wte, const 
   int blocks = (rows + 3) / 4;
   int cap = num_sms() * 16;
   if (blocks > cap) blocks = cap;
-  embedding_fwd_kernel<<<blocks, 128, 0, static_cast<cudaStream_t>(stream)>>>(
+  B200_CUDA(launch_k(embedding_fwd_kernel, dim3(blocks), dim3(128), 0, static_cast<cudaStream_t>(stream), 
       tokens, static_cast<const __nv_bfloat16*>(wte), static_cast<const __nv_bfloat16*>(wpe),
-      static_cast<__nv_bfloat16*>(out), rows, seq, dim);
-  count_launch();
+      static_cast<__nv_bfloat16*>(out), rows, seq, dim));
   B200_CUDA(cudaGetLastError());
   return 0;
 }
@@ -311,9 +316,8 @@ extern "C" int b200_embedding_bwd(const int64_t* tokens, const void* dout, float
   int blocks = (rows + 3) / 4;
   int cap = num_sms() * 16;
   if (blocks > cap) blocks = cap;
-  embedding_bwd_kernel<<<blocks, 128, 0, static_cast<cudaStream_t>(stream)>>>(
-      tokens, static_cast<const __nv_bfloat16*>(dout), dwte, dwpe, rows, seq, dim);
-  count_launch();
+  B200_CUDA(launch_k(embedding_bwd_kernel, dim3(blocks), dim3(128), 0, static_cast<cudaStream_t>(stream), 
+      tokens, static_cast<const __nv_bfloat16*>(dout), dwte, dwpe, rows, seq, dim));
   B200_CUDA(cudaGetLastError());
   return 0;
 }
@@ -333,9 +337,8 @@ extern "C" int b200_embedding_fwd_sharded(const int64_t* tokens, void* const* wt
   int blocks = (rows + 3) / 4;
   int cap = num_sms() * 16;
   if (blocks > cap) blocks = cap;
-  embedding_fwd_sharded_kernel<<<blocks, 128, 0, static_cast<cudaStream_t>(stream)>>>(
-      tokens, a, wte_rows_per_shard, b, wpe_rows_per_shard, static_cast<__nv_bfloat16*>(out), rows, seq, dim);
-  count_launch();
+  B200_CUDA(launch_k(embedding_fwd_sharded_kernel, dim3(blocks), dim3(128), 0, static_cast<cudaStream_t>(stream), 
+      tokens, a, wte_rows_per_shard, b, wpe_rows_per_shard, static_cast<__nv_bfloat16*>(out), rows, seq, dim));
   B200_CUDA(cudaGetLastError());
   return 0;
 }
