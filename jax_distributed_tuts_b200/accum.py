@@ -5,10 +5,12 @@ slices, per-minibatch RNG from ``split(key, n)``, gradients *averaged* (``/ n_mi
 util.py:77) and metrics *summed* (util.py:75).
 
 ``accum_grads_scan`` is the reference's ``lax.scan`` variant (one compiled body instead of n
-unrolled copies, util.py:81-137). There is no tracing compiler here; its B200 counterpart is
-one CUDA-graph-captured minibatch body replayed n times over a sliding window of the static
-batch buffer, accumulating into zero-initialised carries exactly like the scan carry
-(util.py:123-133). On CPU (or when capture is unavailable) it runs the same body eagerly.
+unrolled copies, util.py:81-137): zero-initialised carries with the shapes of one minibatch
+step (util.py:123-129) and the same body applied to ``narrow``-ed windows of the batch
+(the ``dynamic_slice_in_dim`` of util.py:97-105). There is no tracing compiler here, so in the
+generic tier the body simply runs n times; the compiled-once counterpart lives in the fused
+engines, whose whole step is one captured CUDA graph (and which can fold the minibatch loop
+into the GEMMs themselves, ``engine.MLPEngine(fuse_minibatches=True)``).
 """
 from __future__ import annotations
 

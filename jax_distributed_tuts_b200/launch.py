@@ -88,3 +88,27 @@ def sim_multiCPU_dev(fn: Callable[..., Any], device_count: int = 8, args: tuple 
         if errs or any(p.exitcode != 0 for p in procs):
             raise RuntimeError("sim_multiCPU_dev worker failed:\n" + "\n".join(errs))
         return [torch.load(os.path.join(d, f"rank{r}.pt"), weights_only=False) for r in range(device_count)]
+
+
+def _run_script(rank: int, world: int, script: str, argv: list) -> None:
+    import runpy
+    import sys
+    sys.argv = [script] + list(argv)
+    runpy.run_path(script, run_name="__main__")
+
+
+def main(argv=None) -> None:
+    """``python -m jax_distributed_tuts_b200.launch --cpu N script.py [args]``: runs a script on N CPU
+    processes joined by gloo (RANK / WORLD_SIZE / MASTER_* set like torchrun does), the analogue of
+    the reference's ``sim_multiCPU_dev()`` call at the top of every script. For GPUs use torchrun."""
+    import argparse
+    ap = argparse.ArgumentParser(prog="jax_distributed_tuts_b200.launch")
+    ap.add_argument("--cpu", type=int, default=8, help="number of simulated devices (CPU processes)")
+    ap.add_argument("script")
+    ap.add_argument("args", nargs=argparse.REMAINDER)
+    a = ap.parse_args(argv)
+    sim_multiCPU_dev(_run_script, device_count=a.cpu, args=(os.path.abspath(a.script), a.args))
+
+
+if __name__ == "__main__":
+    main()

@@ -161,3 +161,30 @@ def fsdp_ckpt_worker(rank, world, path):
         same = torch.equal(k0.value, k1.value) and k1.names == k0.names
         same &= torch.equal(state.params["output_dense"]["bias"], restored["output_dense"]["bias"])
     return {"reload_equal": bool(same), "local_shape": tuple(k1.value.shape)}
+
+
+def fsdp2d_worker(rank, world, steps, lr):
+    """2-D mesh (data=2, fsdp=world/2): parameters sharded over `fsdp`, gradients additionally
+    averaged over `data` by sync_gradients (param_sharding.py:293-322)."""
+    cfg = fsdp_config()
+    cfg.model.dropout_rate = 0.0
+    mesh = Mesh((2, world // 2), ("data", "fsdp"))
+    wrap = lambda m: fsdp.shard_module_params(m, axis_name="fsdp", min_weight_size=16)
+    model = Classifier(cfg.model, dense_wrapper=wrap)
+    model_rng, batch = make_batch(cfg)
+    with mesh:
+        state = fsdp.init_model(model_rng, batch.inputs, model, learning_rate=lr)
+        # every rank of the (data, fsdp) grid takes a distinct slice of the batch
+        n, i = mesh.size, mesh.axis_index(("data", "fsdp"))
+        per = batch.inputs.shape[0] // n
+        local = batch.slice(i * per, (i + 1) * per)
+        loss_fn = dp.make_loss_fn("fsdp")
+        step = fsdp.make_train_step_fsdp(mesh, num_minibatches=cfg.num_minibatches, data_axis_name="fsdp",
+                                         loss_fn=loss_fn, sync_axes=("data", "fsdp"))
+        metrics = None
+        for _ in range(steps):
+            state, metrics = step(state, metrics, local)
+        full = fsdp.unshard_params(state.params)
+        names = {k: {kk: (vv.names if is_partitioned(vv) else None) for kk, vv in v.items()}
+                 for k, v in state.params.items()}
+    return {"params": full, "metrics": metrics, "names": names, "coords": mesh.coords}

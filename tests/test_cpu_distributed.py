@@ -92,3 +92,18 @@ def test_fsdp_default_min_weight_size_only_shards_big_kernel():
     names = res[0]["names"]
     assert names["input_dense"]["kernel"] == ("data", None)
     assert names["input_dense"]["bias"] is None and names["output_dense"]["kernel"] is None
+
+
+def test_fsdp_on_2d_mesh_matches_dp():
+    """BASELINE.json config 5 (2-D mesh data x param sharding), generic tier on the CPU fake cluster."""
+    world, steps, lr = 8, 2, 1e-3
+    res = sim_multiCPU_dev(W.fsdp2d_worker, world, args=(steps, lr))
+    r0 = res[0]
+    assert r0["names"]["input_dense"]["kernel"] == ("fsdp", None)      # 784 / 4 = 196 rows per shard
+    dp_res = sim_multiCPU_dev(W.dp_lr_worker, world, args=(steps, lr))[0]
+    for a, b in zip(tree_leaves(r0["params"]), tree_leaves(dp_res["params"])):
+        assert _close(a, b), (a - b).abs().mean()
+    for r in res[1:]:       # all 8 ranks reassemble the same parameters
+        for a, b in zip(tree_leaves(r0["params"]), tree_leaves(r["params"])):
+            assert torch.equal(a, b)
+    assert r0["metrics"]["loss"][1] == 128 * steps

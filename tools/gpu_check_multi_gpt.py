@@ -90,6 +90,36 @@ def main():
                 traceback.print_exc()
                 log(f"[FAIL] gpt2-tiny {name}: {type(e).__name__}: {e}")
                 ok_all = False
+        # ---- 2-D mesh (data x fsdp): shards over `fsdp`, gradient mean over both axes ----
+        if world >= 4:
+            try:
+                mesh2 = Mesh((2, world // 2), ("data", "fsdp"))
+                with mesh2:
+                    eng = GPT2Engine(cfg, mesh2, mode="fsdp", shard_axis="fsdp", batch_per_rank=per, seq_len=T, lr=lr,
+                                     num_minibatches=1, init_params=params, use_graph=True, min_weight_size=2 ** 12,
+                                     comm_blocks=32, fsdp_weights="fused")
+                    s2 = eng.make_state(model, rng.PRNGKey(5))
+                    losses = []
+                    for _ in range(steps):
+                        s2, m2 = eng.train_step(s2, None, local)
+                        losses.append(float(m2["loss"][0]) / m2["loss"][1])
+                    torch.cuda.synchronize()
+                    good = all(abs(a - b) < 3e-2 for a, b in zip(gen_losses, losses))
+                    got = dict(tree_leaves_with_path(eng.params_tree()))
+                    for k, a in ref.items():
+                        b = got[k]
+                        b = b[: a.shape[0]] if b.shape != a.shape else b
+                        d = (a.float() - b.float()).abs()
+                        if d.mean().item() > (0.6 if k.endswith("bias") else 0.08) * lr * steps:
+                            good = False
+                    log(f"[{'ok' if good else 'FAIL'}] gpt2-tiny 2-D mesh data=2 x fsdp={world // 2}: losses "
+                        f"{[f'{x:.4f}' for x in losses]} shard group {eng.shard_peer_ranks}")
+                    ok_all &= good
+                    del eng
+            except Exception as e:  # noqa: BLE001
+                traceback.print_exc()
+                log(f"[FAIL] 2-D mesh: {type(e).__name__}: {e}")
+                ok_all = False
         # ---- GPT-2 small timing ----
         scfg = gpt2_config("small")
         smodel = GPT2(scfg)
