@@ -38,6 +38,8 @@ CONFIGS = {
     "gpt2m_2d": dict(model="gpt2_medium_355M", gpt="medium", per_gpu_batch=8, minibatches=1, seq=1024, mode="fsdp",
                      mesh2d=True),
     "gpt2_tiny": dict(model="gpt2_tiny", gpt="tiny", per_gpu_batch=4, minibatches=1, seq=128, mode="dp"),
+    # 4-stage GPipe over NCCL p2p (BASELINE.json config 4): per_gpu_batch is per *pipeline* (data replica)
+    "gpt2s_pp4": dict(model="gpt2_small_124M", gpt="small", per_gpu_batch=8, minibatches=4, seq=1024, mode="pp", stages=4),
 }
 
 
@@ -205,7 +207,11 @@ def main() -> None:
     cfg = dp_config()
     B = c["per_gpu_batch"]
     is_gpt = "gpt" in c
-    if c.get("mesh2d") and world >= 4:
+    if c["mode"] == "pp":
+        assert world % c["stages"] == 0, f"{args.config} needs a multiple of {c['stages']} GPUs"
+        mesh = Mesh((world // c["stages"], c["stages"]), ("data", "pipe"))
+        shard_axis = "data"
+    elif c.get("mesh2d") and world >= 4:
         mesh = Mesh((2, world // 2), ("data", "fsdp"))
         shard_axis = "fsdp"
     else:
@@ -215,7 +221,7 @@ def main() -> None:
     model_rng, data_rng, label_rng = rng.split(key, 3)
     # synthetic data of the named shape; a distinct shard per rank, fixed across steps like the
     # reference's single synthetic batch (data_paral.py:113-124)
-    gx = rng.uniform_generator(rng.fold_in(data_rng, rank))
+    gx = rng.uniform_generator(rng.fold_in(data_rng, rank if c["mode"] != "pp" else mesh.axis_index("data")))
     if is_gpt:
         from jax_distributed_tuts_b200.engine import GPT2Engine
         from jax_distributed_tuts_b200.models.gpt2 import GPT2, gpt2_config
@@ -259,6 +265,31 @@ def main() -> None:
                 return last["loss"].item()
 
             backend, launches_per_step = "nccl" if world > 1 else "local", 0
+        elif c["mode"] == "pp":
+            from jax_distributed_tuts_b200.parallel import pp
+            from jax_distributed_tuts_b200.tree import tree_map
+            stage = pp.GPT2Stage(model, mesh.axis_index("pipe"), c["stages"])
+            st0 = pp.init_pp(model_rng, x[:1], stage, learning_rate=3e-4)
+            st0 = st0.replace(params=tree_map(lambda t: t.to(device), st0.params), rng=st0.rng.to(device))
+            st0 = st0.replace(opt_state=st0.tx.init(st0.params))
+            pp_step = pp.make_train_step_pp(mesh, stage_model=stage, num_microbatches=c["minibatches"], pipe_axis="pipe",
+                                            data_axis="data" if mesh.axis_size("data") > 1 else None)
+            xd, yd = torch.empty_like(x, device=device), torch.empty_like(y, device=device)
+            holder = {"state": st0, "metrics": None}
+
+            def load_batch():
+                xd.copy_(x, non_blocking=True)
+                yd.copy_(y, non_blocking=True)
+
+            def run_step():
+                holder["state"], holder["metrics"] = pp_step(holder["state"], None, Batch(xd, yd))
+
+            def api_step():
+                load_batch()
+                run_step()
+                return holder["metrics"]["loss"][0].item() / holder["metrics"]["loss"][1]
+
+            backend, launches_per_step = "nccl-p2p", 0
         else:
             if is_gpt:
                 params = model.init({"params": model_rng}, x[:1])["params"]      # random init of the named architecture
@@ -330,7 +361,7 @@ def main() -> None:
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dev_ms, e2e_max = t[0].item(), t[1].item()
-        if args.impl == "baseline":
+        if args.impl == "baseline" or c["mode"] == "pp":
             final_loss = loss_val
         else:
             rows = eng._rows_per_step()
@@ -338,7 +369,7 @@ def main() -> None:
             backend, launches_per_step = eng.arena.backend, int(getattr(eng, "launches_per_step", 0))
 
     if rank == 0:
-        gb = B * world
+        gb = B * world if c["mode"] != "pp" else B * (world // c["stages"])
         ms_per_step = dev_ms / args.steps
         out = {
             "metric": "train samples/sec (device-timed, max over ranks)",
@@ -350,7 +381,8 @@ def main() -> None:
             "dtype": "bf16", "data": "synthetic (random-normal inputs, uniform labels, random-init weights)",
             "impl": args.impl,
             "config": {"model": c["model"], "global_batch": gb, "per_gpu_batch": B, "minibatches": c["minibatches"],
-                       "seq_len": c.get("seq"), "parallelism": ("dp2xfsdp%d" % (world // 2)) if (c.get("mesh2d") and world >= 4) else f"{c['mode']}{world}",
+                       "seq_len": c.get("seq"), "parallelism": ("dp2xfsdp%d" % (world // 2)) if (c.get("mesh2d") and world >= 4) else
+                                      (f"dp{world // c['stages']}xpp{c['stages']}" if c["mode"] == "pp" else f"{c['mode']}{world}"),
                        "optimizer": "adamw",
                        "name": args.config, "l2": "flushed between timed steps (256 MiB write)",
                        "cuda_graph": (not args.no_graph) and args.impl == "ours", "comm": backend},
