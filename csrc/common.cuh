@@ -328,25 +328,30 @@ __host__ __device__ constexpr uint32_t umma_idesc_bf16(int m, int n, int a_mn, i
 }
 
 // ---- small math ----
-__device__ __forceinline__ float silu_f(float x) { return __fdividef(x, 1.0f + __expf(-x)); }
+// One MUFU op per activation: tanh.approx.f32 (relative error ~2^-11, far below bf16 resolution).
+__device__ __forceinline__ float tanh_fast(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float sigmoid_fast(float x) { return fmaf(0.5f, tanh_fast(0.5f * x), 0.5f); }
+__device__ __forceinline__ float silu_f(float x) { return x * sigmoid_fast(x); }
 __device__ __forceinline__ float silu_grad_f(float x) {
-  float s = __fdividef(1.0f, 1.0f + __expf(-x));
-  return s * (1.0f + x * (1.0f - s));
+  const float s = sigmoid_fast(x);
+  return s * fmaf(x, 1.0f - s, 1.0f);
 }
 // GPT-2 "gelu_new" (tanh approximation)
 __device__ __forceinline__ float gelu_f(float x) {
   const float k0 = 0.7978845608028654f, k1 = 0.044715f;
-  float u = k0 * (x + k1 * x * x * x);
-  float t = 1.0f - __fdividef(2.0f, 1.0f + __expf(2.0f * u));  // tanh(u)
+  const float t = tanh_fast(k0 * fmaf(k1 * x * x, x, x));
   return 0.5f * x * (1.0f + t);
 }
 __device__ __forceinline__ float gelu_grad_f(float x) {
   const float k0 = 0.7978845608028654f, k1 = 0.044715f;
-  float x2 = x * x;
-  float u = k0 * (x + k1 * x * x2);
-  float t = 1.0f - __fdividef(2.0f, 1.0f + __expf(2.0f * u));
-  float du = k0 * (1.0f + 3.0f * k1 * x2);
-  return 0.5f * (1.0f + t) + 0.5f * x * (1.0f - t * t) * du;
+  const float x2 = x * x;
+  const float t = tanh_fast(k0 * fmaf(k1 * x2, x, x));
+  const float du = k0 * fmaf(3.0f * k1, x2, 1.0f);
+  return fmaf(0.5f * x * (1.0f - t * t), du, 0.5f * (1.0f + t));
 }
 
 // ---- counter-based dropout RNG ----
