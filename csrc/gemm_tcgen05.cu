@@ -108,6 +108,24 @@ __device__ __forceinline__ void epilogue_tile_fast(const GemmDev& p, int row_bas
   if (row_base >= p.M || col_base >= n_limit) return;   // warp-uniform
   const int rows_left = p.M - row_base;
   const float alpha = p.alpha;
+  // kinds that read global memory in the epilogue keep the loads of the *next* 32-column chunk in
+  // flight while the current chunk is processed (and issue them as a batch: the output stores
+  // could alias them as far as the compiler knows, so it would not hoist them itself)
+  constexpr bool LOADS8 = KIND == EPI_BWD_GELU || KIND == EPI_BIAS_RESID;
+  const __nv_bfloat16* lsrc = KIND == EPI_BWD_GELU ? p.aux : p.resid;
+  const int lds = KIND == EPI_BWD_GELU ? p.ldaux : p.ldres;
+  uint2 nxt8[LOADS8 ? 8 : 1];
+  auto issue_loads = [&](int cc) {
+    if (!LOADS8) return;
+    const int colx = col_base + cc * 32 + lchunk * 4;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      nxt8[LOADS8 ? i : 0] = make_uint2(0u, 0u);
+      if (i * 4 + lrow < rows_left && colx < n_limit)
+        nxt8[LOADS8 ? i : 0] = *reinterpret_cast<const uint2*>(lsrc + static_cast<size_t>(row_base + lrow + i * 4) * lds + colx);
+    }
+  };
+  issue_loads(0);
   uint32_t r[32];
   tmem_ld_32x32b_x32(taddr, r);
 #pragma unroll 1
@@ -132,19 +150,12 @@ __device__ __forceinline__ void epilogue_tile_fast(const GemmDev& p, int row_bas
       b2 = bf16_bits_to_f(bw.y & 0xFFFF); b3 = bf16_bits_to_f(bw.y >> 16);
     }
     const size_t row0 = static_cast<size_t>(row_base + lrow);
-    // kinds that read global memory in the epilogue: issue all eight loads of this chunk first (the
-    // output stores below could alias them as far as the compiler knows, so it would not)
-    constexpr bool LOADS8 = KIND == EPI_BWD_GELU || KIND == EPI_BIAS_RESID;
     uint2 ld8[LOADS8 ? 8 : 1];
     float4 acc8[KIND == EPI_PLAIN_F32 ? 8 : 1];
     if (LOADS8) {
-      const __nv_bfloat16* src = KIND == EPI_BWD_GELU ? p.aux : p.resid;
-      const int lds = KIND == EPI_BWD_GELU ? p.ldaux : p.ldres;
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        ld8[i] = make_uint2(0u, 0u);
-        if (i * 4 + lrow < rows_left && col_ok) ld8[i] = *reinterpret_cast<const uint2*>(src + (row0 + i * 4) * lds + col);
-      }
+      for (int i = 0; i < 8; ++i) ld8[i] = nxt8[i];
+      if (c + 1 < CHUNKS && col0 + 32 < n_limit) issue_loads(c + 1);
     }
     if (KIND == EPI_PLAIN_F32 && p.accumulate && !p.atomic_out) {
 #pragma unroll
