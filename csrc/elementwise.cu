@@ -15,7 +15,8 @@ namespace b200 {
 // ------------------------------------------------------------------------------------------
 __global__ void xent_warp_kernel(const float* __restrict__ logits, int ld, const int64_t* __restrict__ labels,
                                  int rows, int classes, float grad_scale, __nv_bfloat16* __restrict__ dlogits,
-                                 int ldd, float* __restrict__ metrics, float* __restrict__ row_loss) {
+                                 int ldd, float* __restrict__ metrics, float* __restrict__ row_loss,
+                                 float* __restrict__ dbias) {
   pdl_sync();
   const int warps_per_block = blockDim.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -46,7 +47,9 @@ __global__ void xent_warp_kernel(const float* __restrict__ logits, int ld, const
       __nv_bfloat16* d = dlogits + static_cast<size_t>(row) * ldd;
       for (int c = lane; c < classes; c += 32) {
         float pch = __expf(x[c] - mx) * inv;
-        d[c] = __float2bfloat16_rn((pch - (c == label ? 1.0f : 0.0f)) * grad_scale);
+        const __nv_bfloat16 gv = __float2bfloat16_rn((pch - (c == label ? 1.0f : 0.0f)) * grad_scale);
+        d[c] = gv;
+        if (dbias != nullptr) atomicAdd(&dbias[c], __bfloat162float(gv));   // few classes on this path: the head's bias gradient
       }
     }
     if (lane == 0) {
@@ -375,9 +378,20 @@ static inline int stream_grid(int64_t work_items, int threads) {
 
 using namespace b200;
 
+extern "C" int b200_softmax_xent_dbias(const float* logits, int ld_logits, const int64_t* labels, int rows,
+                                       int classes, float grad_scale, void* dlogits, int ld_dlogits,
+                                       float* metrics, float* row_loss, float* dbias, void* stream);
+
 extern "C" int b200_softmax_xent(const float* logits, int ld_logits, const int64_t* labels, int rows,
                                  int classes, float grad_scale, void* dlogits, int ld_dlogits,
                                  float* metrics, float* row_loss, void* stream) {
+  return b200_softmax_xent_dbias(logits, ld_logits, labels, rows, classes, grad_scale, dlogits, ld_dlogits, metrics,
+                                 row_loss, nullptr, stream);
+}
+
+extern "C" int b200_softmax_xent_dbias(const float* logits, int ld_logits, const int64_t* labels, int rows,
+                                       int classes, float grad_scale, void* dlogits, int ld_dlogits,
+                                       float* metrics, float* row_loss, float* dbias, void* stream) {
   B200_REQUIRE(rows > 0 && classes > 0, "xent: empty input");
   const int threads = 128;
   int blocks = (rows + 3) / 4;
@@ -385,7 +399,7 @@ extern "C" int b200_softmax_xent(const float* logits, int ld_logits, const int64
   if (blocks > cap) blocks = cap;
   B200_CUDA(launch_k(xent_warp_kernel, dim3(blocks), dim3(threads), 0, static_cast<cudaStream_t>(stream), 
       logits, ld_logits, labels, rows, classes, grad_scale, static_cast<__nv_bfloat16*>(dlogits),
-      ld_dlogits, metrics, row_loss));
+      ld_dlogits, metrics, row_loss, dbias));
   B200_CUDA(cudaGetLastError());
   return 0;
 }

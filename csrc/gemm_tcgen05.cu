@@ -50,6 +50,7 @@ struct GemmDev {
   int vec_d, vec_pre, vec_aux, vec_res;  // 16-byte vector access allowed
   int epi_kind;                          // EPI_*: compile-time specialised epilogue, or EPI_GENERIC
   int k_splits, atomic_out;              // split-K: tile index also selects a K range; partials are red.add-ed
+  float* dbias;                          // column sums of the stored output, added atomically (or null)
 };
 
 // Specialised epilogues (fully vectorised, no run-time feature tests in the inner loop). Anything
@@ -150,6 +151,7 @@ __device__ __forceinline__ void epilogue_tile_fast(const GemmDev& p, int row_bas
       b2 = bf16_bits_to_f(bw.y & 0xFFFF); b3 = bf16_bits_to_f(bw.y >> 16);
     }
     const size_t row0 = static_cast<size_t>(row_base + lrow);
+    float cs0 = 0.f, cs1 = 0.f, cs2 = 0.f, cs3 = 0.f;   // column sums of what this lane stores (dbias)
     uint2 ld8[LOADS8 ? 8 : 1];
     float4 acc8[KIND == EPI_PLAIN_F32 ? 8 : 1];
     if (LOADS8) {
@@ -206,8 +208,19 @@ __device__ __forceinline__ void epilogue_tile_fast(const GemmDev& p, int row_bas
           __nv_bfloat162 t0 = __floats2bfloat162_rn(v0, v1), t1 = __floats2bfloat162_rn(v2, v3);
           *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.d) + row * p.ldd + col) =
               make_uint2(*reinterpret_cast<uint32_t*>(&t0), *reinterpret_cast<uint32_t*>(&t1));
+          cs0 += __bfloat162float(t0.x); cs1 += __bfloat162float(t0.y);
+          cs2 += __bfloat162float(t1.x); cs3 += __bfloat162float(t1.y);
         }
       }
+    }
+    if (KIND != EPI_PLAIN_F32 && p.dbias != nullptr) {   // warp-uniform
+      // lanes l, l^8, l^16, l^24 hold the same four columns for different rows
+      cs0 += __shfl_xor_sync(0xffffffffu, cs0, 8);  cs1 += __shfl_xor_sync(0xffffffffu, cs1, 8);
+      cs2 += __shfl_xor_sync(0xffffffffu, cs2, 8);  cs3 += __shfl_xor_sync(0xffffffffu, cs3, 8);
+      cs0 += __shfl_xor_sync(0xffffffffu, cs0, 16); cs1 += __shfl_xor_sync(0xffffffffu, cs1, 16);
+      cs2 += __shfl_xor_sync(0xffffffffu, cs2, 16); cs3 += __shfl_xor_sync(0xffffffffu, cs3, 16);
+      if (lrow == 0 && col_ok)
+        asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p.dbias + col), "f"(cs0), "f"(cs1), "f"(cs2), "f"(cs3) : "memory");
     }
     __syncwarp();
   }
@@ -250,6 +263,7 @@ __device__ __forceinline__ void epilogue_tile(const GemmDev& p, int row_base, in
     const bool full4 = col + 4 <= n_limit;
     const bool col_ok = col < n_limit;
     float bias4[4] = {0.f, 0.f, 0.f, 0.f};
+    float cs[4] = {0.f, 0.f, 0.f, 0.f};   // column sums of what this lane stores (dbias)
     if (!p.bwd && p.bias != nullptr && col_ok) {
 #pragma unroll
       for (int j = 0; j < 4; ++j)
@@ -361,6 +375,18 @@ __device__ __forceinline__ void epilogue_tile(const GemmDev& p, int row_base, in
       }
     }
     __syncwarp();   // staging is reused by the next chunk
+    if (p.dbias != nullptr && !p.d_fp32) {   // warp-uniform
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        cs[j] += __shfl_xor_sync(0xffffffffu, cs[j], 8);
+        cs[j] += __shfl_xor_sync(0xffffffffu, cs[j], 16);
+      }
+      if (lrow == 0) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          if (col + j < n_limit) atomicAdd(p.dbias + col + j, cs[j]);
+      }
+    }
   }
   if (warp_active) tmem_ld_wait();
 }
@@ -1021,6 +1047,9 @@ extern "C" int b200_gemm_bf16(const b200_gemm_args* args, void* stream) {
   // call does not accumulate.
   dev.k_splits = 1;
   dev.atomic_out = 0;
+  dev.dbias = a.dbias;
+  B200_REQUIRE(a.dbias == nullptr || (!a.d_fp32 && (reinterpret_cast<uintptr_t>(a.dbias) & 15) == 0),
+               "gemm: dbias needs a bf16 output and a 16-byte aligned fp32 vector");
   if (dev.epi_kind == EPI_PLAIN_F32 && a.b_shard_mode != 1 && a.split_k != 1) {
     const long long row_tile = use_pair ? 2 * BM : BM;
     const long long mn = ((a.m + row_tile - 1) / row_tile) * (((a.b_shard_mode == 2 ? a.b_shard_len : a.n) + bn - 1) / bn) *

@@ -85,21 +85,22 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
                      const __nv_bfloat16* __restrict__ gamma, const float* __restrict__ mean,
                      const float* __restrict__ rstd, const __nv_bfloat16* __restrict__ dresid,
                      __nv_bfloat16* __restrict__ dx, float* __restrict__ dgamma,
-                     float* __restrict__ dbeta, int rows, int cols) {
+                     float* __restrict__ dbeta, float* __restrict__ dxsum, int rows, int cols) {
   pdl_sync();
   extern __shared__ float sm[];
   float* s_dg = sm;
   float* s_db = sm + cols;
-  for (int i = threadIdx.x; i < 2 * cols; i += blockDim.x) sm[i] = 0.f;
+  float* s_dx = sm + 2 * cols;
+  for (int i = threadIdx.x; i < 3 * cols; i += blockDim.x) sm[i] = 0.f;
   __syncthreads();
   const int lane = threadIdx.x & 31;
   const int wpb = blockDim.x >> 5;
   const int nchunk = cols >> 3;
-  float acc_g[NCH][8], acc_b[NCH][8];
+  float acc_g[NCH][8], acc_b[NCH][8], acc_x[NCH][8];   // acc_x: column sums of the emitted dx (optional)
 #pragma unroll
   for (int c = 0; c < NCH; ++c) {
 #pragma unroll
-    for (int j = 0; j < 8; ++j) { acc_g[c][j] = 0.f; acc_b[c][j] = 0.f; }
+    for (int j = 0; j < 8; ++j) { acc_g[c][j] = 0.f; acc_b[c][j] = 0.f; acc_x[c][j] = 0.f; }
   }
   for (int row = blockIdx.x * wpb + (threadIdx.x >> 5); row < rows; row += gridDim.x * wpb) {
     const uint4* xr = reinterpret_cast<const uint4*>(x + static_cast<size_t>(row) * cols);
@@ -153,7 +154,14 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
 #pragma unroll
           for (int j = 0; j < 8; ++j) o[j] += rr[j];
         }
-        or_[idx] = pack8(o);
+        const uint4 ow = pack8(o);
+        or_[idx] = ow;
+        if (dxsum != nullptr) {
+          float q[8];
+          unpack8(ow, q);      // sum what was stored (bf16), like a column sum over dx would
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc_x[c][j] += q[j];
+        }
       }
     }
   }
@@ -165,6 +173,7 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
       for (int j = 0; j < 8; ++j) {
         atomicAdd(&s_dg[idx * 8 + j], acc_g[c][j]);
         atomicAdd(&s_db[idx * 8 + j], acc_b[c][j]);
+        if (dxsum != nullptr) atomicAdd(&s_dx[idx * 8 + j], acc_x[c][j]);
       }
     }
   }
@@ -172,6 +181,7 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
   for (int i = threadIdx.x; i < cols; i += blockDim.x) {
     atomicAdd(&dgamma[i], s_dg[i]);
     atomicAdd(&dbeta[i], s_db[i]);
+    if (dxsum != nullptr) atomicAdd(&dxsum[i], s_dx[i]);
   }
 }
 
@@ -270,18 +280,28 @@ extern "C" int b200_layernorm_fwd(const void* x, const void* gamma, const void* 
   return 0;
 }
 
+extern "C" int b200_layernorm_bwd_dxsum(const void* dy, const void* x, const void* gamma, const float* mean,
+                                        const float* rstd, const void* dresid, void* dx, float* dgamma, float* dbeta,
+                                        float* dxsum, int rows, int cols, void* stream);
+
 extern "C" int b200_layernorm_bwd(const void* dy, const void* x, const void* gamma, const float* mean,
                                   const float* rstd, const void* dresid, void* dx, float* dgamma, float* dbeta,
                                   int rows, int cols, void* stream) {
+  return b200_layernorm_bwd_dxsum(dy, x, gamma, mean, rstd, dresid, dx, dgamma, dbeta, nullptr, rows, cols, stream);
+}
+
+extern "C" int b200_layernorm_bwd_dxsum(const void* dy, const void* x, const void* gamma, const float* mean,
+                                        const float* rstd, const void* dresid, void* dx, float* dgamma, float* dbeta,
+                                        float* dxsum, int rows, int cols, void* stream) {
   B200_REQUIRE(rows > 0 && cols > 0 && cols % 8 == 0 && cols <= 2048, "layernorm: cols=%d must be a multiple of 8, <= 2048", cols);
   int blocks = (rows + 7) / 8;
   int cap = num_sms() * 2;
   if (blocks > cap) blocks = cap;
   auto launch = [&](auto kern) -> int {
-    B200_CUDA(launch_k(kern, dim3(blocks), dim3(256), 2 * cols * sizeof(float), static_cast<cudaStream_t>(stream), 
+    B200_CUDA(launch_k(kern, dim3(blocks), dim3(256), 3 * cols * sizeof(float), static_cast<cudaStream_t>(stream), 
         static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(x),
         static_cast<const __nv_bfloat16*>(gamma), mean, rstd, static_cast<const __nv_bfloat16*>(dresid),
-        static_cast<__nv_bfloat16*>(dx), dgamma, dbeta, rows, cols));
+        static_cast<__nv_bfloat16*>(dx), dgamma, dbeta, dxsum, rows, cols));
     return 0;
   };
   int rc;

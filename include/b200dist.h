@@ -16,7 +16,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 11
+#define B200_ABI_VERSION 12
 
 const char* b200_last_error(void);
 int b200_abi_version(void);
@@ -90,6 +90,10 @@ typedef struct b200_gemm_args {
   /* split-K for fp32 outputs: 0 = choose (when the M x N tile grid cannot fill the chip),
    * 1 = never, n > 1 = that many K ranges. Partials are summed with red.global.add. */
   int32_t split_k;
+  /* Column sums of the stored output, added atomically: dbias[n] += sum_m D[m][n] (fp32 [N], 16-byte
+   * aligned, caller zeroes it). Lets a dgrad GEMM emit the bias gradient of the layer it feeds
+   * without a separate pass over D. NULL = off. */
+  float* dbias;
 } b200_gemm_args;
 
 int b200_gemm_bf16(const b200_gemm_args* args, void* stream);
@@ -105,6 +109,10 @@ int b200_gemm_bf16(const b200_gemm_args* args, void* stream);
 int b200_softmax_xent(const float* logits, int ld_logits, const int64_t* labels, int rows,
                       int classes, float grad_scale, void* dlogits, int ld_dlogits,
                       float* metrics, float* row_loss, void* stream);
+/* Same, and dbias[c] += sum_rows dlogits[row][c] (the head's bias gradient; caller zeroes it). */
+int b200_softmax_xent_dbias(const float* logits, int ld_logits, const int64_t* labels, int rows,
+                            int classes, float grad_scale, void* dlogits, int ld_dlogits,
+                            float* metrics, float* row_loss, float* dbias, void* stream);
 /* bf16-logit variant for large vocabularies (GPT-2 head): logits are overwritten in place by
  * dlogits. */
 int b200_softmax_xent_bf16_inplace(void* logits_bf16, int ld, const int64_t* labels, int rows,
@@ -161,6 +169,11 @@ int b200_layernorm_fwd(const void* x, const void* gamma, const void* beta, void*
 int b200_layernorm_bwd(const void* dy, const void* x, const void* gamma, const float* mean,
                        const float* rstd, const void* dresid, void* dx, float* dgamma, float* dbeta,
                        int rows, int cols, void* stream);
+/* Same, and dxsum[c] += sum_rows dx[row][c] (fp32 [cols], accumulated): dx is the gradient of the
+ * residual stream, whose column sums are the bias gradient of the projection that wrote into it. */
+int b200_layernorm_bwd_dxsum(const void* dy, const void* x, const void* gamma, const float* mean,
+                             const float* rstd, const void* dresid, void* dx, float* dgamma, float* dbeta,
+                             float* dxsum, int rows, int cols, void* stream);
 /* out[b,t,:] = wte[tok[b,t],:] + wpe[t,:]   (bf16 tables, int64 tokens) */
 int b200_embedding_fwd(const int64_t* tokens, const void* wte, const void* wpe, void* out,
                        int batch, int seq, int dim, void* stream);

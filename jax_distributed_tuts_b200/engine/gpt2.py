@@ -60,12 +60,20 @@ class GPT2Engine(FusedEngine):
         self.mbB = self.B // num_minibatches
         self.M = self.mbB * self.T
         c, L = self.C, self.L
-        # buckets in gradient-ready order: final norm, layers L-1 .. 0, embeddings
-        leaves = [("ln_f/scale", (c,), 0), ("ln_f/bias", (c,), 0)]
+        # Buckets in gradient-ready order: the matrices of layers L-1 .. 0 (bucket j = layer L-1-j), then
+        # one last bucket with the embeddings and *all* 1-D leaves (biases, norm scales). Keeping the
+        # vectors together makes their gradients one contiguous region: it is cleared with a single
+        # launch per step and filled by atomics from the kernels that already hold the data (dgrad
+        # epilogues, LayerNorm backward) instead of separate column-sum passes.
+        mats, vecs = [], []
         for j, i in enumerate(range(L - 1, -1, -1)):
-            leaves += _layer_leaves(i, c, 1 + j)
-        leaves += [("wte", (self.Vp, c), L + 1), ("wpe", (config.n_ctx, c), L + 1)]
+            for path, shape, _ in _layer_leaves(i, c, j):
+                (mats if len(shape) == 2 else vecs).append((path, shape, j if len(shape) == 2 else L))
+        leaves = mats + [("wte", (self.Vp, c), L), ("wpe", (config.n_ctx, c), L)] + vecs + \
+            [("ln_f/scale", (c,), L), ("ln_f/bias", (c,), L)]
         self._setup_buffers(FlatLayout(leaves, self.world))
+        first_vec, last_vec = self.layout.leaves[vecs[0][0]], self.layout.leaves["ln_f/bias"]
+        self._vec_grads = self.g32[first_vec.offset: last_vec.offset + last_vec.ld]
         d, M = self.device, self.M
         bf, f32 = torch.bfloat16, torch.float32
         self.tokens = torch.zeros(self.B, self.T, dtype=torch.int64, device=d)
@@ -151,9 +159,9 @@ class GPT2Engine(FusedEngine):
         if self.overlap:
             torch.cuda.current_stream().wait_stream(self.side_stream)
         else:
-            for b in range(self.L + 1):
+            for b in range(self.L):
                 self._sync_bucket(b, last=False)
-        self._sync_bucket(self.L + 1, last=True)
+        self._sync_bucket(self.L, last=True)
         K.rng_split_(self.rng_base, None, _rng.salt_word(next_rng), 0)
         self.release_gathered()
 
@@ -161,11 +169,11 @@ class GPT2Engine(FusedEngine):
         c = self.C
         self._embed(tok)
         x = self.x0
-        bucket_of = lambda layer: 1 + (self.L - 1 - layer)
+        bucket_of = lambda layer: self.L - 1 - layer
         self.prefetch_bucket(bucket_of(0))
         for i in range(self.L):
             p, A = f"h_{i}/", self.acts[i]
-            self.prefetch_bucket(bucket_of(i + 1) if i + 1 < self.L else self.L + 1, keep=bucket_of(i))   # next layer / the tied head
+            self.prefetch_bucket(bucket_of(i + 1) if i + 1 < self.L else self.L, keep=bucket_of(i))   # next layer / the tied head
             K.layernorm_fwd(x, self.vec(p + "ln_1/scale"), self.vec(p + "ln_1/bias"), A["a"], A["mean1"], A["rstd1"])
             self.gemm_w(A["a"], p + "attn/c_attn/kernel", A["qkv"], bias=self.vec(p + "attn/c_attn/bias"))
             K.attention_fwd(A["qkv"], A["att"], A["lse"], self.mbB, self.T, self.Hh)
@@ -184,50 +192,45 @@ class GPT2Engine(FusedEngine):
         c, M = self.C, self.M
         g2, g1 = self.grad2d, self.grad1d
         acc = accumulate
+        if not acc:
+            K.scale_(self._vec_grads, 0.0)                   # every bias / norm gradient of the model, one launch
         logits = self.logits[:, : self.V]
         K.softmax_xent_bf16_(logits, tgt.reshape(-1), grad_scale=1.0 / M, metrics=self.step_metrics)
         dlog = self.logits                                   # now the gradient (pad columns stay zero)
-        self.prefetch_bucket(1, keep=self.L + 1)             # top layer's weights while the head runs
+        self.prefetch_bucket(0, keep=self.L)                 # top layer's weights while the head runs
         K.gemm(dlog, self.xf, g2("wte"), a_mn=True, b_mn=True, accumulate=acc)      # dwte = dlogits^T xf
         self.gemm_w(dlog, "wte", self.dm)                                            # dxf = dlogits wte
         dx, spare = self.dxa, self.dxb
-        if not acc:
-            K.scale_(g1("ln_f/scale"), 0.0)
-            K.scale_(g1("ln_f/bias"), 0.0)
+        top = f"h_{self.L - 1}/"
+        # d(residual stream) out of the final norm; its column sums are the top layer's mlp/c_proj bias gradient
         K.layernorm_bwd(self.dm, self._x_last, self.vec("ln_f/scale"), self.meanf, self.rstdf, dx, g1("ln_f/scale"),
-                        g1("ln_f/bias"))
-        if last and self.overlap:
-            self._sync_bucket_async(0)
+                        g1("ln_f/bias"), dxsum=g1(top + "mlp/c_proj/bias"))
         for j, i in enumerate(range(self.L - 1, -1, -1)):
             p, A = f"h_{i}/", self.acts[i]
             if i > 0:
-                self.prefetch_bucket(1 + j + 1, keep=1 + j)  # the layer below, needed next
-            # x2 = x1 + gelu(m2 Wfc + bfc) Wproj + bproj
+                self.prefetch_bucket(j + 1, keep=j)          # the layer below, needed next
+            # x2 = x1 + gelu(m2 Wfc + bfc) Wproj + bproj          (bias gradient of Wproj: already summed from dx)
             K.gemm(A["hact"], dx, g2(p + "mlp/c_proj/kernel"), a_mn=True, b_mn=True, accumulate=acc)
-            K.colsum(dx, g1(p + "mlp/c_proj/bias"), accumulate=acc)
-            self.gemm_wT(dx, p + "mlp/c_proj/kernel", self.dh, bwd=True, aux=A["hpre"], act="gelu")
+            self.gemm_wT(dx, p + "mlp/c_proj/kernel", self.dh, bwd=True, aux=A["hpre"], act="gelu",
+                         dbias=g1(p + "mlp/c_fc/bias"))      # dh = d(pre-GELU); its column sums = c_fc bias gradient
             K.gemm(A["m2"], self.dh, g2(p + "mlp/c_fc/kernel"), a_mn=True, b_mn=True, accumulate=acc)
-            K.colsum(self.dh, g1(p + "mlp/c_fc/bias"), accumulate=acc)
             self.gemm_wT(self.dh, p + "mlp/c_fc/kernel", self.dm)
-            if not acc:
-                for q in ("ln_1/scale", "ln_1/bias", "ln_2/scale", "ln_2/bias"):
-                    K.scale_(g1(p + q), 0.0)
             K.layernorm_bwd(self.dm, A["x1"], self.vec(p + "ln_2/scale"), A["mean2"], A["rstd2"], spare,
-                            g1(p + "ln_2/scale"), g1(p + "ln_2/bias"), dresid=dx)
+                            g1(p + "ln_2/scale"), g1(p + "ln_2/bias"), dresid=dx, dxsum=g1(p + "attn/c_proj/bias"))
             dx, spare = spare, dx                           # dx = d(x1)
             # x1 = x + att Wo + bo
             K.gemm(A["att"], dx, g2(p + "attn/c_proj/kernel"), a_mn=True, b_mn=True, accumulate=acc)
-            K.colsum(dx, g1(p + "attn/c_proj/bias"), accumulate=acc)
             self.gemm_wT(dx, p + "attn/c_proj/kernel", self.dm)                      # d(att)
             K.attention_bwd(A["qkv"], A["att"], self.dm, A["lse"], self.dqkv, self.att_scratch, self.mbB, self.T, self.Hh)
             K.gemm(A["a"], self.dqkv, g2(p + "attn/c_attn/kernel"), a_mn=True, b_mn=True, accumulate=acc)
-            K.colsum(self.dqkv, g1(p + "attn/c_attn/bias"), accumulate=acc)
+            K.colsum(self.dqkv, g1(p + "attn/c_attn/bias"), accumulate=True)
             self.gemm_wT(self.dqkv, p + "attn/c_attn/kernel", self.dm)               # d(a)
+            below = g1(f"h_{i - 1}/mlp/c_proj/bias") if i > 0 else None
             K.layernorm_bwd(self.dm, A["x_in"], self.vec(p + "ln_1/scale"), A["mean1"], A["rstd1"], spare,
-                            g1(p + "ln_1/scale"), g1(p + "ln_1/bias"), dresid=dx)
+                            g1(p + "ln_1/scale"), g1(p + "ln_1/bias"), dresid=dx, dxsum=below)
             dx, spare = spare, dx                           # dx = d(x_in)
             if last and self.overlap:
-                self._sync_bucket_async(1 + j)
+                self._sync_bucket_async(j)                   # this layer's matrices: reduce + update under the rest
         if not acc:
             K.scale_(self.grad2d_full("wpe"), 0.0)
         K.embedding_bwd(tok, dx, self.grad2d_full("wte"), self.grad2d_full("wpe"))

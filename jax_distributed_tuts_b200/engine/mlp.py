@@ -56,13 +56,17 @@ class MLPEngine(FusedEngine):
         # launches, the wgrad K loop does the summation and the dropout epilogue switches RNG
         # stream per minibatch row block, so results equal the reference's loop (util.py:58-77).
         self.fuse_minibatches = fuse_minibatches and num_minibatches <= 16
-        # bucket 0 = output layer (gradients complete first in backward), bucket 1 = input layer
+        # bucket 0 = output layer's matrix (its gradient completes first in backward), bucket 1 = input
+        # layer's matrix + both bias vectors (contiguous: cleared with one launch, filled by atomics
+        # from the xent kernel and the dgrad epilogue instead of separate column-sum passes)
         self._setup_buffers(FlatLayout([
             ("output_dense/kernel", (self.H, self.Cn), 0),
-            ("output_dense/bias", (self.Cn,), 0),
             ("input_dense/kernel", (self.In, self.H), 1),
             ("input_dense/bias", (self.H,), 1),
+            ("output_dense/bias", (self.Cn,), 1),
         ], self.world))
+        b1, b2 = self.layout.leaves["input_dense/bias"], self.layout.leaves["output_dense/bias"]
+        self._vec_grads = self.g32[b1.offset: b2.offset + b2.ld]
         d = self.device
         rows = self.B if self.fuse_minibatches else self.mb
         pad8 = lambda c: _round_up(c, 8)
@@ -100,6 +104,7 @@ class MLPEngine(FusedEngine):
         axis_idx = self.mesh.axis_index(self.data_axis_name)
         salts = [_rng.salt_word(_rng.fold_in(mb_keys[i], axis_idx)) for i in range(nmb)]
         K.scale_(self.step_metrics, 0.0)
+        K.scale_(self._vec_grads, 0.0)
         xb = self.x_bf[:, : self.In]
         if self.x_bf.shape[1] == self.In:
             K.cast_f32_bf16(self.x_in, self.x_bf)
@@ -128,11 +133,11 @@ class MLPEngine(FusedEngine):
         drop = dict(drop_key=self.rng_base, drop_rate=self.rate, drop_salts=salts, drop_rows_per_salt=rows_per_salt)
         self.gemm_w(xs, "input_dense/kernel", self.h, bias=self.vec("input_dense/bias"), act="silu", pre=self.pre, **drop)
         self.gemm_w(self.h, "output_dense/kernel", logits, bias=self.vec("output_dense/bias"))
-        K.softmax_xent(logits, lab, grad_scale=1.0 / self.mb, dlogits=dlogits, metrics=self.step_metrics)
+        K.softmax_xent(logits, lab, grad_scale=1.0 / self.mb, dlogits=dlogits, metrics=self.step_metrics,
+                       dbias=self.grad1d("output_dense/bias"))
         K.gemm(self.h, dlogits, self.grad2d("output_dense/kernel"), a_mn=True, b_mn=True, accumulate=accumulate)
-        K.colsum(dlogits, self.grad1d("output_dense/bias"), accumulate=accumulate)
         if last and self.overlap:
-            self._sync_bucket_async(0)   # output layer's bucket: reduce + update under the rest of the backward
-        self.gemm_wT(dlogits, "output_dense/kernel", self.dpre, bwd=True, aux=self.pre, act="silu", **drop)
+            self._sync_bucket_async(0)   # output layer's matrix: reduce + update under the rest of the backward
+        self.gemm_wT(dlogits, "output_dense/kernel", self.dpre, bwd=True, aux=self.pre, act="silu",
+                     dbias=self.grad1d("input_dense/bias"), **drop)
         K.gemm(xs, self.dpre, self.grad2d("input_dense/kernel"), a_mn=True, b_mn=True, accumulate=accumulate)
-        K.colsum(self.dpre, self.grad1d("input_dense/bias"), accumulate=accumulate)

@@ -10,7 +10,7 @@ from typing import Optional
 
 from . import _build
 
-ABI_VERSION = 11
+ABI_VERSION = 12
 
 _lib: Optional[C.CDLL] = None
 
@@ -45,6 +45,7 @@ class GemmArgs(C.Structure):
         ("drop_salts", C.c_uint64 * 16),
         ("pair_mode", C.c_int32),
         ("split_k", C.c_int32),
+        ("dbias", C.c_void_p),
     ]
 
 
@@ -100,6 +101,8 @@ def _declare(lib: C.CDLL) -> None:
     sigs = {
         "b200_gemm_bf16": [C.POINTER(GemmArgs), vp],
         "b200_softmax_xent": [vp, i32, vp, i32, i32, f32, vp, i32, vp, vp, vp],
+        "b200_softmax_xent_dbias": [vp, i32, vp, i32, i32, f32, vp, i32, vp, vp, vp, vp],
+        "b200_layernorm_bwd_dxsum": [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, vp],
         "b200_softmax_xent_bf16_inplace": [vp, i32, vp, i32, i32, f32, vp, vp, vp],
         "b200_colsum_bf16": [vp, i32, i32, i32, vp, i32, vp],
         "b200_adamw": [vp, vp, vp, vp, vp, i64, C.POINTER(AdamWHParams), vp, i32, i32, vp],

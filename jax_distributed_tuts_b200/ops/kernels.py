@@ -58,6 +58,7 @@ def gemm(
     block_n: int = 0,
     pair_mode: int = 0,
     split_k: int = 0,
+    dbias: Optional[torch.Tensor] = None,
 ) -> torch.Tensor:
     """``out (+)= epilogue(A @ B)`` on tcgen05 (see ``include/b200dist.h`` for the layouts).
 
@@ -121,19 +122,23 @@ def gemm(
     args.block_n = block_n
     args.pair_mode = pair_mode
     args.split_k = split_k
+    if dbias is not None:
+        assert dbias.dtype == torch.float32 and dbias.numel() >= n
+        args.dbias = dbias.data_ptr()
     _lib.check(_lib.lib().b200_gemm_bf16(C.byref(args), _stream()))
     return out
 
 
 def softmax_xent(logits: torch.Tensor, labels: torch.Tensor, *, grad_scale: float,
                  dlogits: Optional[torch.Tensor], metrics: Optional[torch.Tensor],
-                 row_loss: Optional[torch.Tensor] = None) -> None:
-    """fp32 logits [rows, classes] -> dlogits bf16, metrics[0] += loss sum, metrics[1] += #correct."""
+                 row_loss: Optional[torch.Tensor] = None, dbias: Optional[torch.Tensor] = None) -> None:
+    """fp32 logits [rows, classes] -> dlogits bf16, metrics[0] += loss sum, metrics[1] += #correct;
+    ``dbias[c] += sum_rows dlogits[:, c]`` when given."""
     assert logits.dtype == torch.float32 and labels.dtype == torch.int64
     rows, classes = logits.shape
-    _lib.check(_lib.lib().b200_softmax_xent(
+    _lib.check(_lib.lib().b200_softmax_xent_dbias(
         logits.data_ptr(), _ld(logits), labels.data_ptr(), rows, classes, grad_scale,
-        _ptr(dlogits), _ld(dlogits) if dlogits is not None else 0, _ptr(metrics), _ptr(row_loss),
+        _ptr(dlogits), _ld(dlogits) if dlogits is not None else 0, _ptr(metrics), _ptr(row_loss), _ptr(dbias),
         _stream()))
 
 
@@ -210,11 +215,11 @@ def layernorm_fwd(x, gamma, beta, y, mean, rstd, eps: float = 1e-5):
     return y
 
 
-def layernorm_bwd(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, dresid=None):
+def layernorm_bwd(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, dresid=None, dxsum=None):
     rows, cols = x.shape
-    _lib.check(_lib.lib().b200_layernorm_bwd(dy.data_ptr(), x.data_ptr(), gamma.data_ptr(), mean.data_ptr(),
-                                              rstd.data_ptr(), _ptr(dresid), dx.data_ptr(), dgamma.data_ptr(),
-                                              dbeta.data_ptr(), rows, cols, _stream()))
+    _lib.check(_lib.lib().b200_layernorm_bwd_dxsum(dy.data_ptr(), x.data_ptr(), gamma.data_ptr(), mean.data_ptr(),
+                                                    rstd.data_ptr(), _ptr(dresid), dx.data_ptr(), dgamma.data_ptr(),
+                                                    dbeta.data_ptr(), _ptr(dxsum), rows, cols, _stream()))
     return dx
 
 
