@@ -176,6 +176,7 @@ def main() -> None:
                          "reference = the unmodified reference (not installable here)")
     ap.add_argument("--config", default="mlp_dp", choices=sorted(CONFIGS))
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--per-gpu-batch", type=int, default=0, help="override the config's per-GPU batch (exploration)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-extra", action="store_true",
                     help="skip the secondary GPT-2 small measurement that the default config appends as `extra`")
@@ -203,7 +204,9 @@ def main() -> None:
     rank, world, device = init_from_env()
     assert device.type == "cuda", "bench.py needs a GPU"
     assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run"
-    c = CONFIGS[args.config]
+    c = dict(CONFIGS[args.config])
+    if args.per_gpu_batch:
+        c["per_gpu_batch"] = args.per_gpu_batch
     cfg = dp_config()
     B = c["per_gpu_batch"]
     is_gpt = "gpt" in c

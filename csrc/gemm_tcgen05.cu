@@ -364,6 +364,8 @@ __device__ __forceinline__ void epilogue_tile(const GemmDev& p, int row_base, in
       } else {
         __nv_bfloat16* dp = reinterpret_cast<__nv_bfloat16*>(p.d) + static_cast<size_t>(row) * p.ldd + col;
         __nv_bfloat162 t0 = __floats2bfloat162_rn(v[0], v[1]), t1 = __floats2bfloat162_rn(v[2], v[3]);
+        cs[0] += __bfloat162float(t0.x); cs[1] += __bfloat162float(t0.y);
+        cs[2] += __bfloat162float(t1.x); cs[3] += __bfloat162float(t1.y);
         if (full4 && p.vec_d) {
           *reinterpret_cast<uint2*>(dp) = make_uint2(*reinterpret_cast<uint32_t*>(&t0), *reinterpret_cast<uint32_t*>(&t1));
         } else {

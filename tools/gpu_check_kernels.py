@@ -188,6 +188,18 @@ def group_gemm_epilogue():
     pg = pre.float().requires_grad_(True)
     F.gelu(pg, approximate="tanh").backward(dy.float())
     ok &= _report("bwd epilogue gelu'", _rel_err(dpre, pg.grad), 1.5e-2)
+    # dbias: column sums of the stored output from inside the epilogue (fast and generic variants)
+    for (mm, nn, kk, kw) in [(64, 512, 16, dict()), (64, 512, 16, dict(bwd=True, act="silu")),
+                             (300, 768, 256, dict(bwd=True, act="gelu")), (1024, 3072, 768, dict(bwd=True, act="gelu"))]:
+        a2 = torch.randn(mm, kk, device="cuda", dtype=torch.bfloat16)
+        b2 = torch.randn(nn, kk, device="cuda", dtype=torch.bfloat16) * 0.1
+        aux2 = torch.randn(mm, nn, device="cuda", dtype=torch.bfloat16)
+        o2 = torch.empty(mm, nn, device="cuda", dtype=torch.bfloat16)
+        for drop in (0.0, 0.1):
+            db = torch.zeros(nn, device="cuda")
+            K.gemm(a2, b2, o2, dbias=db, drop_key=key, drop_rate=drop, drop_salts=[3, 4], drop_rows_per_salt=max(1, mm // 2),
+                   **kw, **(dict(aux=aux2) if kw.get("bwd") else {}))
+            ok &= _report(f"dbias m={mm} n={nn} {kw.get('act')} drop={drop}", _rel_err(db, o2.float().sum(0)), 1e-5)
     # different salt -> different mask
     out2 = torch.empty_like(out)
     K.gemm(x, w, out2, b_mn=True, bias=bias, act="silu", drop_key=key, drop_salt=8, drop_rate=0.1)
