@@ -32,10 +32,10 @@ CONFIGS = {
     "mlp_fsdp": dict(model="mlp_784_512_10", per_gpu_batch=16, minibatches=4, hidden=512, inp=784, classes=10,
                      mode="fsdp"),
     # transformer configurations of BASELINE.json (samples = sequences of 1024 tokens)
-    "gpt2s_dp": dict(model="gpt2_small_124M", gpt="small", per_gpu_batch=8, minibatches=1, seq=1024, mode="dp"),
-    "gpt2s_fsdp": dict(model="gpt2_small_124M", gpt="small", per_gpu_batch=8, minibatches=1, seq=1024, mode="fsdp"),
-    "gpt2m_dp": dict(model="gpt2_medium_355M", gpt="medium", per_gpu_batch=8, minibatches=1, seq=1024, mode="dp"),
-    "gpt2m_2d": dict(model="gpt2_medium_355M", gpt="medium", per_gpu_batch=8, minibatches=1, seq=1024, mode="fsdp",
+    "gpt2s_dp": dict(model="gpt2_small_124M", gpt="small", per_gpu_batch=16, minibatches=1, seq=1024, mode="dp"),
+    "gpt2s_fsdp": dict(model="gpt2_small_124M", gpt="small", per_gpu_batch=16, minibatches=1, seq=1024, mode="fsdp"),
+    "gpt2m_dp": dict(model="gpt2_medium_355M", gpt="medium", per_gpu_batch=16, minibatches=1, seq=1024, mode="dp"),
+    "gpt2m_2d": dict(model="gpt2_medium_355M", gpt="medium", per_gpu_batch=16, minibatches=1, seq=1024, mode="fsdp",
                      mesh2d=True),
     "gpt2_tiny": dict(model="gpt2_tiny", gpt="tiny", per_gpu_batch=4, minibatches=1, seq=128, mode="dp"),
     # 4-stage GPipe over NCCL p2p (BASELINE.json config 4): per_gpu_batch is per *pipeline* (data replica)
@@ -114,7 +114,7 @@ class ClockSampler:
 
 
 def run_secondary(args, rank, world, device) -> dict:
-    """DP GPT-2 small (124M), 8 x 1024 tokens per GPU, 10 timed steps, same timing rules."""
+    """DP GPT-2 small (124M), 16 x 1024 tokens per GPU, 10 timed steps, same timing rules."""
     import torch
     import torch.distributed as dist
 
@@ -124,7 +124,7 @@ def run_secondary(args, rank, world, device) -> dict:
     from jax_distributed_tuts_b200.models.gpt2 import GPT2, gpt2_config
     from jax_distributed_tuts_b200.state import Batch
 
-    steps, warm, B, T = 10, 3, 8, 1024
+    steps, warm, B, T = 10, 3, 16, 1024
     gcfg = gpt2_config("small")
     model = GPT2(gcfg)
     mesh = Mesh((world,), ("data",))

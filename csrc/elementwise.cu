@@ -331,11 +331,34 @@ __global__ void scale_f32_kernel(float* __restrict__ x, int64_t n, float s) {
     x[i] = s == 0.f ? 0.f : x[i] * s;
 }
 
-__global__ void rng_split_kernel(uint64_t* key, uint64_t* out_step, uint64_t salt_next, uint64_t salt_step) {
+__global__ void rng_split_kernel(uint64_t* key, uint64_t* out_step, uint64_t salt_next, uint64_t salt_step,
+                                 int32_t* step_count) {
   pdl_sync();
   uint64_t k = *key;
   if (out_step != nullptr) *out_step = mix64(k ^ salt_step);
   *key = mix64(k ^ salt_next);
+  if (step_count != nullptr) *step_count += 1;   // end-of-step bookkeeping rides along
+}
+
+// Start-of-step housekeeping in one launch: fp32 -> bf16 cast of the inputs and zeroing of up to two
+// small fp32 regions (step metrics, bias-gradient vectors).
+__global__ void cast_zero_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int64_t n,
+                                 float* __restrict__ z0, int64_t n0, float* __restrict__ z1, int64_t n1) {
+  pdl_sync();
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  const int64_t tid = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const int64_t n4 = n >> 2;
+  for (int64_t i = tid; i < n4; i += stride) {
+    float4 a = reinterpret_cast<const float4*>(src)[i];
+    __nv_bfloat162 lo = __floats2bfloat162_rn(a.x, a.y), hi = __floats2bfloat162_rn(a.z, a.w);
+    uint2 w;
+    w.x = *reinterpret_cast<uint32_t*>(&lo);
+    w.y = *reinterpret_cast<uint32_t*>(&hi);
+    reinterpret_cast<uint2*>(dst)[i] = w;
+  }
+  for (int64_t i = (n4 << 2) + tid; i < n; i += stride) dst[i] = __float2bfloat16_rn(src[i]);
+  for (int64_t i = tid; i < n0; i += stride) z0[i] = 0.f;
+  for (int64_t i = tid; i < n1; i += stride) z1[i] = 0.f;
 }
 
 // stand-alone activation + dropout (rows x cols, pitch ld)
@@ -485,9 +508,32 @@ extern "C" int b200_scale_f32(float* x, int64_t n, float scale, void* stream) {
   return 0;
 }
 
+extern "C" int b200_rng_split_bump(uint64_t* key, uint64_t* out_step, uint64_t salt_next, uint64_t salt_step,
+                                   int32_t* step_count, void* stream) {
+  B200_CUDA(launch_k(rng_split_kernel, dim3(1), dim3(1), 0, static_cast<cudaStream_t>(stream), key, out_step, salt_next,
+                     salt_step, step_count));
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200_cast_zero(const float* src, void* dst, int64_t n, float* z0, int64_t n0, float* z1, int64_t n1,
+                              void* stream) {
+  B200_REQUIRE(n >= 0 && n0 >= 0 && n1 >= 0, "cast_zero: negative size");
+  B200_REQUIRE(n == 0 || ((reinterpret_cast<uintptr_t>(src) & 15) == 0 && (reinterpret_cast<uintptr_t>(dst) & 7) == 0),
+               "cast_zero: misaligned buffers");
+  int64_t work = n / 4 + 1;
+  if (n0 > work) work = n0;
+  if (n1 > work) work = n1;
+  B200_CUDA(launch_k(cast_zero_kernel, dim3(stream_grid(work, 256)), dim3(256), 0, static_cast<cudaStream_t>(stream), src,
+                     static_cast<__nv_bfloat16*>(dst), n, z0, n0, z1, n1));
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
+
 extern "C" int b200_rng_split(uint64_t* key, uint64_t* out_step, uint64_t salt_next, uint64_t salt_step,
                               void* stream) {
-  B200_CUDA(launch_k(rng_split_kernel, dim3(1), dim3(1), 0, static_cast<cudaStream_t>(stream), key, out_step, salt_next, salt_step));
+  B200_CUDA(launch_k(rng_split_kernel, dim3(1), dim3(1), 0, static_cast<cudaStream_t>(stream), key, out_step, salt_next, salt_step,
+                     static_cast<int32_t*>(nullptr)));
   B200_CUDA(cudaGetLastError());
   return 0;
 }

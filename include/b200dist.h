@@ -16,7 +16,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 12
+#define B200_ABI_VERSION 13
 
 const char* b200_last_error(void);
 int b200_abi_version(void);
@@ -146,6 +146,14 @@ int b200_scale_f32(float* x, int64_t n, float scale, void* stream);
 /* RNG key evolution on the device: key[0] <- mix64(key[0] ^ salt_next); out_step[0] <-
  * mix64(old ^ salt_step). Mirrors `rng, step_rng = split(state.rng)` (data_paral.py:199). */
 int b200_rng_split(uint64_t* key, uint64_t* out_step, uint64_t salt_next, uint64_t salt_step,
+                   void* stream);
+
+/* The same plus `*step_count += 1` (end-of-step bookkeeping in one launch). */
+int b200_rng_split_bump(uint64_t* key, uint64_t* out_step, uint64_t salt_next, uint64_t salt_step,
+                        int32_t* step_count, void* stream);
+/* Start-of-step housekeeping in one launch: dst = bf16(src) and two small fp32 regions zeroed
+ * (either may be NULL / 0). */
+int b200_cast_zero(const float* src, void* dst, int64_t n, float* z0, int64_t n0, float* z1, int64_t n1,
                    void* stream);
 
 /* Activation / dropout as a stand-alone op (used when it cannot ride in a GEMM epilogue).

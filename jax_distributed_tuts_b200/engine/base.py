@@ -503,9 +503,23 @@ class FusedEngine:
         for b in order:
             self.bucket_segs.append((self._segs_to_device(per_bucket[b]), len(per_bucket[b])))
 
+    def _sync_all_buckets(self) -> None:
+        """All buckets in one launch (used when there is nothing to overlap with: one rank, or overlap off)."""
+        if not hasattr(self, "_all_segs"):
+            raws = [bytes(t.cpu().numpy().tobytes()) for t, _ in self.bucket_segs]
+            self._all_segs = (torch.frombuffer(bytearray(b"".join(raws)), dtype=torch.uint8).to(self.device),
+                              sum(n for _, n in self.bucket_segs))
+        self._sync_bucket(-1, last=True)
+
+    def _end_step(self, next_rng) -> None:
+        """state.rng <- rebase(next_rng) (the salt folds into the device-resident key in place) and
+        step counter += 1, one launch."""
+        K.rng_split_bump_(self.rng_base, _rng.salt_word(next_rng), self.step_count)
+        self.release_gathered()
+
     def _sync_bucket(self, b: int, last: bool) -> None:
         """Fused reduce + mean + AdamW + publish of one gradient bucket (one launch)."""
-        segs, nseg = self.bucket_segs[b]
+        segs, nseg = self._all_segs if b < 0 else self.bucket_segs[b]
         hp = AdamWHParams(self.hp["lr"], self.hp["beta1"], self.hp["beta2"], self.hp["eps"],
                           self.hp["weight_decay"], 1.0 / (self.num_minibatches * self.world))
         nmet = len(self.metric_names)
@@ -513,7 +527,7 @@ class FusedEngine:
         _lib.check(_lib.lib().b200_fused_reduce_adamw(
             C.byref(self.ctx), segs.data_ptr(), nseg, int(dp),
             None if dp else self.p_loc.data_ptr(), None if dp else self.pb.data_ptr(),
-            self.m.data_ptr(), self.v.data_ptr(), C.byref(hp), self.step_count.data_ptr(), int(last),
+            self.m.data_ptr(), self.v.data_ptr(), C.byref(hp), self.step_count.data_ptr(), 0,   # bumped by _end_step
             self.step_metrics.data_ptr() if last else None, self.metrics_acc.data_ptr() if last else None,
             nmet if last else 0, self.comm_blocks, torch.cuda.current_stream().cuda_stream))
 

@@ -149,7 +149,7 @@ class GPT2Engine(FusedEngine):
 
     def _step_body(self) -> None:
         nmb = self.num_minibatches
-        K.scale_(self.step_metrics, 0.0)
+        K.cast_zero(None, None, self.step_metrics, self._vec_grads)   # metrics + every bias / norm gradient, one launch
         self._gather_small()
         next_rng = _rng.split(_rng.Key(self.rng_base, 0), 2)[0]
         for i in range(nmb):
@@ -158,12 +158,10 @@ class GPT2Engine(FusedEngine):
             self._backward(self.tokens[sl], self.targets[sl], accumulate=i > 0, last=i == nmb - 1)
         if self.overlap:
             torch.cuda.current_stream().wait_stream(self.side_stream)
+            self._sync_bucket(self.L, last=True)
         else:
-            for b in range(self.L):
-                self._sync_bucket(b, last=False)
-        self._sync_bucket(self.L, last=True)
-        K.rng_split_(self.rng_base, None, _rng.salt_word(next_rng), 0)
-        self.release_gathered()
+            self._sync_all_buckets()
+        self._end_step(next_rng)
 
     def _forward(self, tok: torch.Tensor) -> None:
         c = self.C
@@ -192,8 +190,6 @@ class GPT2Engine(FusedEngine):
         c, M = self.C, self.M
         g2, g1 = self.grad2d, self.grad1d
         acc = accumulate
-        if not acc:
-            K.scale_(self._vec_grads, 0.0)                   # every bias / norm gradient of the model, one launch
         logits = self.logits[:, : self.V]
         K.softmax_xent_bf16_(logits, tgt.reshape(-1), grad_scale=1.0 / M, metrics=self.step_metrics)
         dlog = self.logits                                   # now the gradient (pad columns stay zero)

@@ -103,12 +103,11 @@ class MLPEngine(FusedEngine):
         mb_keys = _rng.split(step_rng, nmb)
         axis_idx = self.mesh.axis_index(self.data_axis_name)
         salts = [_rng.salt_word(_rng.fold_in(mb_keys[i], axis_idx)) for i in range(nmb)]
-        K.scale_(self.step_metrics, 0.0)
-        K.scale_(self._vec_grads, 0.0)
         xb = self.x_bf[:, : self.In]
         if self.x_bf.shape[1] == self.In:
-            K.cast_f32_bf16(self.x_in, self.x_bf)
+            K.cast_zero(self.x_in, self.x_bf, self.step_metrics, self._vec_grads)     # one launch
         else:
+            K.cast_zero(None, None, self.step_metrics, self._vec_grads)
             xb.copy_(self.x_in)
         self._gather_small()
         if self.fuse_minibatches:
@@ -119,12 +118,10 @@ class MLPEngine(FusedEngine):
                               accumulate=i > 0, last=i == nmb - 1)
         if self.overlap:
             torch.cuda.current_stream().wait_stream(self.side_stream)
+            self._sync_bucket(1, last=True)
         else:
-            self._sync_bucket(0, last=False)
-        self._sync_bucket(1, last=True)
-        # state.rng <- rebase(next_rng): the salt folds into the device-resident key in place
-        K.rng_split_(self.rng_base, None, _rng.salt_word(next_rng), 0)
-        self.release_gathered()
+            self._sync_all_buckets()
+        self._end_step(next_rng)
 
     def _fwd_bwd(self, xs, lab, salts, rows_per_salt: int, *, accumulate: bool, last: bool) -> None:
         """Forward + backward of one row block (a minibatch, or all minibatches at once)."""

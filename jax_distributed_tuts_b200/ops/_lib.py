@@ -10,7 +10,7 @@ from typing import Optional
 
 from . import _build
 
-ABI_VERSION = 12
+ABI_VERSION = 13
 
 _lib: Optional[C.CDLL] = None
 
@@ -110,6 +110,8 @@ def _declare(lib: C.CDLL) -> None:
         "b200_cast_bf16_f32": [vp, vp, i64, vp],
         "b200_scale_f32": [vp, i64, f32, vp],
         "b200_rng_split": [vp, vp, u64, u64, vp],
+        "b200_rng_split_bump": [vp, vp, u64, u64, vp, vp],
+        "b200_cast_zero": [vp, vp, i64, vp, i64, vp, i64, vp],
         "b200_act_dropout_fwd": [vp, vp, i64, i32, i32, i32, vp, u64, f32, vp],
         "b200_act_dropout_bwd": [vp, vp, vp, i64, i32, i32, i32, vp, u64, f32, vp],
         "b200_layernorm_fwd": [vp, vp, vp, vp, vp, vp, i32, i32, f32, vp],

@@ -192,6 +192,20 @@ def rng_split_(key: torch.Tensor, out_step: Optional[torch.Tensor], salt_next: i
                                           salt_step & (2**64 - 1), _stream()))
 
 
+def rng_split_bump_(key: torch.Tensor, salt_next: int, step_count: torch.Tensor) -> None:
+    """``key <- mix64(key ^ salt_next)`` and ``step_count += 1`` in one launch."""
+    _lib.check(_lib.lib().b200_rng_split_bump(key.data_ptr(), None, salt_next & (2**64 - 1), 0, step_count.data_ptr(),
+                                               _stream()))
+
+
+def cast_zero(src: Optional[torch.Tensor], dst: Optional[torch.Tensor], z0: Optional[torch.Tensor] = None,
+              z1: Optional[torch.Tensor] = None) -> None:
+    """bf16 cast of ``src`` into ``dst`` plus zeroing of up to two fp32 regions, one launch."""
+    _lib.check(_lib.lib().b200_cast_zero(_ptr(src), _ptr(dst), src.numel() if src is not None else 0,
+                                          _ptr(z0), z0.numel() if z0 is not None else 0,
+                                          _ptr(z1), z1.numel() if z1 is not None else 0, _stream()))
+
+
 def act_dropout_fwd(x: torch.Tensor, y: torch.Tensor, act, drop_key, drop_salt: int, drop_rate: float):
     rows, cols = x.shape
     _lib.check(_lib.lib().b200_act_dropout_fwd(x.data_ptr(), y.data_ptr(), rows, cols, _ld(x), _ACT[act],
