@@ -1032,7 +1032,9 @@ extern "C" int b200_gemm_bf16(const b200_gemm_args* args, void* stream) {
       double e256 = (double)t256 / (double)(((t256 + sms - 1) / sms) * sms);
       double e128 = (double)t128 / (double)(((t128 + sms - 1) / sms) * sms);
       // a problem that fits in one wave even with 128-wide tiles is latency-bound: more, smaller CTAs
+      long long t64 = m_tiles * ((n_eff + 63) / 64) * reps;
       if (splittable) bn = 256;            // split-K fills the chip; wide tiles halve L2 traffic
+      else if (t64 <= sms / 2) bn = 64;    // tiny problem: latency-bound, spread the weight stream over more CTAs
       else if (t128 <= sms) bn = 128;
       else bn = (e256 * 1.5 >= e128) ? 256 : 128;
     }
