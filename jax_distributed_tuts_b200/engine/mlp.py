@@ -65,6 +65,9 @@ class MLPEngine(FusedEngine):
             ("input_dense/bias", (self.H,), 1),
             ("output_dense/bias", (self.Cn,), 1),
         ], self.world))
+        # a sub-megabyte model: one fused reduce+update launch (two cross-GPU barriers) beats two
+        # overlapped launches (four barriers); bucket-level overlap pays off from a few MB per bucket
+        self.overlap = self.overlap and self.layout.total * 4 > (8 << 20)
         b1, b2 = self.layout.leaves["input_dense/bias"], self.layout.leaves["output_dense/bias"]
         self._vec_grads = self.g32[b1.offset: b2.offset + b2.ld]
         d = self.device
