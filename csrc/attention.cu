@@ -10,8 +10,10 @@
 // place through one 2-D tensor map), out bf16 [batch][seq][heads][64], lse fp32
 // [batch][heads][seq] in log2 units of the scaled scores.
 //
-// Warp roles (192 threads): warp 0 TMA producer, warp 1 MMA issuer (+ TMEM owner),
-// warps 2..5 one thread per query row (softmax / gradient math / epilogue).
+// Warp roles: warp 0 TMA producer, warp 1 MMA issuer (+ TMEM owner), the rest math warps.
+// Forward: 4 math warps (a thread owns one query row); two CTAs share an SM and fill each other's
+// MMA <-> softmax dependency bubbles. Backward: 8 math warps, two per TMEM lane quadrant, a thread
+// owns one query row and half of the tile's columns.
 #include "../include/b200dist.h"
 #include "common.cuh"
 
@@ -21,7 +23,8 @@ constexpr int HD = 64;        // head dim
 constexpr int BQ = 128;       // query rows per tile
 constexpr int BKV = 128;      // key/value rows per tile
 constexpr int TILE_BYTES = 128 * 64 * 2;   // one [128][64] bf16 swizzled tile = 16 KB
-constexpr int ATT_THREADS = 192;
+constexpr int ATT_FWD_THREADS = 192;   // TMA warp + MMA warp + 4 math warps (one query row per thread); two CTAs per SM
+constexpr int ATT_BWD_THREADS = 320;   // TMA warp + MMA warp + 8 math warps (two per TMEM lane quadrant, half the columns each)
 
 __device__ __forceinline__ uint64_t kdesc(uint32_t addr) { return umma_smem_desc(addr, 16, 1024); }
 __device__ __forceinline__ uint64_t mndesc(uint32_t addr, uint32_t lbo) { return umma_smem_desc(addr, lbo, 1024); }
@@ -56,36 +59,166 @@ struct AttnFwdSmem {
   static constexpr int V0 = K0 + 2 * TILE_BYTES;       // 2 stages
   static constexpr int P = V0 + 2 * TILE_BYTES;        // 2 tiles
   static constexpr int BAR = P + 2 * TILE_BYTES;
-  static constexpr int BYTES = BAR + 128 + 1024;
+  // No alignment slack: two CTAs must fit in one SM's 228 KB (2 x (BYTES + 1 KB reserved) <= 233472),
+  // so the kernel requires (and checks) a 1024-byte aligned dynamic shared memory base.
+  static constexpr int BYTES = BAR + 128;
 };
+static_assert(2 * (AttnFwdSmem::BYTES + 1024) <= 233472, "forward attention: two CTAs per SM must fit");
 
-__global__ void __launch_bounds__(ATT_THREADS, 2)
+// Work item = one (q tile, head, sequence). Items are numbered heavy-first (late q tiles see the
+// most kv tiles) and dealt to the persistent CTAs in snake order, so every CTA gets nearly the
+// same number of kv steps.
+struct FwdItem {
+  int qt, h, b;
+};
+__device__ __forceinline__ int fwd_item_index(int round, int n_cta, int cta) {
+  return round * n_cta + ((round & 1) ? n_cta - 1 - cta : cta);
+}
+__device__ __forceinline__ FwdItem fwd_item_decode(int item, int nq, int heads, int hb) {
+  FwdItem w;
+  const int q = item / hb;
+  const int rem = item - q * hb;
+  w.qt = nq - 1 - q;
+  w.b = rem / heads;
+  w.h = rem - w.b * heads;
+  return w;
+}
+
+constexpr float kRescaleThreshold = 8.0f;   // log2 units: P stays below 2^8, far inside bf16/fp32 range
+
+// One kv step of the softmax for row `r`: S (TMEM) -> registers, row maximum, lazily rescaled running
+// state, probabilities -> bf16 -> swizzled shared memory (A operand of the P V MMA).
+// The output accumulator O stays in TMEM: the P V MMAs accumulate into it, and it is only
+// multiplied by 2^(m_old - m_new) when the row maximum grew by more than kRescaleThreshold
+// (otherwise the stale maximum keeps being used for P and l, which is exact after the final 1/l).
+template <bool DIAG>
+__device__ __forceinline__ void fwd_softmax_step(uint32_t tmem_s_lane, uint32_t tmem_o_lane, uint8_t* sp, int r, int lane,
+                                                 float scale_log2, bool first, float& m_used, float& l_run,
+                                                 uint64_t* s_free, uint64_t* o_full, uint32_t o_prev_parity,
+                                                 uint64_t* p_full) {
+  // pass 1: row maximum, 32 columns at a time (few live registers: the O rescale below needs room)
+  float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    uint32_t v[32];
+    tmem_ld_32x32b_x32(tmem_s_lane + c * 32, v);
+    tmem_ld_wait();
+#pragma unroll
+    for (int i = 0; i < 32; ++i) {
+      float x = __uint_as_float(v[i]);
+      if (DIAG && (c * 32 + i) > r) x = -INFINITY;
+      mx[i & 3] = fmaxf(mx[i & 3], x);
+    }
+  }
+  const float m_tile = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3])) * scale_log2;
+  bool o_seen = first;                      // first step of an item: no earlier P V to wait for
+  if (first) {
+    m_used = m_tile;
+  } else {
+    const bool need = m_tile > m_used + kRescaleThreshold;
+    if (__any_sync(0xffffffffu, need)) {
+      mbar_wait(o_full, o_prev_parity);     // every P V issued so far has landed in O
+      tc_fence_after();
+      o_seen = true;
+      const float alpha = need ? fast_exp2(m_used - m_tile) : 1.0f;
+      if (need) m_used = m_tile;
+      l_run *= alpha;
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        uint32_t o[32];
+        tmem_ld_32x32b_x32(tmem_o_lane + c * 32, o);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+        tmem_st_32x32b_x32(tmem_o_lane + c * 32, o);
+      }
+      tmem_st_wait();
+    }
+  }
+  // pass 2: the whole row into registers, then S is free for the next tile's Q K^T
+  uint32_t sv[4][32];
+#pragma unroll
+  for (int c = 0; c < 4; ++c) tmem_ld_32x32b_x32(tmem_s_lane + c * 32, sv[c]);
+  tmem_ld_wait();
+  tc_fence_before();
+  __syncwarp();
+  if (lane == 0) mbar_arrive(s_free);
+  float ls[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+  for (int c = 0; c < 4; ++c)
+#pragma unroll
+    for (int i = 0; i < 32; ++i) {
+      float e = fast_exp2(fmaf(__uint_as_float(sv[c][i]), scale_log2, -m_used));
+      if (DIAG && (c * 32 + i) > r) e = 0.f;
+      ls[i & 3] += e;
+      sv[c][i] = __float_as_uint(e);
+    }
+  l_run += (ls[0] + ls[1]) + (ls[2] + ls[3]);
+  if (!o_seen) {                            // P buffer: the previous step's P V must have read it
+    mbar_wait(o_full, o_prev_parity);
+    tc_fence_after();
+  }
+#pragma unroll
+  for (int c = 0; c < 4; ++c)
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      uint4 w;
+      w.x = pack_bf16x2(__uint_as_float(sv[c][g * 8 + 0]), __uint_as_float(sv[c][g * 8 + 1]));
+      w.y = pack_bf16x2(__uint_as_float(sv[c][g * 8 + 2]), __uint_as_float(sv[c][g * 8 + 3]));
+      w.z = pack_bf16x2(__uint_as_float(sv[c][g * 8 + 4]), __uint_as_float(sv[c][g * 8 + 5]));
+      w.w = pack_bf16x2(__uint_as_float(sv[c][g * 8 + 6]), __uint_as_float(sv[c][g * 8 + 7]));
+      st_swizzled_16B(sp, r, c * 32 + g * 8, w);
+    }
+  tc_fence_before();
+  fence_proxy_async_smem();     // generic-proxy smem writes -> visible to the tensor core
+  __syncwarp();
+  if (lane == 0) mbar_arrive(p_full);
+}
+
+// Persistent: gridDim.x CTAs (two per SM) walk the work items; all pipelines (K and V stages, S, P,
+// O) keep running across item boundaries, so the next item's Q/K loads and first S = Q K^T are
+// in flight while the math warps finish the current item.
+__global__ void __launch_bounds__(ATT_FWD_THREADS, 2)
 attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* __restrict__ out,
-                     float* __restrict__ lse, int seq, int heads, float scale_log2) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+                     float* __restrict__ lse, int seq, int heads, int batch, float scale_log2) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;
+  if ((smem_u32(smem) & 1023u) != 0) {      // swizzled TMA / UMMA tiles need a 1024-byte aligned base
+    if (threadIdx.x == 0) printf("b200: attention_fwd shared memory base is not 1024-byte aligned\n");
+    __trap();
+  }
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + AttnFwdSmem::BAR);
   uint64_t* q_full = bars + 0;
-  uint64_t* kv_full = bars + 1;   // [2]
-  uint64_t* kv_empty = bars + 3;  // [2]
-  uint64_t* s_full = bars + 5;
-  uint64_t* p_full = bars + 6;
-  uint64_t* o_full = bars + 7;
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 8);
+  uint64_t* q_empty = bars + 1;
+  uint64_t* k_full = bars + 2;    // [2]
+  uint64_t* k_empty = bars + 4;   // [2]
+  uint64_t* v_full = bars + 6;    // [2]
+  uint64_t* v_empty = bars + 8;   // [2]
+  uint64_t* s_full = bars + 10;
+  uint64_t* s_free = bars + 11;
+  uint64_t* p_full = bars + 12;
+  uint64_t* o_full = bars + 13;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 14);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nq = seq / BQ;
-  const int qt = nq - 1 - static_cast<int>(blockIdx.x);   // heavy (late) tiles first
-  const int h = blockIdx.y, b = blockIdx.z;
+  const int hb = heads * batch;
+  const int n_items = nq * hb;
+  const int n_cta = gridDim.x, cta = blockIdx.x;
   const int C = heads * HD;
-  const int row0 = b * seq;
-  const int nkv = qt + 1;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tm_qkv);
     mbar_init(q_full, 1);
-    for (int s = 0; s < 2; ++s) { mbar_init(&kv_full[s], 1); mbar_init(&kv_empty[s], 1); }
+    mbar_init(q_empty, 1);
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&k_full[s], 1);
+      mbar_init(&k_empty[s], 1);
+      mbar_init(&v_full[s], 1);
+      mbar_init(&v_empty[s], 1);
+    }
     mbar_init(s_full, 1);
+    mbar_init(s_free, 4);
     mbar_init(p_full, 4);
     mbar_init(o_full, 1);
     mbar_fence_init();
@@ -100,135 +233,122 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* 
   const uint32_t tmem_o = tmem_base + 128;    // 64 columns
 
   if (warp == 0) {
-    if (lane == 0) {
-      mbar_expect_tx(q_full, TILE_BYTES);
-      tma_load_2d(smem + AttnFwdSmem::Q, &tm_qkv, q_full, h * HD, row0 + qt * BQ);
-      for (int j = 0; j < nkv; ++j) {
-        const int s = j & 1;
-        mbar_wait(&kv_empty[s], ((j >> 1) & 1) ^ 1);
-        mbar_expect_tx(&kv_full[s], 2 * TILE_BYTES);
-        tma_load_2d(smem + AttnFwdSmem::K0 + s * TILE_BYTES, &tm_qkv, &kv_full[s], C + h * HD, row0 + j * BKV);
-        tma_load_2d(smem + AttnFwdSmem::V0 + s * TILE_BYTES, &tm_qkv, &kv_full[s], 2 * C + h * HD, row0 + j * BKV);
+    if (elect_one()) {
+      int g = 0, n = 0;       // g: kv steps issued so far (all items), n: items so far
+      for (int round = 0;; ++round, ++n) {
+        const int item = fwd_item_index(round, n_cta, cta);
+        if (item >= n_items) break;
+        const FwdItem w = fwd_item_decode(item, nq, heads, hb);
+        const int row0 = w.b * seq;
+        mbar_wait(q_empty, (n & 1) ^ 1);
+        mbar_expect_tx(q_full, TILE_BYTES);
+        tma_load_2d(smem + AttnFwdSmem::Q, &tm_qkv, q_full, w.h * HD, row0 + w.qt * BQ);
+        for (int j = 0; j <= w.qt; ++j, ++g) {
+          const int s = g & 1;
+          const uint32_t ph = ((g >> 1) & 1) ^ 1;
+          mbar_wait(&k_empty[s], ph);
+          mbar_expect_tx(&k_full[s], TILE_BYTES);
+          tma_load_2d(smem + AttnFwdSmem::K0 + s * TILE_BYTES, &tm_qkv, &k_full[s], C + w.h * HD, row0 + j * BKV);
+          mbar_wait(&v_empty[s], ph);
+          mbar_expect_tx(&v_full[s], TILE_BYTES);
+          tma_load_2d(smem + AttnFwdSmem::V0 + s * TILE_BYTES, &tm_qkv, &v_full[s], 2 * C + w.h * HD, row0 + j * BKV);
+        }
       }
     }
   } else if (warp == 1) {
     constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, 0, 0);   // S = Q K^T
-    constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);    // O = P V (V is MN-major)
+    constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);    // O += P V (V is MN-major)
     const uint32_t sq = smem_u32(smem + AttnFwdSmem::Q);
     const uint32_t sp = smem_u32(smem + AttnFwdSmem::P);
-    mbar_wait(q_full, 0);
-    for (int j = 0; j < nkv; ++j) {
-      const int s = j & 1;
+    // S(g) = Q K(g)^T into the single S accumulator; `last` also releases the Q tile
+    auto issue_s = [&](int g, bool last) {
+      const int s = g & 1;
       const uint32_t sk = smem_u32(smem + AttnFwdSmem::K0 + s * TILE_BYTES);
-      const uint32_t sv = smem_u32(smem + AttnFwdSmem::V0 + s * TILE_BYTES);
-      mbar_wait(&kv_full[s], (j >> 1) & 1);
+      mbar_wait(&k_full[s], (g >> 1) & 1);
       tc_fence_after();
-      if (lane == 0) {
+      if (elect_one()) {
 #pragma unroll
         for (int k = 0; k < HD / 16; ++k) umma_bf16(tmem_s, kdesc(sq + k * 32), kdesc(sk + k * 32), idesc_s, k ? 1u : 0u);
         umma_commit(s_full);
+        umma_commit(&k_empty[s]);
+        if (last) umma_commit(q_empty);
       }
       __syncwarp();
-      mbar_wait(p_full, j & 1);
-      tc_fence_after();
-      if (lane == 0) {
+    };
+    int g = 0, n = 0;
+    for (int round = 0;; ++round, ++n) {
+      const int item = fwd_item_index(round, n_cta, cta);
+      if (item >= n_items) break;
+      const int nkv = (nq - 1 - item / hb) + 1;
+      mbar_wait(q_full, n & 1);
+      if (g > 0) mbar_wait(s_free, (g - 1) & 1);     // the previous item's last scores have been read
+      issue_s(g, nkv == 1);
+      for (int j = 0; j < nkv; ++j, ++g) {
+        if (j + 1 < nkv) {
+          mbar_wait(s_free, g & 1);                  // S(g) is in registers: overwrite it under the exponentials
+          issue_s(g + 1, j + 2 == nkv);
+        }
+        const int s = g & 1;
+        const uint32_t sv = smem_u32(smem + AttnFwdSmem::V0 + s * TILE_BYTES);
+        mbar_wait(p_full, g & 1);
+        mbar_wait(&v_full[s], (g >> 1) & 1);
+        tc_fence_after();
+        if (elect_one()) {
 #pragma unroll
-        for (int k = 0; k < BKV / 16; ++k)
-          umma_bf16(tmem_o, kdesc(sp + (k >> 2) * TILE_BYTES + (k & 3) * 32), mndesc(sv + k * 2048, TILE_BYTES),
-                    idesc_o, k ? 1u : 0u);
-        umma_commit(o_full);
-        umma_commit(&kv_empty[s]);
+          for (int k = 0; k < BKV / 16; ++k)
+            umma_bf16(tmem_o, kdesc(sp + (k >> 2) * TILE_BYTES + (k & 3) * 32), mndesc(sv + k * 2048, TILE_BYTES),
+                      idesc_o, (j | k) ? 1u : 0u);
+          umma_commit(o_full);
+          umma_commit(&v_empty[s]);
+        }
+        __syncwarp();
       }
-      __syncwarp();
     }
   } else {
     const int quad = warp & 3;
     const int r = quad * 32 + lane;                 // row within the q tile
     const uint32_t lane_off = static_cast<uint32_t>(quad * 32) << 16;
-    float o_acc[HD];
-#pragma unroll
-    for (int i = 0; i < HD; ++i) o_acc[i] = 0.f;
-    float m_run = -INFINITY, l_run = 0.f;
     uint8_t* sp = smem + AttnFwdSmem::P;
-    for (int j = 0; j < nkv; ++j) {
-      mbar_wait(s_full, j & 1);
-      tc_fence_after();
-      const bool diag = (j == qt);
-      // pass 1: row maximum
-      float m_tile = -INFINITY;
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t v[32];
-        tmem_ld_32x32b_x32(tmem_s + lane_off + c * 32, v);
-        tmem_ld_wait();
-#pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          float x = __uint_as_float(v[i]);
-          if (diag && (c * 32 + i) > r) x = -INFINITY;
-          m_tile = fmaxf(m_tile, x);
-        }
+    int g = 0;
+    for (int round = 0;; ++round) {
+      const int item = fwd_item_index(round, n_cta, cta);
+      if (item >= n_items) break;
+      const FwdItem w = fwd_item_decode(item, nq, heads, hb);
+      float m_used = -INFINITY, l_run = 0.f;
+      for (int j = 0; j < w.qt; ++j, ++g) {
+        mbar_wait(s_full, g & 1);
+        tc_fence_after();
+        fwd_softmax_step<false>(tmem_s + lane_off, tmem_o + lane_off, sp, r, lane, scale_log2, j == 0, m_used, l_run,
+                                s_free, o_full, (g - 1) & 1, p_full);
       }
-      const float m_new = fmaxf(m_run, m_tile * scale_log2);
-      const float alpha = fast_exp2(m_run - m_new);     // m_run = -inf on the first tile -> 0
-      float l_tile = 0.f;
-      // pass 2: probabilities -> bf16 -> swizzled shared memory
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t v[32];
-        tmem_ld_32x32b_x32(tmem_s + lane_off + c * 32, v);
-        tmem_ld_wait();
-        float p[32];
-#pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          float x = __uint_as_float(v[i]) * scale_log2 - m_new;
-          float e = fast_exp2(x);
-          if (diag && (c * 32 + i) > r) e = 0.f;
-          p[i] = e;
-          l_tile += e;
-        }
-#pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          uint4 w;
-          w.x = pack_bf16x2(p[g * 8 + 0], p[g * 8 + 1]);
-          w.y = pack_bf16x2(p[g * 8 + 2], p[g * 8 + 3]);
-          w.z = pack_bf16x2(p[g * 8 + 4], p[g * 8 + 5]);
-          w.w = pack_bf16x2(p[g * 8 + 6], p[g * 8 + 7]);
-          st_swizzled_16B(sp, r, c * 32 + g * 8, w);
-        }
-      }
-      l_run = l_run * alpha + l_tile;
-      m_run = m_new;
-#pragma unroll
-      for (int i = 0; i < HD; ++i) o_acc[i] *= alpha;
-      tc_fence_before();
-      fence_proxy_async_smem();     // generic-proxy smem writes -> visible to the tensor core
-      __syncwarp();
-      if (lane == 0) mbar_arrive(p_full);
-      // O += P V
-      mbar_wait(o_full, j & 1);
+      mbar_wait(s_full, g & 1);     // the diagonal tile: the only one that needs the causal mask
       tc_fence_after();
+      fwd_softmax_step<true>(tmem_s + lane_off, tmem_o + lane_off, sp, r, lane, scale_log2, w.qt == 0, m_used, l_run,
+                             s_free, o_full, (g - 1) & 1, p_full);
+      mbar_wait(o_full, g & 1);     // last P V of the item
+      tc_fence_after();
+      ++g;
+      const float inv = 1.0f / l_run;
+      const size_t grow = static_cast<size_t>(w.b) * seq + w.qt * BQ + r;
+      __nv_bfloat16* op = out + (grow * heads + w.h) * HD;
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
-        uint32_t v[32];
-        tmem_ld_32x32b_x32(tmem_o + lane_off + c * 32, v);
+        uint32_t o[32];
+        tmem_ld_32x32b_x32(tmem_o + lane_off + c * 32, o);
         tmem_ld_wait();
 #pragma unroll
-        for (int i = 0; i < 32; ++i) o_acc[c * 32 + i] += __uint_as_float(v[i]);
+        for (int q = 0; q < 4; ++q) {
+          uint4 wv;
+          wv.x = pack_bf16x2(__uint_as_float(o[q * 8 + 0]) * inv, __uint_as_float(o[q * 8 + 1]) * inv);
+          wv.y = pack_bf16x2(__uint_as_float(o[q * 8 + 2]) * inv, __uint_as_float(o[q * 8 + 3]) * inv);
+          wv.z = pack_bf16x2(__uint_as_float(o[q * 8 + 4]) * inv, __uint_as_float(o[q * 8 + 5]) * inv);
+          wv.w = pack_bf16x2(__uint_as_float(o[q * 8 + 6]) * inv, __uint_as_float(o[q * 8 + 7]) * inv);
+          reinterpret_cast<uint4*>(op)[c * 4 + q] = wv;
+        }
       }
+      tc_fence_before();            // O reads done before the next item's first P V (ordered by p_full)
+      lse[(static_cast<size_t>(w.b) * heads + w.h) * seq + w.qt * BQ + r] = m_used + __log2f(l_run);
     }
-    const float inv = 1.0f / l_run;
-    const size_t grow = static_cast<size_t>(row0 + qt * BQ + r);
-    __nv_bfloat16* op = out + (grow * heads + h) * HD;
-#pragma unroll
-    for (int g = 0; g < HD / 8; ++g) {
-      uint4 w;
-      w.x = pack_bf16x2(o_acc[g * 8 + 0] * inv, o_acc[g * 8 + 1] * inv);
-      w.y = pack_bf16x2(o_acc[g * 8 + 2] * inv, o_acc[g * 8 + 3] * inv);
-      w.z = pack_bf16x2(o_acc[g * 8 + 4] * inv, o_acc[g * 8 + 5] * inv);
-      w.w = pack_bf16x2(o_acc[g * 8 + 6] * inv, o_acc[g * 8 + 7] * inv);
-      reinterpret_cast<uint4*>(op)[g] = w;
-    }
-    lse[(static_cast<size_t>(b) * heads + h) * seq + qt * BQ + r] = m_run + __log2f(l_run);
   }
   tc_fence_before();
   __syncthreads();
@@ -241,42 +361,70 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* 
 // =============================================================================================
 // backward
 // =============================================================================================
-// delta[b,h,t] = sum_d dO*O ; dq_accum zeroed. One warp per (b,t,h) row of 64.
-__global__ void attention_bwd_prep_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ d_o,
-                                          float* __restrict__ delta, float* __restrict__ dq_accum, int batch, int seq,
-                                          int heads) {
+// delta[b,h,t] = sum_d dO*O ; dq_accum zeroed. 8 lanes per (b,t,h) row of 64, 16-byte loads/stores.
+__global__ void __launch_bounds__(256)
+attention_bwd_prep_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ d_o,
+                          float* __restrict__ delta, float* __restrict__ dq_accum, int batch, int seq, int heads) {
   pdl_sync();
-  const int lane = threadIdx.x & 31;
-  const int64_t rows = static_cast<int64_t>(batch) * seq * heads;
-  for (int64_t row = static_cast<int64_t>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5); row < rows;
-       row += static_cast<int64_t>(gridDim.x) * (blockDim.x >> 5)) {
-    const __nv_bfloat162 a = reinterpret_cast<const __nv_bfloat162*>(o + row * HD)[lane];
-    const __nv_bfloat162 g = reinterpret_cast<const __nv_bfloat162*>(d_o + row * HD)[lane];
-    float s = __bfloat162float(a.x) * __bfloat162float(g.x) + __bfloat162float(a.y) * __bfloat162float(g.y);
-    s = warp_sum(s);
-    reinterpret_cast<float2*>(dq_accum + row * HD)[lane] = make_float2(0.f, 0.f);
-    if (lane == 0) {
-      const int64_t bt = row / heads;
-      const int hh = static_cast<int>(row - bt * heads);
-      const int64_t bb = bt / seq;
-      const int t = static_cast<int>(bt - bb * seq);
-      delta[(bb * heads + hh) * seq + t] = s;
+  const uint32_t rows = static_cast<uint32_t>(batch) * seq * heads;
+  const uint32_t total = rows * 8u;                      // uint4 chunks (host checks rows < 2^28)
+  const uint32_t useq = seq, uheads = heads;
+  // warp-uniform trip count: the shuffles below need all 32 lanes
+  for (uint32_t base = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u; base < total; base += gridDim.x * blockDim.x) {
+    const uint32_t i = base + (threadIdx.x & 31u);
+    float s = 0.f;
+    const bool live = i < total;
+    if (live) {
+      const uint4 a = reinterpret_cast<const uint4*>(o)[i];
+      const uint4 g = reinterpret_cast<const uint4*>(d_o)[i];
+      const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, gw[4] = {g.x, g.y, g.z, g.w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float2 af = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&aw[k]));
+        const float2 gf = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&gw[k]));
+        s = fmaf(af.x, gf.x, fmaf(af.y, gf.y, s));
+      }
+      float4* z = reinterpret_cast<float4*>(dq_accum) + static_cast<size_t>(i) * 2;
+      z[0] = make_float4(0.f, 0.f, 0.f, 0.f);
+      z[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    s += __shfl_xor_sync(0xffffffffu, s, 1);
+    s += __shfl_xor_sync(0xffffffffu, s, 2);
+    s += __shfl_xor_sync(0xffffffffu, s, 4);
+    if (live && (i & 7u) == 0) {
+      const uint32_t row = i >> 3;
+      const uint32_t bt = row / uheads, hh = row - bt * uheads;
+      const uint32_t bb = bt / useq, t = bt - bb * useq;
+      delta[(static_cast<size_t>(bb) * uheads + hh) * useq + t] = s;
     }
   }
 }
 
-// dq bf16 <- dq_accum fp32, written into dqkv[..., 0, h, :]
-__global__ void attention_bwd_post_kernel(const float* __restrict__ dq_accum, __nv_bfloat16* __restrict__ dqkv,
-                                          int64_t rows_bt, int heads) {
+// dq bf16 <- dq_accum fp32, written into dqkv[..., 0, h, :]; 8 values per thread.
+// dq_accum is tile-major: [(b*heads + h)*nq + q tile][128 rows][64] fp32, and within a row the
+// sixteen 16-byte chunks are stored at position chunk ^ (row & 15) (the layout the backward kernel
+// stages in shared memory so that its bulk reduce-add is one contiguous 32 KB transfer).
+__global__ void __launch_bounds__(256)
+attention_bwd_post_kernel(const float* __restrict__ dq_accum, __nv_bfloat16* __restrict__ dqkv, int batch, int seq,
+                          int heads) {
   pdl_sync();
-  const int64_t total = rows_bt * heads * (HD / 2);
-  const int C = heads * HD;
-  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
-       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
-    const int64_t bt = i / (C / 2);
-    const int c2 = static_cast<int>(i - bt * (C / 2));
-    const float2 v = reinterpret_cast<const float2*>(dq_accum)[i];
-    reinterpret_cast<__nv_bfloat162*>(dqkv + bt * 3 * C)[c2] = __floats2bfloat162_rn(v.x, v.y);
+  const uint32_t uheads = heads, useq = seq, nq = useq / BQ;
+  const uint32_t total = static_cast<uint32_t>(batch) * useq * uheads * 8u;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const uint32_t c8 = i & 7u;
+    const uint32_t rh = i >> 3;
+    const uint32_t bt = rh / uheads, hh = rh - bt * uheads;
+    const uint32_t bb = bt / useq, t = bt - bb * useq;
+    const uint32_t qi = t / BQ, r = t - qi * BQ;
+    const float* src = dq_accum + (static_cast<size_t>((bb * uheads + hh) * nq + qi) * BQ + r) * HD;
+    const float4 v0 = *reinterpret_cast<const float4*>(src + (((2 * c8) ^ (r & 15u)) << 2));
+    const float4 v1 = *reinterpret_cast<const float4*>(src + (((2 * c8 + 1) ^ (r & 15u)) << 2));
+    uint4 w;
+    w.x = pack_bf16x2(v0.x, v0.y);
+    w.y = pack_bf16x2(v0.z, v0.w);
+    w.z = pack_bf16x2(v1.x, v1.y);
+    w.w = pack_bf16x2(v1.z, v1.w);
+    *reinterpret_cast<uint4*>(dqkv + static_cast<size_t>(bt) * 3 * uheads * HD + hh * HD + c8 * 8) = w;
   }
 }
 
@@ -287,24 +435,91 @@ struct AttnBwdSmem {
   static constexpr int DO0 = Q0 + 2 * TILE_BYTES;        // 2 stages
   static constexpr int P = DO0 + 2 * TILE_BYTES;         // 2 tiles
   static constexpr int DS = P + 2 * TILE_BYTES;          // 2 tiles
-  static constexpr int BAR = DS + 2 * TILE_BYTES;
-  static constexpr int BYTES = BAR + 128 + 1024;
+  static constexpr int DQ = DS + 2 * TILE_BYTES;         // fp32 [128][64] staging for the bulk reduce-add
+  static constexpr int BAR = DQ + 2 * TILE_BYTES;
+  static constexpr int BYTES = BAR + 128;                // 1024-aligned base required (checked in the kernel)
 };
+static_assert(AttnBwdSmem::BYTES + 1024 <= 232448, "backward attention: shared memory budget");
 
-__global__ void __launch_bounds__(ATT_THREADS, 1)
+__device__ __forceinline__ void named_barrier_sync(int id, int threads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
+
+// One q tile of the backward math for this warp's 64 columns (`half`) of row r:
+//   P = exp2(S * scale_log2 - lse), dS = P * (dP - delta) * scale
+// S and dP are pulled out of TMEM in one go (then released to the MMA warp through `sdp_free`), the
+// results are kept packed in registers until the previous tile's MMAs have stopped reading the
+// P / dS shared-memory operands (`prev_mma_done`), and only then stored.
+template <bool DIAG>
+__device__ __forceinline__ void bwd_math_tile(uint32_t tm_s, uint32_t tm_dp, int half, int r, int lane, float lse_r,
+                                              float dls, float scale, float scale_log2, uint8_t* sp, uint8_t* sds,
+                                              uint64_t* sdp_free, uint64_t* prev_mma_done, uint32_t prev_parity,
+                                              bool wait_prev) {
+  uint32_t sv_[2][32], dv_[2][32];
+#pragma unroll
+  for (int c = 0; c < 2; ++c) {
+    tmem_ld_32x32b_x32(tm_s + half * 64 + c * 32, sv_[c]);
+    tmem_ld_32x32b_x32(tm_dp + half * 64 + c * 32, dv_[c]);
+  }
+  tmem_ld_wait();
+  tc_fence_before();
+  __syncwarp();
+  if (lane == 0) mbar_arrive(sdp_free);     // S / dP accumulators may be overwritten by the next q tile
+  uint32_t pp[2][16], dd[2][16];
+#pragma unroll
+  for (int c = 0; c < 2; ++c)
+#pragma unroll
+    for (int i = 0; i < 32; i += 2) {
+      float e0 = fast_exp2(fmaf(__uint_as_float(sv_[c][i]), scale_log2, -lse_r));
+      float e1 = fast_exp2(fmaf(__uint_as_float(sv_[c][i + 1]), scale_log2, -lse_r));
+      if (DIAG && (half * 64 + c * 32 + i) > r) e0 = 0.f;
+      if (DIAG && (half * 64 + c * 32 + i + 1) > r) e1 = 0.f;
+      const float d0 = e0 * fmaf(__uint_as_float(dv_[c][i]), scale, -dls);
+      const float d1 = e1 * fmaf(__uint_as_float(dv_[c][i + 1]), scale, -dls);
+      pp[c][i >> 1] = pack_bf16x2(e0, e1);
+      dd[c][i >> 1] = pack_bf16x2(d0, d1);
+    }
+  if (wait_prev) {
+    mbar_wait(prev_mma_done, prev_parity);
+    tc_fence_after();
+  }
+#pragma unroll
+  for (int c = 0; c < 2; ++c)
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      st_swizzled_16B(sp, r, half * 64 + c * 32 + g * 8,
+                      make_uint4(pp[c][g * 4 + 0], pp[c][g * 4 + 1], pp[c][g * 4 + 2], pp[c][g * 4 + 3]));
+      st_swizzled_16B(sds, r, half * 64 + c * 32 + g * 8,
+                      make_uint4(dd[c][g * 4 + 0], dd[c][g * 4 + 1], dd[c][g * 4 + 2], dd[c][g * 4 + 3]));
+    }
+}
+
+// One CTA per (kv tile, head, sequence), looping over the q tiles jt..nq-1:
+//   tensor pipe :  S,dP(0) | S,dP(1)  dV,dK,dQ(0) | S,dP(2)  dV,dK,dQ(1) | ...
+//   math warps  :          | P,dS(0)              | P,dS(1)  dQ(0) out   | P,dS(2)  dQ(1) out ...
+// S/dP(i+1) are issued as soon as the math warps hold S/dP(i) in registers, so they run under the
+// exponentials; dV/dK/dQ(i) run under the math of tile i+1. dQ tiles leave through shared memory
+// with one bulk reduce-add (cp.reduce.async.bulk ... add.f32) per tile into the fp32 accumulator
+// that the CTAs of the other kv tiles add to as well.
+__global__ void __launch_bounds__(ATT_BWD_THREADS, 1)
 attention_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_do,
                      const float* __restrict__ lse, const float* __restrict__ delta, float* __restrict__ dq_accum,
                      __nv_bfloat16* __restrict__ dqkv, int seq, int heads, float scale, float scale_log2) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;
+  if ((smem_u32(smem) & 1023u) != 0) {
+    if (threadIdx.x == 0) printf("b200: attention_bwd shared memory base is not 1024-byte aligned\n");
+    __trap();
+  }
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + AttnBwdSmem::BAR);
   uint64_t* kv_full = bars + 0;
   uint64_t* qdo_full = bars + 1;   // [2]
   uint64_t* qdo_empty = bars + 3;  // [2]
   uint64_t* sdp_full = bars + 5;
-  uint64_t* pds_full = bars + 6;
-  uint64_t* dq_full = bars + 7;
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 8);
+  uint64_t* sdp_free = bars + 6;
+  uint64_t* pds_full = bars + 7;
+  uint64_t* dq_full = bars + 8;    // [2]
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 10);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nq = seq / BQ;
@@ -318,10 +533,14 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_co
     tma_prefetch_desc(&tm_qkv);
     tma_prefetch_desc(&tm_do);
     mbar_init(kv_full, 1);
-    for (int s = 0; s < 2; ++s) { mbar_init(&qdo_full[s], 1); mbar_init(&qdo_empty[s], 1); }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&qdo_full[s], 1);
+      mbar_init(&qdo_empty[s], 1);
+      mbar_init(&dq_full[s], 1);
+    }
     mbar_init(sdp_full, 1);
-    mbar_init(pds_full, 4);
-    mbar_init(dq_full, 1);
+    mbar_init(sdp_free, 8);
+    mbar_init(pds_full, 8);
     mbar_fence_init();
   }
   if (warp == 1) tmem_alloc<512>(tmem_ptr);
@@ -331,10 +550,10 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_co
   const uint32_t tmem_base = *tmem_ptr;
   pdl_sync();
   const uint32_t tm_s = tmem_base, tm_dp = tmem_base + 128, tm_dv = tmem_base + 256, tm_dk = tmem_base + 320,
-                 tm_dq = tmem_base + 384;
+                 tm_dq = tmem_base + 384;     // two 64-column dQ buffers: 384, 448
 
   if (warp == 0) {
-    if (lane == 0) {
+    if (elect_one()) {
       mbar_expect_tx(kv_full, 2 * TILE_BYTES);
       tma_load_2d(smem + AttnBwdSmem::K, &tm_qkv, kv_full, C + h * HD, row0 + jt * BKV);
       tma_load_2d(smem + AttnBwdSmem::V, &tm_qkv, kv_full, 2 * C + h * HD, row0 + jt * BKV);
@@ -353,14 +572,12 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_co
     constexpr uint32_t id_q = umma_idesc_bf16(128, 64, 0, 1);     // dQ = dS K
     const uint32_t sk = smem_u32(smem + AttnBwdSmem::K), sv = smem_u32(smem + AttnBwdSmem::V);
     const uint32_t sp = smem_u32(smem + AttnBwdSmem::P), sds = smem_u32(smem + AttnBwdSmem::DS);
-    mbar_wait(kv_full, 0);
-    for (int it = 0; it < niter; ++it) {
-      const int s = it & 1;
-      const uint32_t sq = smem_u32(smem + AttnBwdSmem::Q0 + s * TILE_BYTES);
-      const uint32_t sdo = smem_u32(smem + AttnBwdSmem::DO0 + s * TILE_BYTES);
-      mbar_wait(&qdo_full[s], (it >> 1) & 1);
+    auto issue_sdp = [&](int it) {      // S and dP of q tile `it`
+      const uint32_t sq = smem_u32(smem + AttnBwdSmem::Q0 + (it & 1) * TILE_BYTES);
+      const uint32_t sdo = smem_u32(smem + AttnBwdSmem::DO0 + (it & 1) * TILE_BYTES);
+      mbar_wait(&qdo_full[it & 1], (it >> 1) & 1);
       tc_fence_after();
-      if (lane == 0) {
+      if (elect_one()) {
 #pragma unroll
         for (int k = 0; k < HD / 16; ++k) umma_bf16(tm_s, kdesc(sq + k * 32), kdesc(sk + k * 32), id_s, k ? 1u : 0u);
 #pragma unroll
@@ -368,9 +585,20 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_co
         umma_commit(sdp_full);
       }
       __syncwarp();
-      mbar_wait(pds_full, it & 1);
+    };
+    mbar_wait(kv_full, 0);
+    issue_sdp(0);
+    for (int it = 0; it < niter; ++it) {
+      const int s = it & 1;
+      const uint32_t sq = smem_u32(smem + AttnBwdSmem::Q0 + s * TILE_BYTES);
+      const uint32_t sdo = smem_u32(smem + AttnBwdSmem::DO0 + s * TILE_BYTES);
+      if (it + 1 < niter) {
+        mbar_wait(sdp_free, it & 1);      // S/dP(it) are in the math warps' registers
+        issue_sdp(it + 1);
+      }
+      mbar_wait(pds_full, it & 1);        // P/dS(it) in shared memory
       tc_fence_after();
-      if (lane == 0) {
+      if (elect_one()) {
         // contraction over the 128 query rows of this tile, 16 at a time
 #pragma unroll
         for (int k = 0; k < BQ / 16; ++k) {
@@ -381,81 +609,82 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_co
         // dQ tile: contraction over the 128 kv rows
 #pragma unroll
         for (int k = 0; k < BKV / 16; ++k)
-          umma_bf16(tm_dq, kdesc(sds + (k >> 2) * TILE_BYTES + (k & 3) * 32), mndesc(sk + k * 2048, TILE_BYTES), id_q,
-                    k ? 1u : 0u);
-        umma_commit(dq_full);
+          umma_bf16(tm_dq + s * 64, kdesc(sds + (k >> 2) * TILE_BYTES + (k & 3) * 32), mndesc(sk + k * 2048, TILE_BYTES),
+                    id_q, k ? 1u : 0u);
+        umma_commit(&dq_full[s]);
         umma_commit(&qdo_empty[s]);
       }
       __syncwarp();
     }
   } else {
     const int quad = warp & 3;
+    const int half = (warp - 2) >> 2;     // columns [64*half, +64) of S / dP, [32*half, +32) of dQ / dK / dV
     const int r = quad * 32 + lane;
     const uint32_t lane_off = static_cast<uint32_t>(quad * 32) << 16;
+    const bool issuer = (threadIdx.x == 64);      // first math thread issues the bulk reduce-adds
     uint8_t* sp = smem + AttnBwdSmem::P;
     uint8_t* sds = smem + AttnBwdSmem::DS;
+    float* sdq = reinterpret_cast<float*>(smem + AttnBwdSmem::DQ);
+    const size_t stat0 = (static_cast<size_t>(b) * heads + h) * seq + r;
+    float lse_r = lse[stat0 + jt * BQ];
+    float dls = delta[stat0 + jt * BQ] * scale;
+    // dQ tile `it` (complete in TMEM once dq_full[it&1] has fired): TMEM -> swizzled fp32 staging ->
+    // one 32 KB bulk reduce-add into the accumulator tile of (b, h, q tile jt+it)
+    auto flush_dq = [&](int it) {
+      uint32_t v[32];
+      tmem_ld_32x32b_x32(tm_dq + (it & 1) * 64 + lane_off + half * 32, v);
+      tmem_ld_wait();
+      if (issuer) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // staging no longer read
+      named_barrier_sync(1, 256);
+#pragma unroll
+      for (int q = 0; q < 8; ++q)
+        *reinterpret_cast<uint4*>(sdq + r * HD + (((half * 8 + q) ^ (r & 15)) << 2)) =
+            make_uint4(v[q * 4 + 0], v[q * 4 + 1], v[q * 4 + 2], v[q * 4 + 3]);
+      fence_proxy_async_smem();
+      named_barrier_sync(2, 256);
+      if (issuer) {
+        float* dst = dq_accum + (static_cast<size_t>((b * heads + h) * nq + jt + it)) * (BQ * HD);
+        asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], %2;" ::"l"(dst),
+                     "r"(smem_u32(sdq)), "r"(BQ * HD * 4)
+                     : "memory");
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      }
+    };
     for (int it = 0; it < niter; ++it) {
-      const int qi = jt + it;
-      const bool diag = (qi == jt);
-      const size_t stat = (static_cast<size_t>(b) * heads + h) * seq + qi * BQ + r;
-      const float lse_r = lse[stat];
-      const float dl_r = delta[stat];
+      // row statistics of the next q tile: in flight while this one is processed
+      float lse_n = 0.f, dls_n = 0.f;
+      if (it + 1 < niter) {
+        lse_n = lse[stat0 + (jt + it + 1) * BQ];
+        dls_n = delta[stat0 + (jt + it + 1) * BQ] * scale;
+      }
       mbar_wait(sdp_full, it & 1);
       tc_fence_after();
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t sv_[32], dv_[32];
-        tmem_ld_32x32b_x32(tm_s + lane_off + c * 32, sv_);
-        tmem_ld_32x32b_x32(tm_dp + lane_off + c * 32, dv_);
-        tmem_ld_wait();
-        float p[32], ds[32];
-#pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          float e = fast_exp2(__uint_as_float(sv_[i]) * scale_log2 - lse_r);
-          if (diag && (c * 32 + i) > r) e = 0.f;
-          p[i] = e;
-          ds[i] = e * (__uint_as_float(dv_[i]) - dl_r) * scale;
-        }
-#pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          uint4 w, u;
-          w.x = pack_bf16x2(p[g * 8 + 0], p[g * 8 + 1]);   w.y = pack_bf16x2(p[g * 8 + 2], p[g * 8 + 3]);
-          w.z = pack_bf16x2(p[g * 8 + 4], p[g * 8 + 5]);   w.w = pack_bf16x2(p[g * 8 + 6], p[g * 8 + 7]);
-          u.x = pack_bf16x2(ds[g * 8 + 0], ds[g * 8 + 1]); u.y = pack_bf16x2(ds[g * 8 + 2], ds[g * 8 + 3]);
-          u.z = pack_bf16x2(ds[g * 8 + 4], ds[g * 8 + 5]); u.w = pack_bf16x2(ds[g * 8 + 6], ds[g * 8 + 7]);
-          st_swizzled_16B(sp, r, c * 32 + g * 8, w);
-          st_swizzled_16B(sds, r, c * 32 + g * 8, u);
-        }
-      }
+      // the diagonal tile (q tile == kv tile, it == 0) is the only one that needs the causal mask
+      if (it == 0)
+        bwd_math_tile<true>(tm_s + lane_off, tm_dp + lane_off, half, r, lane, lse_r, dls, scale, scale_log2, sp, sds,
+                            sdp_free, nullptr, 0, false);
+      else
+        bwd_math_tile<false>(tm_s + lane_off, tm_dp + lane_off, half, r, lane, lse_r, dls, scale, scale_log2, sp, sds,
+                             sdp_free, &dq_full[(it - 1) & 1], ((it - 1) >> 1) & 1, true);
       tc_fence_before();
       fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) mbar_arrive(pds_full);
-      // dQ tile -> fp32 accumulation buffer (other kv tiles add into the same rows)
-      mbar_wait(dq_full, it & 1);
-      tc_fence_after();
-      float* dqp = dq_accum + ((static_cast<size_t>(row0 + qi * BQ + r)) * heads + h) * HD;
-#pragma unroll
-      for (int c = 0; c < 2; ++c) {
-        uint32_t v[32];
-        tmem_ld_32x32b_x32(tm_dq + lane_off + c * 32, v);
-        tmem_ld_wait();
-#pragma unroll
-        for (int i = 0; i < 32; i += 4)
-          asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(dqp + c * 32 + i), "f"(__uint_as_float(v[i])),
-                       "f"(__uint_as_float(v[i + 1])), "f"(__uint_as_float(v[i + 2])), "f"(__uint_as_float(v[i + 3]))
-                       : "memory");
-      }
+      if (it > 0) flush_dq(it - 1);       // dq_full of tile it-1 was observed inside bwd_math_tile
+      lse_r = lse_n;
+      dls = dls_n;
     }
+    mbar_wait(&dq_full[(niter - 1) & 1], ((niter - 1) >> 1) & 1);
+    tc_fence_after();
+    flush_dq(niter - 1);
     // dK, dV of this kv tile (the last dq_full commit covers every MMA issued before it)
     const size_t grow = static_cast<size_t>(row0 + jt * BKV + r);
-    __nv_bfloat16* dkp = dqkv + grow * 3 * C + C + h * HD;
-    __nv_bfloat16* dvp = dqkv + grow * 3 * C + 2 * C + h * HD;
-#pragma unroll
-    for (int c = 0; c < 2; ++c) {
+    __nv_bfloat16* dkp = dqkv + grow * 3 * C + C + h * HD + half * 32;
+    __nv_bfloat16* dvp = dqkv + grow * 3 * C + 2 * C + h * HD + half * 32;
+    {
       uint32_t a[32], bb[32];
-      tmem_ld_32x32b_x32(tm_dk + lane_off + c * 32, a);
-      tmem_ld_32x32b_x32(tm_dv + lane_off + c * 32, bb);
+      tmem_ld_32x32b_x32(tm_dk + lane_off + half * 32, a);
+      tmem_ld_32x32b_x32(tm_dv + lane_off + half * 32, bb);
       tmem_ld_wait();
 #pragma unroll
       for (int g = 0; g < 4; ++g) {
@@ -468,10 +697,11 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_co
         u.y = pack_bf16x2(__uint_as_float(bb[g * 8 + 2]), __uint_as_float(bb[g * 8 + 3]));
         u.z = pack_bf16x2(__uint_as_float(bb[g * 8 + 4]), __uint_as_float(bb[g * 8 + 5]));
         u.w = pack_bf16x2(__uint_as_float(bb[g * 8 + 6]), __uint_as_float(bb[g * 8 + 7]));
-        reinterpret_cast<uint4*>(dkp)[c * 4 + g] = w;
-        reinterpret_cast<uint4*>(dvp)[c * 4 + g] = u;
+        reinterpret_cast<uint4*>(dkp)[g] = w;
+        reinterpret_cast<uint4*>(dvp)[g] = u;
       }
     }
+    if (issuer) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");    // staging must outlive the last reduce
   }
   tc_fence_before();
   __syncthreads();
@@ -484,6 +714,8 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_co
 static int check_attn_args(int batch, int seq, int heads) {
   B200_REQUIRE(batch > 0 && heads > 0 && seq > 0 && seq % 128 == 0, "attention: seq=%d must be a positive multiple of 128", seq);
   B200_REQUIRE(batch <= 65535 && heads <= 65535, "attention: batch/heads too large for the grid");
+  B200_REQUIRE((long long)batch * seq * heads < (1ll << 28), "attention: batch*seq*heads=%lld exceeds the 2^28 row limit",
+               (long long)batch * seq * heads);
   return 0;
 }
 
@@ -505,9 +737,10 @@ extern "C" int b200_attention_fwd(const void* qkv, void* out, float* lse, int ba
     attr = true;
   }
   const float scale_log2 = 1.4426950408889634f / 8.0f;   // log2(e) / sqrt(64)
-  dim3 grid(seq / BQ, heads, batch);
-  B200_CUDA(launch_k(attention_fwd_kernel, dim3(grid), dim3(ATT_THREADS), AttnFwdSmem::BYTES, static_cast<cudaStream_t>(stream), 
-      tm, static_cast<__nv_bfloat16*>(out), lse, seq, heads, scale_log2));
+  const int n_items = (seq / BQ) * heads * batch;
+  const int grid = n_items < 2 * num_sms() ? n_items : 2 * num_sms();      // persistent, two CTAs per SM
+  B200_CUDA(launch_k(attention_fwd_kernel, dim3(grid), dim3(ATT_FWD_THREADS), AttnFwdSmem::BYTES, static_cast<cudaStream_t>(stream),
+      tm, static_cast<__nv_bfloat16*>(out), lse, seq, heads, batch, scale_log2));
   B200_CUDA(cudaGetLastError());
   return 0;
 }
@@ -537,20 +770,21 @@ extern "C" int b200_attention_bwd(const void* qkv, const void* out, const void* 
     B200_CUDA(cudaFuncSetAttribute(attention_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AttnBwdSmem::BYTES));
     attr = true;
   }
-  int pblocks = (int)((rows + 7) / 8);
-  if (pblocks > num_sms() * 16) pblocks = num_sms() * 16;
+  int pblocks = (int)((rows * 8 + 255) / 256);
+  if (pblocks > num_sms() * 8) pblocks = num_sms() * 8;
   B200_CUDA(launch_k(attention_bwd_prep_kernel, dim3(pblocks), dim3(256), 0, s, static_cast<const __nv_bfloat16*>(out),
                                                     static_cast<const __nv_bfloat16*>(dout), delta, dq_accum, batch, seq,
                                                     heads));
   const float scale = 0.125f, scale_log2 = 1.4426950408889634f / 8.0f;
   dim3 grid(seq / BKV, heads, batch);
-  B200_CUDA(launch_k(attention_bwd_kernel, dim3(grid), dim3(ATT_THREADS), AttnBwdSmem::BYTES, s, tm_qkv, tm_do, lse, delta, dq_accum,
+  B200_CUDA(launch_k(attention_bwd_kernel, dim3(grid), dim3(ATT_BWD_THREADS), AttnBwdSmem::BYTES, s, tm_qkv, tm_do, lse, delta, dq_accum,
                                                                     static_cast<__nv_bfloat16*>(dqkv), seq, heads, scale,
                                                                     scale_log2));
-  int64_t total = (int64_t)batch * seq * C / 2;
+  int64_t total = (int64_t)batch * seq * C / 8;
   int qblocks = (int)((total + 255) / 256);
-  if (qblocks > num_sms() * 16) qblocks = num_sms() * 16;
-  B200_CUDA(launch_k(attention_bwd_post_kernel, dim3(qblocks), dim3(256), 0, s, dq_accum, static_cast<__nv_bfloat16*>(dqkv), (int64_t)batch * seq, heads));
+  if (qblocks > num_sms() * 8) qblocks = num_sms() * 8;
+  B200_CUDA(launch_k(attention_bwd_post_kernel, dim3(qblocks), dim3(256), 0, s, static_cast<const float*>(dq_accum),
+                     static_cast<__nv_bfloat16*>(dqkv), batch, seq, heads));
   B200_CUDA(cudaGetLastError());
   return 0;
 }

@@ -470,7 +470,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
 
   if (warp == 0) {
     // ===================== TMA producer =====================
-    if (lane == 0) {
+    if (elect_one()) {   // elect.sync keeps the issue code on the uniform datapath
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
@@ -539,7 +539,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
       for (int it = it_begin; it < it_end; ++it) {
         mbar_wait(&full_bar[stage], phase);
         tc_fence_after();
-        if (lane == 0) {
+        if (elect_one()) {   // elect.sync keeps the issue code on the uniform datapath
           const uint32_t sa = smem_u32(smem + stage * Cfg::STAGE_BYTES);
           const uint32_t sb = sa + Cfg::A_BYTES;
 #pragma unroll
@@ -713,7 +713,7 @@ gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
 
   if (warp == 0) {
     // ===================== TMA producer (both CTAs) =====================
-    if (lane == 0) {
+    if (elect_one()) {   // elect.sync keeps the issue code on the uniform datapath
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
@@ -783,7 +783,7 @@ gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
         for (int it = it_begin; it < it_end; ++it) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
-          if (lane == 0) {
+          if (elect_one()) {   // elect.sync keeps the issue code on the uniform datapath
             const uint32_t sa = smem_u32(smem + stage * Cfg::STAGE_BYTES);
             const uint32_t sb = sa + Cfg::A_BYTES;
 #pragma unroll

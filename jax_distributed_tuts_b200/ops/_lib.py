@@ -6,6 +6,8 @@ The library is loaded lazily. On a machine with a GPU a missing or stale library
 from __future__ import annotations
 
 import ctypes as C
+import os
+from pathlib import Path
 from typing import Optional
 
 from . import _build
@@ -140,7 +142,7 @@ def lib() -> C.CDLL:
     global _lib
     if _lib is not None:
         return _lib
-    path = _build.LIB_PATH
+    path = Path(os.environ["B200DIST_LIB"]) if os.environ.get("B200DIST_LIB") else _build.LIB_PATH   # override: A/B builds
     if not path.exists():
         raise B200Error(
             f"{path} is missing: build the CUDA library first "

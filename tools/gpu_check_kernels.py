@@ -380,6 +380,42 @@ def group_attention():
         K.attention_bwd(qkv, out, dout, lse, dqkv, scratch, b, t, h)
         for i, (nm, gref) in enumerate((("dq", q.grad), ("dk", k.grad), ("dv", v.grad))):
             ok &= _report(f"attention {nm}", _rel_err(dqkv[:, :, i].permute(0, 2, 1, 3), gref), 2e-2)
+    # timing at the GPT-2 small bench shape (per layer): 8 and 16 sequences of 1024, 12 heads
+    for b in (8, 16):
+        t, h = 1024, 12
+        qkv = torch.randn(b, t, 3, h, 64, device="cuda").bfloat16()
+        out = torch.empty(b, t, h, 64, device="cuda", dtype=torch.bfloat16)
+        dout = torch.randn_like(out)
+        lse = torch.empty(b, h, t, device="cuda")
+        dqkv = torch.empty_like(qkv)
+        scratch = torch.empty(K.attention_bwd_scratch_numel(b, t, h), device="cuda")
+        flops = 2 * 2 * b * h * t * t * 64 / 2      # causal: half of the score matrix
+        for name, fn, mult in (("fwd", lambda: K.attention_fwd(qkv, out, lse, b, t, h), 1.0),
+                               ("bwd", lambda: K.attention_bwd(qkv, out, dout, lse, dqkv, scratch, b, t, h), 2.5)):
+            for _ in range(3):
+                fn()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize()
+            e0.record()
+            for _ in range(20):
+                fn()
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / 20
+            print(f"  attention {name} b={b}: {ms * 1e3:.1f} us  {flops * mult / ms / 1e9:.0f} TFLOP/s (causal flops)")
+    # per-kernel device times (CUPTI through torch.profiler), b=16
+    try:
+        from torch.profiler import ProfilerActivity, profile
+        with profile(activities=[ProfilerActivity.CUDA]) as prof:
+            for _ in range(5):
+                K.attention_fwd(qkv, out, lse, b, t, h)
+                K.attention_bwd(qkv, out, dout, lse, dqkv, scratch, b, t, h)
+            torch.cuda.synchronize()
+        for ev in prof.key_averages():
+            if "attention" in ev.key:
+                print(f"    {ev.key[:60]:60s} {ev.device_time_total / max(ev.count, 1):8.1f} us x{ev.count}")
+    except Exception as e:     # profiler availability is not part of the check
+        print("  (torch.profiler unavailable:", e, ")")
     return ok
 
 
