@@ -43,6 +43,10 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
   return *reinterpret_cast<uint32_t*>(&t);
 }
 
+__device__ __forceinline__ void named_barrier_sync(int id, int threads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
+
 __device__ __forceinline__ float fast_exp2(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -95,7 +99,7 @@ template <bool DIAG>
 __device__ __forceinline__ void fwd_softmax_step(uint32_t tmem_s_lane, uint32_t tmem_o_lane, uint8_t* sp, int r, int lane,
                                                  float scale_log2, bool first, float& m_used, float& l_run,
                                                  uint64_t* s_free, uint64_t* o_full, uint32_t o_prev_parity,
-                                                 uint64_t* p_full) {
+                                                 uint64_t* p_full, bool store_issuer) {
   // pass 1: row maximum, 32 columns at a time (few live registers: the O rescale below needs room)
   float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
@@ -158,6 +162,10 @@ __device__ __forceinline__ void fwd_softmax_step(uint32_t tmem_s_lane, uint32_t 
     mbar_wait(o_full, o_prev_parity);
     tc_fence_after();
   }
+  if (first) {                              // ... and so must the previous item's output tile (TMA store)
+    if (store_issuer) tma_store_wait_read<0>();
+    named_barrier_sync(2, 128);
+  }
 #pragma unroll
   for (int c = 0; c < 4; ++c)
 #pragma unroll
@@ -179,7 +187,7 @@ __device__ __forceinline__ void fwd_softmax_step(uint32_t tmem_s_lane, uint32_t 
 // O) keep running across item boundaries, so the next item's Q/K loads and first S = Q K^T are
 // in flight while the math warps finish the current item.
 __global__ void __launch_bounds__(ATT_FWD_THREADS, 2)
-attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* __restrict__ out,
+attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_out,
                      float* __restrict__ lse, int seq, int heads, int batch, float scale_log2) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw;
@@ -209,6 +217,7 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* 
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tm_qkv);
+    tma_prefetch_desc(&tm_out);
     mbar_init(q_full, 1);
     mbar_init(q_empty, 1);
     for (int s = 0; s < 2; ++s) {
@@ -308,6 +317,7 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* 
     const int quad = warp & 3;
     const int r = quad * 32 + lane;                 // row within the q tile
     const uint32_t lane_off = static_cast<uint32_t>(quad * 32) << 16;
+    const bool store_issuer = (threadIdx.x == 64);  // first math thread issues the output TMA stores
     uint8_t* sp = smem + AttnFwdSmem::P;
     int g = 0;
     for (int round = 0;; ++round) {
@@ -319,18 +329,17 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* 
         mbar_wait(s_full, g & 1);
         tc_fence_after();
         fwd_softmax_step<false>(tmem_s + lane_off, tmem_o + lane_off, sp, r, lane, scale_log2, j == 0, m_used, l_run,
-                                s_free, o_full, (g - 1) & 1, p_full);
+                                s_free, o_full, (g - 1) & 1, p_full, store_issuer);
       }
       mbar_wait(s_full, g & 1);     // the diagonal tile: the only one that needs the causal mask
       tc_fence_after();
       fwd_softmax_step<true>(tmem_s + lane_off, tmem_o + lane_off, sp, r, lane, scale_log2, w.qt == 0, m_used, l_run,
-                             s_free, o_full, (g - 1) & 1, p_full);
-      mbar_wait(o_full, g & 1);     // last P V of the item
+                             s_free, o_full, (g - 1) & 1, p_full, store_issuer);
+      mbar_wait(o_full, g & 1);     // last P V of the item: O complete, P buffer free
       tc_fence_after();
       ++g;
+      // O / l -> bf16 -> swizzled tile in the (idle) P buffer -> one TMA store
       const float inv = 1.0f / l_run;
-      const size_t grow = static_cast<size_t>(w.b) * seq + w.qt * BQ + r;
-      __nv_bfloat16* op = out + (grow * heads + w.h) * HD;
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
         uint32_t o[32];
@@ -343,12 +352,19 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* 
           wv.y = pack_bf16x2(__uint_as_float(o[q * 8 + 2]) * inv, __uint_as_float(o[q * 8 + 3]) * inv);
           wv.z = pack_bf16x2(__uint_as_float(o[q * 8 + 4]) * inv, __uint_as_float(o[q * 8 + 5]) * inv);
           wv.w = pack_bf16x2(__uint_as_float(o[q * 8 + 6]) * inv, __uint_as_float(o[q * 8 + 7]) * inv);
-          reinterpret_cast<uint4*>(op)[c * 4 + q] = wv;
+          st_swizzled_16B(sp, r, c * 32 + q * 8, wv);
         }
       }
       tc_fence_before();            // O reads done before the next item's first P V (ordered by p_full)
       lse[(static_cast<size_t>(w.b) * heads + w.h) * seq + w.qt * BQ + r] = m_used + __log2f(l_run);
+      fence_proxy_async_smem();
+      named_barrier_sync(1, 128);
+      if (store_issuer) {
+        tma_store_2d(&tm_out, sp, w.h * HD, w.b * seq + w.qt * BQ);
+        tma_store_commit();
+      }
     }
+    if (store_issuer) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   }
   tc_fence_before();
   __syncthreads();
@@ -429,9 +445,9 @@ attention_bwd_post_kernel(const float* __restrict__ dq_accum, __nv_bfloat16* __r
 }
 
 struct AttnBwdSmem {
-  static constexpr int K = 0;
-  static constexpr int V = K + TILE_BYTES;
-  static constexpr int Q0 = V + TILE_BYTES;              // 2 stages
+  static constexpr int K0 = 0;                           // 2 stages (items alternate)
+  static constexpr int V0 = K0 + 2 * TILE_BYTES;         // 2 stages
+  static constexpr int Q0 = V0 + 2 * TILE_BYTES;         // 2 stages
   static constexpr int DO0 = Q0 + 2 * TILE_BYTES;        // 2 stages
   static constexpr int P = DO0 + 2 * TILE_BYTES;         // 2 tiles
   static constexpr int DS = P + 2 * TILE_BYTES;          // 2 tiles
@@ -441,8 +457,18 @@ struct AttnBwdSmem {
 };
 static_assert(AttnBwdSmem::BYTES + 1024 <= 232448, "backward attention: shared memory budget");
 
-__device__ __forceinline__ void named_barrier_sync(int id, int threads) {
-  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
+// Work item = one (kv tile, head, sequence); kv tile jt meets q tiles jt..nq-1. Heavy-first
+// numbering and snake dealing as in the forward.
+struct BwdItem {
+  int jt, h, b;
+};
+__device__ __forceinline__ BwdItem bwd_item_decode(int item, int heads, int hb) {
+  BwdItem w;
+  w.jt = item / hb;
+  const int rem = item - w.jt * hb;
+  w.b = rem / heads;
+  w.h = rem - w.b * heads;
+  return w;
 }
 
 // One q tile of the backward math for this warp's 64 columns (`half`) of row r:
@@ -494,17 +520,19 @@ __device__ __forceinline__ void bwd_math_tile(uint32_t tm_s, uint32_t tm_dp, int
     }
 }
 
-// One CTA per (kv tile, head, sequence), looping over the q tiles jt..nq-1:
+// Persistent, one CTA per SM. Per item the q tiles jt..nq-1 are pipelined as
 //   tensor pipe :  S,dP(0) | S,dP(1)  dV,dK,dQ(0) | S,dP(2)  dV,dK,dQ(1) | ...
 //   math warps  :          | P,dS(0)              | P,dS(1)  dQ(0) out   | P,dS(2)  dQ(1) out ...
 // S/dP(i+1) are issued as soon as the math warps hold S/dP(i) in registers, so they run under the
 // exponentials; dV/dK/dQ(i) run under the math of tile i+1. dQ tiles leave through shared memory
 // with one bulk reduce-add (cp.reduce.async.bulk ... add.f32) per tile into the fp32 accumulator
-// that the CTAs of the other kv tiles add to as well.
+// that the CTAs of the other kv tiles add to as well. All pipelines run across item boundaries
+// (K/V double-buffered), so the next item's loads and first S,dP overlap the current item's tail.
 __global__ void __launch_bounds__(ATT_BWD_THREADS, 1)
 attention_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_do,
-                     const float* __restrict__ lse, const float* __restrict__ delta, float* __restrict__ dq_accum,
-                     __nv_bfloat16* __restrict__ dqkv, int seq, int heads, float scale, float scale_log2) {
+                     const __grid_constant__ CUtensorMap tm_dqkv, const float* __restrict__ lse,
+                     const float* __restrict__ delta, float* __restrict__ dq_accum, int seq, int heads, int batch,
+                     float scale, float scale_log2) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw;
   if ((smem_u32(smem) & 1023u) != 0) {
@@ -512,28 +540,30 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_co
     __trap();
   }
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + AttnBwdSmem::BAR);
-  uint64_t* kv_full = bars + 0;
-  uint64_t* qdo_full = bars + 1;   // [2]
-  uint64_t* qdo_empty = bars + 3;  // [2]
-  uint64_t* sdp_full = bars + 5;
-  uint64_t* sdp_free = bars + 6;
-  uint64_t* pds_full = bars + 7;
-  uint64_t* dq_full = bars + 8;    // [2]
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 10);
+  uint64_t* kv_full = bars + 0;    // [2]
+  uint64_t* kv_empty = bars + 2;   // [2]
+  uint64_t* qdo_full = bars + 4;   // [2]
+  uint64_t* qdo_empty = bars + 6;  // [2]
+  uint64_t* sdp_full = bars + 8;
+  uint64_t* sdp_free = bars + 9;
+  uint64_t* pds_full = bars + 10;
+  uint64_t* dq_full = bars + 11;   // [2]
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 13);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nq = seq / BQ;
-  const int jt = blockIdx.x;            // kv tile owned by this CTA (tile 0 has the most work)
-  const int h = blockIdx.y, b = blockIdx.z;
+  const int hb = heads * batch;
+  const int n_items = nq * hb;
+  const int n_cta = gridDim.x, cta = blockIdx.x;
   const int C = heads * HD;
-  const int row0 = b * seq;
-  const int niter = nq - jt;            // q tiles jt .. nq-1
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tm_qkv);
     tma_prefetch_desc(&tm_do);
-    mbar_init(kv_full, 1);
+    tma_prefetch_desc(&tm_dqkv);
     for (int s = 0; s < 2; ++s) {
+      mbar_init(&kv_full[s], 1);
+      mbar_init(&kv_empty[s], 1);
       mbar_init(&qdo_full[s], 1);
       mbar_init(&qdo_empty[s], 1);
       mbar_init(&dq_full[s], 1);
@@ -554,28 +584,37 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_co
 
   if (warp == 0) {
     if (elect_one()) {
-      mbar_expect_tx(kv_full, 2 * TILE_BYTES);
-      tma_load_2d(smem + AttnBwdSmem::K, &tm_qkv, kv_full, C + h * HD, row0 + jt * BKV);
-      tma_load_2d(smem + AttnBwdSmem::V, &tm_qkv, kv_full, 2 * C + h * HD, row0 + jt * BKV);
-      for (int it = 0; it < niter; ++it) {
-        const int s = it & 1;
-        const int qi = jt + it;
-        mbar_wait(&qdo_empty[s], ((it >> 1) & 1) ^ 1);
-        mbar_expect_tx(&qdo_full[s], 2 * TILE_BYTES);
-        tma_load_2d(smem + AttnBwdSmem::Q0 + s * TILE_BYTES, &tm_qkv, &qdo_full[s], h * HD, row0 + qi * BQ);
-        tma_load_2d(smem + AttnBwdSmem::DO0 + s * TILE_BYTES, &tm_do, &qdo_full[s], h * HD, row0 + qi * BQ);
+      int g = 0, n = 0;       // g: q-tile steps so far (all items), n: items so far
+      for (int round = 0;; ++round, ++n) {
+        const int item = fwd_item_index(round, n_cta, cta);
+        if (item >= n_items) break;
+        const BwdItem w = bwd_item_decode(item, heads, hb);
+        const int row0 = w.b * seq;
+        const int ks = n & 1;
+        mbar_wait(&kv_empty[ks], ((n >> 1) & 1) ^ 1);
+        mbar_expect_tx(&kv_full[ks], 2 * TILE_BYTES);
+        tma_load_2d(smem + AttnBwdSmem::K0 + ks * TILE_BYTES, &tm_qkv, &kv_full[ks], C + w.h * HD, row0 + w.jt * BKV);
+        tma_load_2d(smem + AttnBwdSmem::V0 + ks * TILE_BYTES, &tm_qkv, &kv_full[ks], 2 * C + w.h * HD, row0 + w.jt * BKV);
+        for (int qi = w.jt; qi < nq; ++qi, ++g) {
+          const int s = g & 1;
+          mbar_wait(&qdo_empty[s], ((g >> 1) & 1) ^ 1);
+          mbar_expect_tx(&qdo_full[s], 2 * TILE_BYTES);
+          tma_load_2d(smem + AttnBwdSmem::Q0 + s * TILE_BYTES, &tm_qkv, &qdo_full[s], w.h * HD, row0 + qi * BQ);
+          tma_load_2d(smem + AttnBwdSmem::DO0 + s * TILE_BYTES, &tm_do, &qdo_full[s], w.h * HD, row0 + qi * BQ);
+        }
       }
     }
   } else if (warp == 1) {
     constexpr uint32_t id_s = umma_idesc_bf16(128, 128, 0, 0);    // S = Q K^T, dP = dO V^T
     constexpr uint32_t id_t = umma_idesc_bf16(128, 64, 1, 1);     // dV = P^T dO, dK = dS^T Q
     constexpr uint32_t id_q = umma_idesc_bf16(128, 64, 0, 1);     // dQ = dS K
-    const uint32_t sk = smem_u32(smem + AttnBwdSmem::K), sv = smem_u32(smem + AttnBwdSmem::V);
     const uint32_t sp = smem_u32(smem + AttnBwdSmem::P), sds = smem_u32(smem + AttnBwdSmem::DS);
-    auto issue_sdp = [&](int it) {      // S and dP of q tile `it`
-      const uint32_t sq = smem_u32(smem + AttnBwdSmem::Q0 + (it & 1) * TILE_BYTES);
-      const uint32_t sdo = smem_u32(smem + AttnBwdSmem::DO0 + (it & 1) * TILE_BYTES);
-      mbar_wait(&qdo_full[it & 1], (it >> 1) & 1);
+    auto issue_sdp = [&](int g, int ks) {      // S and dP of step g against the K/V stage ks
+      const uint32_t sk = smem_u32(smem + AttnBwdSmem::K0 + ks * TILE_BYTES);
+      const uint32_t sv = smem_u32(smem + AttnBwdSmem::V0 + ks * TILE_BYTES);
+      const uint32_t sq = smem_u32(smem + AttnBwdSmem::Q0 + (g & 1) * TILE_BYTES);
+      const uint32_t sdo = smem_u32(smem + AttnBwdSmem::DO0 + (g & 1) * TILE_BYTES);
+      mbar_wait(&qdo_full[g & 1], (g >> 1) & 1);
       tc_fence_after();
       if (elect_one()) {
 #pragma unroll
@@ -586,35 +625,45 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_co
       }
       __syncwarp();
     };
-    mbar_wait(kv_full, 0);
-    issue_sdp(0);
-    for (int it = 0; it < niter; ++it) {
-      const int s = it & 1;
-      const uint32_t sq = smem_u32(smem + AttnBwdSmem::Q0 + s * TILE_BYTES);
-      const uint32_t sdo = smem_u32(smem + AttnBwdSmem::DO0 + s * TILE_BYTES);
-      if (it + 1 < niter) {
-        mbar_wait(sdp_free, it & 1);      // S/dP(it) are in the math warps' registers
-        issue_sdp(it + 1);
-      }
-      mbar_wait(pds_full, it & 1);        // P/dS(it) in shared memory
-      tc_fence_after();
-      if (elect_one()) {
-        // contraction over the 128 query rows of this tile, 16 at a time
-#pragma unroll
-        for (int k = 0; k < BQ / 16; ++k) {
-          const uint32_t acc = (it | k) ? 1u : 0u;
-          umma_bf16(tm_dv, mndesc(sp + k * 2048, TILE_BYTES), mndesc(sdo + k * 2048, TILE_BYTES), id_t, acc);
-          umma_bf16(tm_dk, mndesc(sds + k * 2048, TILE_BYTES), mndesc(sq + k * 2048, TILE_BYTES), id_t, acc);
+    int g = 0, n = 0;
+    for (int round = 0;; ++round, ++n) {
+      const int item = fwd_item_index(round, n_cta, cta);
+      if (item >= n_items) break;
+      const int niter = nq - item / hb;
+      const int ks = n & 1;
+      const uint32_t sk = smem_u32(smem + AttnBwdSmem::K0 + ks * TILE_BYTES);
+      mbar_wait(&kv_full[ks], (n >> 1) & 1);
+      if (g > 0) mbar_wait(sdp_free, (g - 1) & 1);     // the previous item's last S/dP have been read
+      issue_sdp(g, ks);
+      for (int it = 0; it < niter; ++it, ++g) {
+        const int s = g & 1;
+        const uint32_t sq = smem_u32(smem + AttnBwdSmem::Q0 + s * TILE_BYTES);
+        const uint32_t sdo = smem_u32(smem + AttnBwdSmem::DO0 + s * TILE_BYTES);
+        if (it + 1 < niter) {
+          mbar_wait(sdp_free, g & 1);       // S/dP(g) are in the math warps' registers
+          issue_sdp(g + 1, ks);
         }
-        // dQ tile: contraction over the 128 kv rows
+        mbar_wait(pds_full, g & 1);         // P/dS(g) in shared memory
+        tc_fence_after();
+        if (elect_one()) {
+          // contraction over the 128 query rows of this tile, 16 at a time
 #pragma unroll
-        for (int k = 0; k < BKV / 16; ++k)
-          umma_bf16(tm_dq + s * 64, kdesc(sds + (k >> 2) * TILE_BYTES + (k & 3) * 32), mndesc(sk + k * 2048, TILE_BYTES),
-                    id_q, k ? 1u : 0u);
-        umma_commit(&dq_full[s]);
-        umma_commit(&qdo_empty[s]);
+          for (int k = 0; k < BQ / 16; ++k) {
+            const uint32_t acc = (it | k) ? 1u : 0u;
+            umma_bf16(tm_dv, mndesc(sp + k * 2048, TILE_BYTES), mndesc(sdo + k * 2048, TILE_BYTES), id_t, acc);
+            umma_bf16(tm_dk, mndesc(sds + k * 2048, TILE_BYTES), mndesc(sq + k * 2048, TILE_BYTES), id_t, acc);
+          }
+          // dQ tile: contraction over the 128 kv rows
+#pragma unroll
+          for (int k = 0; k < BKV / 16; ++k)
+            umma_bf16(tm_dq + s * 64, kdesc(sds + (k >> 2) * TILE_BYTES + (k & 3) * 32), mndesc(sk + k * 2048, TILE_BYTES),
+                      id_q, k ? 1u : 0u);
+          umma_commit(&dq_full[s]);
+          umma_commit(&qdo_empty[s]);
+          if (it + 1 == niter) umma_commit(&kv_empty[ks]);
+        }
+        __syncwarp();
       }
-      __syncwarp();
     }
   } else {
     const int quad = warp & 3;
@@ -625,14 +674,11 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_co
     uint8_t* sp = smem + AttnBwdSmem::P;
     uint8_t* sds = smem + AttnBwdSmem::DS;
     float* sdq = reinterpret_cast<float*>(smem + AttnBwdSmem::DQ);
-    const size_t stat0 = (static_cast<size_t>(b) * heads + h) * seq + r;
-    float lse_r = lse[stat0 + jt * BQ];
-    float dls = delta[stat0 + jt * BQ] * scale;
-    // dQ tile `it` (complete in TMEM once dq_full[it&1] has fired): TMEM -> swizzled fp32 staging ->
-    // one 32 KB bulk reduce-add into the accumulator tile of (b, h, q tile jt+it)
-    auto flush_dq = [&](int it) {
+    // dQ tile of step g (complete in TMEM once dq_full[g&1] has fired): TMEM -> swizzled fp32 staging
+    // -> one 32 KB bulk reduce-add into the accumulator tile `tile`
+    auto flush_dq = [&](int g, size_t tile) {
       uint32_t v[32];
-      tmem_ld_32x32b_x32(tm_dq + (it & 1) * 64 + lane_off + half * 32, v);
+      tmem_ld_32x32b_x32(tm_dq + (g & 1) * 64 + lane_off + half * 32, v);
       tmem_ld_wait();
       if (issuer) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // staging no longer read
       named_barrier_sync(1, 256);
@@ -643,63 +689,96 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_co
       fence_proxy_async_smem();
       named_barrier_sync(2, 256);
       if (issuer) {
-        float* dst = dq_accum + (static_cast<size_t>((b * heads + h) * nq + jt + it)) * (BQ * HD);
+        float* dst = dq_accum + tile * (BQ * HD);
         asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], %2;" ::"l"(dst),
                      "r"(smem_u32(sdq)), "r"(BQ * HD * 4)
                      : "memory");
         asm volatile("cp.async.bulk.commit_group;" ::: "memory");
       }
     };
-    for (int it = 0; it < niter; ++it) {
-      // row statistics of the next q tile: in flight while this one is processed
-      float lse_n = 0.f, dls_n = 0.f;
-      if (it + 1 < niter) {
-        lse_n = lse[stat0 + (jt + it + 1) * BQ];
-        dls_n = delta[stat0 + (jt + it + 1) * BQ] * scale;
+    int g = 0;
+    BwdItem w = bwd_item_decode(cta, heads, hb);      // round 0 item = this CTA's index (the grid never exceeds n_items)
+    size_t stat0 = (static_cast<size_t>(w.b) * heads + w.h) * seq + r;
+    float lse_r = lse[stat0 + w.jt * BQ];
+    float dls = delta[stat0 + w.jt * BQ] * scale;
+    for (int round = 0;; ++round) {
+      const int niter = nq - w.jt;
+      const size_t tile0 = static_cast<size_t>(w.b * heads + w.h) * nq + w.jt;
+      for (int it = 0; it < niter; ++it, ++g) {
+        // row statistics of the next q tile: in flight while this one is processed
+        float lse_n = 0.f, dls_n = 0.f;
+        if (it + 1 < niter) {
+          lse_n = lse[stat0 + (w.jt + it + 1) * BQ];
+          dls_n = delta[stat0 + (w.jt + it + 1) * BQ] * scale;
+        }
+        mbar_wait(sdp_full, g & 1);
+        tc_fence_after();
+        // The diagonal tile (q tile == kv tile, it == 0) is the only one that needs the causal mask.
+        // P/dS stores wait for the previous step's MMAs (dq_full of step g-1); on the first step of
+        // an item that barrier was already consumed by the previous item's tail.
+        if (it == 0)
+          bwd_math_tile<true>(tm_s + lane_off, tm_dp + lane_off, half, r, lane, lse_r, dls, scale, scale_log2, sp, sds,
+                              sdp_free, nullptr, 0, false);
+        else
+          bwd_math_tile<false>(tm_s + lane_off, tm_dp + lane_off, half, r, lane, lse_r, dls, scale, scale_log2, sp, sds,
+                               sdp_free, &dq_full[(g - 1) & 1], ((g - 1) >> 1) & 1, true);
+        tc_fence_before();
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(pds_full);
+        if (it > 0) flush_dq(g - 1, tile0 + it - 1);     // dq_full of step g-1 was observed inside bwd_math_tile
+        lse_r = lse_n;
+        dls = dls_n;
       }
-      mbar_wait(sdp_full, it & 1);
+      // next item's identity and first row statistics: loads in flight under this item's tail
+      const int next_item = fwd_item_index(round + 1, n_cta, cta);
+      const bool more = next_item < n_items;
+      BwdItem wn = w;
+      size_t stat0n = stat0;
+      if (more) {
+        wn = bwd_item_decode(next_item, heads, hb);
+        stat0n = (static_cast<size_t>(wn.b) * heads + wn.h) * seq + r;
+        lse_r = lse[stat0n + wn.jt * BQ];
+        dls = delta[stat0n + wn.jt * BQ] * scale;
+      }
+      mbar_wait(&dq_full[(g - 1) & 1], ((g - 1) >> 1) & 1);
       tc_fence_after();
-      // the diagonal tile (q tile == kv tile, it == 0) is the only one that needs the causal mask
-      if (it == 0)
-        bwd_math_tile<true>(tm_s + lane_off, tm_dp + lane_off, half, r, lane, lse_r, dls, scale, scale_log2, sp, sds,
-                            sdp_free, nullptr, 0, false);
-      else
-        bwd_math_tile<false>(tm_s + lane_off, tm_dp + lane_off, half, r, lane, lse_r, dls, scale, scale_log2, sp, sds,
-                             sdp_free, &dq_full[(it - 1) & 1], ((it - 1) >> 1) & 1, true);
-      tc_fence_before();
-      fence_proxy_async_smem();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(pds_full);
-      if (it > 0) flush_dq(it - 1);       // dq_full of tile it-1 was observed inside bwd_math_tile
-      lse_r = lse_n;
-      dls = dls_n;
-    }
-    mbar_wait(&dq_full[(niter - 1) & 1], ((niter - 1) >> 1) & 1);
-    tc_fence_after();
-    flush_dq(niter - 1);
-    // dK, dV of this kv tile (the last dq_full commit covers every MMA issued before it)
-    const size_t grow = static_cast<size_t>(row0 + jt * BKV + r);
-    __nv_bfloat16* dkp = dqkv + grow * 3 * C + C + h * HD + half * 32;
-    __nv_bfloat16* dvp = dqkv + grow * 3 * C + 2 * C + h * HD + half * 32;
-    {
+      flush_dq(g - 1, tile0 + niter - 1);
+      // dK, dV of this kv tile (the last dq_full commit covers every MMA issued before it):
+      // TMEM -> bf16 -> swizzled tiles in the dQ staging buffer -> two TMA stores
       uint32_t a[32], bb[32];
       tmem_ld_32x32b_x32(tm_dk + lane_off + half * 32, a);
       tmem_ld_32x32b_x32(tm_dv + lane_off + half * 32, bb);
       tmem_ld_wait();
+      tc_fence_before();      // dK/dV reads precede the next item's first accumulate=0 MMA (ordered by pds_full)
+      if (issuer) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // last dQ reduce has read the staging
+      named_barrier_sync(1, 256);
+      uint8_t* sdk = smem + AttnBwdSmem::DQ;
+      uint8_t* sdv = sdk + TILE_BYTES;
 #pragma unroll
-      for (int g = 0; g < 4; ++g) {
-        uint4 w, u;
-        w.x = pack_bf16x2(__uint_as_float(a[g * 8 + 0]), __uint_as_float(a[g * 8 + 1]));
-        w.y = pack_bf16x2(__uint_as_float(a[g * 8 + 2]), __uint_as_float(a[g * 8 + 3]));
-        w.z = pack_bf16x2(__uint_as_float(a[g * 8 + 4]), __uint_as_float(a[g * 8 + 5]));
-        w.w = pack_bf16x2(__uint_as_float(a[g * 8 + 6]), __uint_as_float(a[g * 8 + 7]));
-        u.x = pack_bf16x2(__uint_as_float(bb[g * 8 + 0]), __uint_as_float(bb[g * 8 + 1]));
-        u.y = pack_bf16x2(__uint_as_float(bb[g * 8 + 2]), __uint_as_float(bb[g * 8 + 3]));
-        u.z = pack_bf16x2(__uint_as_float(bb[g * 8 + 4]), __uint_as_float(bb[g * 8 + 5]));
-        u.w = pack_bf16x2(__uint_as_float(bb[g * 8 + 6]), __uint_as_float(bb[g * 8 + 7]));
-        reinterpret_cast<uint4*>(dkp)[g] = w;
-        reinterpret_cast<uint4*>(dvp)[g] = u;
+      for (int q = 0; q < 4; ++q) {
+        uint4 wv, u;
+        wv.x = pack_bf16x2(__uint_as_float(a[q * 8 + 0]), __uint_as_float(a[q * 8 + 1]));
+        wv.y = pack_bf16x2(__uint_as_float(a[q * 8 + 2]), __uint_as_float(a[q * 8 + 3]));
+        wv.z = pack_bf16x2(__uint_as_float(a[q * 8 + 4]), __uint_as_float(a[q * 8 + 5]));
+        wv.w = pack_bf16x2(__uint_as_float(a[q * 8 + 6]), __uint_as_float(a[q * 8 + 7]));
+        u.x = pack_bf16x2(__uint_as_float(bb[q * 8 + 0]), __uint_as_float(bb[q * 8 + 1]));
+        u.y = pack_bf16x2(__uint_as_float(bb[q * 8 + 2]), __uint_as_float(bb[q * 8 + 3]));
+        u.z = pack_bf16x2(__uint_as_float(bb[q * 8 + 4]), __uint_as_float(bb[q * 8 + 5]));
+        u.w = pack_bf16x2(__uint_as_float(bb[q * 8 + 6]), __uint_as_float(bb[q * 8 + 7]));
+        st_swizzled_16B(sdk, r, half * 32 + q * 8, wv);
+        st_swizzled_16B(sdv, r, half * 32 + q * 8, u);
       }
+      fence_proxy_async_smem();
+      named_barrier_sync(2, 256);
+      if (issuer) {
+        tma_store_2d(&tm_dqkv, sdk, C + w.h * HD, w.b * seq + w.jt * BKV);
+        tma_store_2d(&tm_dqkv, sdv, 2 * C + w.h * HD, w.b * seq + w.jt * BKV);
+        tma_store_commit();
+      }
+      if (!more) break;
+      w = wn;
+      stat0 = stat0n;
     }
     if (issuer) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");    // staging must outlive the last reduce
   }
@@ -737,10 +816,13 @@ extern "C" int b200_attention_fwd(const void* qkv, void* out, float* lse, int ba
     attr = true;
   }
   const float scale_log2 = 1.4426950408889634f / 8.0f;   // log2(e) / sqrt(64)
+  CUtensorMap tm_out;
+  rc = make_tmap_2d(&tm_out, out, 2, (uint64_t)C, (uint64_t)batch * seq, (uint64_t)C * 2, 64, 128, 128);
+  if (rc) return rc;
   const int n_items = (seq / BQ) * heads * batch;
   const int grid = n_items < 2 * num_sms() ? n_items : 2 * num_sms();      // persistent, two CTAs per SM
   B200_CUDA(launch_k(attention_fwd_kernel, dim3(grid), dim3(ATT_FWD_THREADS), AttnFwdSmem::BYTES, static_cast<cudaStream_t>(stream),
-      tm, static_cast<__nv_bfloat16*>(out), lse, seq, heads, batch, scale_log2));
+      tm, tm_out, lse, seq, heads, batch, scale_log2));
   B200_CUDA(cudaGetLastError());
   return 0;
 }
@@ -765,6 +847,9 @@ extern "C" int b200_attention_bwd(const void* qkv, const void* out, const void* 
   if (rc) return rc;
   rc = make_tmap_2d(&tm_do, dout, 2, (uint64_t)C, (uint64_t)batch * seq, (uint64_t)C * 2, 64, 128, 128);
   if (rc) return rc;
+  CUtensorMap tm_dqkv;
+  rc = make_tmap_2d(&tm_dqkv, dqkv, 2, (uint64_t)3 * C, (uint64_t)batch * seq, (uint64_t)3 * C * 2, 64, 128, 128);
+  if (rc) return rc;
   static bool attr = false;
   if (!attr) {
     B200_CUDA(cudaFuncSetAttribute(attention_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AttnBwdSmem::BYTES));
@@ -776,10 +861,10 @@ extern "C" int b200_attention_bwd(const void* qkv, const void* out, const void* 
                                                     static_cast<const __nv_bfloat16*>(dout), delta, dq_accum, batch, seq,
                                                     heads));
   const float scale = 0.125f, scale_log2 = 1.4426950408889634f / 8.0f;
-  dim3 grid(seq / BKV, heads, batch);
-  B200_CUDA(launch_k(attention_bwd_kernel, dim3(grid), dim3(ATT_BWD_THREADS), AttnBwdSmem::BYTES, s, tm_qkv, tm_do, lse, delta, dq_accum,
-                                                                    static_cast<__nv_bfloat16*>(dqkv), seq, heads, scale,
-                                                                    scale_log2));
+  const int n_items = (seq / BKV) * heads * batch;
+  const int grid = n_items < num_sms() ? n_items : num_sms();       // persistent, one CTA per SM
+  B200_CUDA(launch_k(attention_bwd_kernel, dim3(grid), dim3(ATT_BWD_THREADS), AttnBwdSmem::BYTES, s, tm_qkv, tm_do, tm_dqkv,
+                     lse, static_cast<const float*>(delta), dq_accum, seq, heads, batch, scale, scale_log2));
   int64_t total = (int64_t)batch * seq * C / 8;
   int qblocks = (int)((total + 255) / 256);
   if (qblocks > num_sms() * 8) qblocks = num_sms() * 8;

@@ -22,7 +22,7 @@ def build():
     others = [str(_build.OBJ_DIR / (s.stem + ".o")) for s in _build._sources() if s.stem != "attention"]
     for v in VARIANTS:
         obj = _build.OBJ_DIR / f"attention_exp{v}.o"
-        subprocess.run([_build._nvcc(), *_build.NVCC_FLAGS, f"-DATT_EXP={v}", "-c", str(_build.CSRC / "attention.cu"),
+        subprocess.run([_build._nvcc(), *_build.NVCC_FLAGS, f"-DATT_EXP={v}", *(["-DATT_TRACE"] if v & 16 else []), "-c", str(_build.CSRC / "attention.cu"),
                         "-o", str(obj)], check=True)
         subprocess.run([_build._nvcc(), "-shared", "-o", str(EXP_DIR / f"libexp{v}.so"), str(obj), *others], check=True)
         print("built variant", v)
@@ -56,6 +56,31 @@ def child():
     print("  ".join(parts), flush=True)
 
 
+def trace():
+    """Cycle stamps of one late backward CTA (library built with -DATT_TRACE)."""
+    import torch
+    from jax_distributed_tuts_b200.ops import kernels as K
+    b, t, h = 16, 1024, 12
+    qkv = torch.randn(b, t, 3, h, 64, device="cuda").bfloat16()
+    out = torch.empty(b, t, h, 64, device="cuda", dtype=torch.bfloat16)
+    lse = torch.zeros(b, h, t, device="cuda")
+    K.attention_fwd(qkv, out, lse, b, t, h)
+    dout = torch.randn_like(out)
+    dqkv = torch.empty_like(qkv)
+    n = K.attention_bwd_scratch_numel(b, t, h)
+    scratch = torch.zeros(n + 4096, device="cuda")
+    for _ in range(2):
+        K.attention_bwd(qkv, out, dout, lse, dqkv, scratch[:n], b, t, h)
+    torch.cuda.synchronize()
+    tr = scratch[n:].cpu().tolist()
+    print("bwd math thread per item: [item start, first sdp_full, 2nd step top, loop done, last dq_full, flushed, dK/dV stored, niter]")
+    for j in range(12):
+        print("  n=%2d " % j + " ".join("%7.0f" % tr[j * 8 + k] for k in range(8)))
+    print("bwd MMA thread per item: [item start, kv_full seen, first S/dP issued]")
+    for j in range(12):
+        print("  n=%2d " % j + " ".join("%7.0f" % tr[512 + j * 4 + k] for k in range(3)))
+
+
 def run():
     for v in VARIANTS:
         env = dict(os.environ, B200DIST_LIB=str(EXP_DIR / f"libexp{v}.so"))
@@ -70,5 +95,7 @@ if __name__ == "__main__":
         build()
     elif "--child" in sys.argv:
         child()
+    elif "--trace" in sys.argv:
+        trace()
     else:
         run()
