@@ -178,6 +178,8 @@ def main() -> None:
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--per-gpu-batch", type=int, default=0, help="override the config's per-GPU batch (exploration)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--kernel-table", action="store_true",
+                    help="after the timed regions, profile 3 more steps with CUPTI and print per-kernel device time to stderr")
     ap.add_argument("--no-extra", action="store_true",
                     help="skip the secondary GPT-2 small measurement that the default config appends as `extra`")
     ap.add_argument("--extra-child", action="store_true", help=argparse.SUPPRESS)
@@ -359,6 +361,20 @@ def main() -> None:
                 loss_val = api_step()
             sync()
             e2e_ms = (time.perf_counter() - t0) * 1e3
+
+        if args.kernel_table and rank == 0:     # diagnostic only: runs after every reported number was taken
+            from torch.profiler import ProfilerActivity, profile
+            sync_local = torch.cuda.synchronize
+            sync_local()
+            with profile(activities=[ProfilerActivity.CUDA]) as prof:
+                for _ in range(3):
+                    run_step()
+                sync_local()
+            rows_ = sorted(prof.key_averages(), key=lambda ev: -ev.device_time_total)
+            tot = sum(ev.device_time_total for ev in rows_) / 3.0
+            print(f"[kernel table] {tot / 1e3:.3f} ms of kernel time per step (sum over kernels, PDL overlap counted twice)", file=sys.stderr)
+            for ev in rows_[:28]:
+                print(f"  {ev.device_time_total / 3e3:8.3f} ms  x{ev.count // 3:4d}  {ev.key[:110]}", file=sys.stderr)
 
         t = torch.tensor([dev_ms, e2e_ms or 0.0], dtype=torch.float64, device=device)
         if world > 1:

@@ -94,7 +94,7 @@ __device__ __forceinline__ void adamw1(float& p, float& m, float& v, float g, co
   p = p - hp.lr * ((m * c1) / (sqrtf(v * c2) + hp.eps) + hp.weight_decay * p);
 }
 
-__global__ void __launch_bounds__(256, 1)
+__global__ void __launch_bounds__(256, 2)
 fused_reduce_adamw_kernel(const CommDev c, const b200_seg* __restrict__ segs, int nseg, int broadcast,
                           float* __restrict__ p_local, __nv_bfloat16* __restrict__ bf16_local,
                           float* __restrict__ m, float* __restrict__ v, const b200_adamw_hparams hp,
@@ -125,7 +125,8 @@ fused_reduce_adamw_kernel(const CommDev c, const b200_seg* __restrict__ segs, in
       const int64_t nthreads = static_cast<int64_t>(gridDim.x) * blockDim.x;
       constexpr int U = 4;   // independent 16-byte vectors per thread per iteration (memory-level parallelism)
       for (int64_t i0 = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i0 < total4; i0 += nthreads * U) {
-        int64_t src[U], loc[U], dst[U];
+        // per vector only (row, col) are kept (32-bit); the three 64-bit offsets are rebuilt where used
+        uint32_t vrow[U], vcol[U];
         bool ok[U];
         float4 g[U], pp[U], mm[U], vv[U];
         float* p_base = broadcast ? c.param[c.rank] : p_local;
@@ -133,25 +134,27 @@ fused_reduce_adamw_kernel(const CommDev c, const b200_seg* __restrict__ segs, in
         for (int u = 0; u < U; ++u) {
           const int64_t i = i0 + u * nthreads;
           ok[u] = i < total4;
-          const int64_t ii = ok[u] ? i : 0;
+          const uint32_t ii = ok[u] ? static_cast<uint32_t>(i) : 0u;
           // rows == 1 (every DP segment, contiguous FSDP shards) needs no division; otherwise the
           // segment is far below 2^31 vectors and a 32-bit division is enough
-          const int64_t row = sg.rows == 1 ? 0 : static_cast<int64_t>(static_cast<uint32_t>(ii) / static_cast<uint32_t>(rl4));
-          const int64_t col = (ii - row * rl4) << 2;
-          src[u] = sg.src_off + row * sg.src_pitch + col;
-          loc[u] = sg.loc_off + row * sg.row_len + col;
-          dst[u] = broadcast ? sg.dst_off + row * sg.row_len + col : loc[u];
+          vrow[u] = sg.rows == 1 ? 0u : ii / static_cast<uint32_t>(rl4);
+          vcol[u] = (ii - vrow[u] * static_cast<uint32_t>(rl4)) << 2;
         }
+        auto src_of = [&](int u) { return sg.src_off + static_cast<int64_t>(vrow[u]) * sg.src_pitch + vcol[u]; };
+        auto loc_of = [&](int u) { return sg.loc_off + static_cast<int64_t>(vrow[u]) * sg.row_len + vcol[u]; };
+        auto dst_of = [&](int u) {
+          return (broadcast ? sg.dst_off : sg.loc_off) + static_cast<int64_t>(vrow[u]) * sg.row_len + vcol[u];
+        };
         // ---- loads (all issued before any use) ----
 #pragma unroll
         for (int u = 0; u < U; ++u) {
           if (!ok[u]) continue;
-          if (c.world == 1) g[u] = *reinterpret_cast<const float4*>(my_grad + src[u]);
-          else if (c.mc_grad != nullptr) g[u] = mc_ld_reduce_f32x4(c.mc_grad + src[u]);
+          if (c.world == 1) g[u] = *reinterpret_cast<const float4*>(my_grad + src_of(u));
+          else if (c.mc_grad != nullptr) g[u] = mc_ld_reduce_f32x4(c.mc_grad + src_of(u));
           else g[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-          mm[u] = *reinterpret_cast<float4*>(m + loc[u]);
-          vv[u] = *reinterpret_cast<float4*>(v + loc[u]);
-          pp[u] = *reinterpret_cast<float4*>(p_base + dst[u]);
+          mm[u] = *reinterpret_cast<float4*>(m + loc_of(u));
+          vv[u] = *reinterpret_cast<float4*>(v + loc_of(u));
+          pp[u] = *reinterpret_cast<float4*>(p_base + dst_of(u));
         }
         if (c.world > 1 && c.mc_grad == nullptr) {
 #pragma unroll 1
@@ -163,7 +166,7 @@ fused_reduce_adamw_kernel(const CommDev c, const b200_seg* __restrict__ segs, in
             float4 t4[U];
 #pragma unroll
             for (int u = 0; u < U; ++u)
-              if (ok[u]) t4[u] = ld_sys_f32x4(c.grad[peer] + src[u]);
+              if (ok[u]) t4[u] = ld_sys_f32x4(c.grad[peer] + src_of(u));
 #pragma unroll
             for (int u = 0; u < U; ++u)
               if (ok[u]) { g[u].x += t4[u].x; g[u].y += t4[u].y; g[u].z += t4[u].z; g[u].w += t4[u].w; }
@@ -177,24 +180,24 @@ fused_reduce_adamw_kernel(const CommDev c, const b200_seg* __restrict__ segs, in
           adamw1(pp[u].y, mm[u].y, vv[u].y, g[u].y * hp.grad_scale, hp, c1, c2);
           adamw1(pp[u].z, mm[u].z, vv[u].z, g[u].z * hp.grad_scale, hp, c1, c2);
           adamw1(pp[u].w, mm[u].w, vv[u].w, g[u].w * hp.grad_scale, hp, c1, c2);
-          *reinterpret_cast<float4*>(m + loc[u]) = mm[u];
-          *reinterpret_cast<float4*>(v + loc[u]) = vv[u];
+          *reinterpret_cast<float4*>(m + loc_of(u)) = mm[u];
+          *reinterpret_cast<float4*>(v + loc_of(u)) = vv[u];
           __nv_bfloat162 lo = __floats2bfloat162_rn(pp[u].x, pp[u].y), hi = __floats2bfloat162_rn(pp[u].z, pp[u].w);
           const uint32_t w0 = *reinterpret_cast<uint32_t*>(&lo), w1 = *reinterpret_cast<uint32_t*>(&hi);
           if (!broadcast || c.world == 1) {
-            *reinterpret_cast<float4*>(p_base + dst[u]) = pp[u];
+            *reinterpret_cast<float4*>(p_base + dst_of(u)) = pp[u];
             __nv_bfloat16* b = broadcast ? c.bf16[c.rank] : bf16_local;
-            if (b != nullptr) *reinterpret_cast<uint2*>(b + dst[u]) = make_uint2(w0, w1);
+            if (b != nullptr) *reinterpret_cast<uint2*>(b + dst_of(u)) = make_uint2(w0, w1);
           } else if (c.mc_param != nullptr) {
-            mc_st_f32x4(c.mc_param + dst[u], pp[u]);
-            if (c.mc_bf16 != nullptr) mc_st_b32x2(c.mc_bf16 + dst[u], w0, w1);
+            mc_st_f32x4(c.mc_param + dst_of(u), pp[u]);
+            if (c.mc_bf16 != nullptr) mc_st_b32x2(c.mc_bf16 + dst_of(u), w0, w1);
           } else {
 #pragma unroll 1
             for (int k = 0; k < c.world; ++k) {
               int peer = c.rank + k;
               if (peer >= c.world) peer -= c.world;
-              *reinterpret_cast<float4*>(c.param[peer] + dst[u]) = pp[u];
-              if (c.bf16[peer] != nullptr) *reinterpret_cast<uint2*>(c.bf16[peer] + dst[u]) = make_uint2(w0, w1);
+              *reinterpret_cast<float4*>(c.param[peer] + dst_of(u)) = pp[u];
+              if (c.bf16[peer] != nullptr) *reinterpret_cast<uint2*>(c.bf16[peer] + dst_of(u)) = make_uint2(w0, w1);
             }
           }
         }
@@ -342,8 +345,12 @@ extern "C" int b200_fused_reduce_adamw(const b200_comm_ctx* ctx, const b200_seg*
   }
   if (!broadcast) B200_REQUIRE(p_local != nullptr, "comm: local mode needs p_local");
   if (blocks <= 0) blocks = 64;
-  if (blocks > B200_COMM_MAX_BLOCKS) blocks = B200_COMM_MAX_BLOCKS;
-  if (blocks > num_sms()) blocks = num_sms();   // every block must be resident: they spin on each other across GPUs
+  if (ctx->world == 1) {
+    blocks = 2 * num_sms();     // no cross-GPU barrier: fill the machine (two resident blocks per SM)
+  } else {
+    if (blocks > B200_COMM_MAX_BLOCKS) blocks = B200_COMM_MAX_BLOCKS;
+    if (blocks > num_sms()) blocks = num_sms();   // every block must be resident: they spin on each other across GPUs
+  }
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   B200_CUDA(launch_k(fused_reduce_adamw_kernel, dim3(blocks), dim3(256), 0, s, d, segs_dev, nseg, broadcast, p_local,
                                                    static_cast<__nv_bfloat16*>(bf16_local), m, v, *hp,

@@ -29,13 +29,16 @@ int cuda_fail(cudaError_t e, const char* what, const char* file, int line) {
 
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
+static std::atomic<int> g_pdl_override{-1};     // -1: follow the environment, 0 / 1: forced by b200_set_pdl
+
 bool pdl_enabled() {
   static int v = -1;
   if (v < 0) {
     const char* e = getenv("B200DIST_NO_PDL");
     v = (e != nullptr && e[0] == '1') ? 0 : 1;
   }
-  return v == 1;
+  const int o = g_pdl_override.load(std::memory_order_relaxed);
+  return v == 1 && o != 0;      // the environment switch always wins when it says "off"
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
@@ -107,4 +110,5 @@ const char* b200_last_error(void) { return b200::g_err; }
 long long b200_launch_count(void) { return b200::g_launches.load(); }
 void b200_reset_launch_count(void) { b200::g_launches.store(0); }
 int b200_abi_version(void) { return B200_ABI_VERSION; }
+void b200_set_pdl(int mode) { b200::g_pdl_override.store(mode < 0 ? -1 : (mode ? 1 : 0)); }
 }

@@ -70,7 +70,156 @@ __global__ void xent_warp_kernel(const float* __restrict__ logits, int ld, const
   }
 }
 
-// Large-vocabulary variant on bf16 logits, in place: logits are replaced by dlogits.
+// bf16 halves of a packed word as fp32, two equivalent encodings (shift/mask and byte permute).
+// The row lives in registers as packed words across several passes; if two passes unpack with the
+// same instructions, ptxas merges them, keeps a whole pass of unpacked floats alive and spills.
+__device__ __forceinline__ float bf16_lo_a(uint32_t w) { return __uint_as_float(w << 16); }
+__device__ __forceinline__ float bf16_hi_a(uint32_t w) { return __uint_as_float(w & 0xFFFF0000u); }
+__device__ __forceinline__ float bf16_lo_b(uint32_t w) { return __uint_as_float(__byte_perm(w, 0u, 0x1044)); }
+__device__ __forceinline__ float bf16_hi_b(uint32_t w) { return __uint_as_float(__byte_perm(w, 0u, 0x3244)); }
+__device__ __forceinline__ uint32_t max_bf16x2(uint32_t a, uint32_t b) {
+  uint32_t r;
+  asm("max.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+  return r;
+}
+__device__ __forceinline__ float ex2_fast(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+template <int NV>
+__global__ void __launch_bounds__(256, 2)
+xent_row_bf16_kernel(__nv_bfloat16* __restrict__ logits, int ld, const int64_t* __restrict__ labels, int rows,
+                     int classes, float grad_scale, float* __restrict__ metrics, float* __restrict__ row_loss) {
+  pdl_sync();
+  __shared__ float s_red[8];
+  __shared__ int s_idx[8];
+  __shared__ float s_bc[2];
+  __shared__ int s_bi;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int nvec = classes >> 3, tail = classes & 7;
+  constexpr float kLog2e = 1.4426950408889634f;
+  const float lscale = log2f(grad_scale);
+  for (int row = blockIdx.x; row < rows; row += gridDim.x) {
+    __nv_bfloat16* x = logits + static_cast<size_t>(row) * ld;
+    const uint4* xv = reinterpret_cast<const uint4*>(x);
+    const int label = static_cast<int>(labels[row]);
+    uint32_t w[NV][4];
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const int i = tid + k * 256;
+      const uint4 t = i < nvec ? xv[i] : make_uint4(0xFF80FF80u, 0xFF80FF80u, 0xFF80FF80u, 0xFF80FF80u);   // -inf pairs
+      w[k][0] = t.x; w[k][1] = t.y; w[k][2] = t.z; w[k][3] = t.w;
+    }
+    const float vt = tid < tail ? __bfloat162float(x[nvec * 8 + tid]) : -INFINITY;
+    const float x_label = (tid == 0) ? __bfloat162float(x[label]) : 0.f;     // read before the row is overwritten
+    // ---- maximum (packed bf16x2) ----
+    uint32_t pm0 = w[0][0], pm1 = w[0][1];
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      pm0 = max_bf16x2(pm0, w[k][0]);
+      pm1 = max_bf16x2(pm1, w[k][1]);
+      pm0 = max_bf16x2(pm0, w[k][2]);
+      pm1 = max_bf16x2(pm1, w[k][3]);
+    }
+    pm0 = max_bf16x2(pm0, pm1);
+    const float mloc = fmaxf(fmaxf(__uint_as_float(pm0 << 16), __uint_as_float(pm0 & 0xFFFF0000u)), vt);
+    float mx = warp_max(mloc);
+    if (lane == 0) s_red[warp] = mx;
+    __syncthreads();
+    if (warp == 0) {
+      float m2 = warp_max(lane < 8 ? s_red[lane] : -INFINITY);
+      if (lane == 0) s_bc[0] = m2;
+    }
+    __syncthreads();
+    const float m = s_bc[0];
+    // first index of the maximum: only threads that hold it look for it
+    int cand = 0x7fffffff;
+    const uint32_t mbits = __float_as_uint(m) >> 16;
+    if (mloc == m) {
+      if (vt == m) cand = nvec * 8 + tid;
+#pragma unroll
+      for (int k = NV - 1; k >= 0; --k) {
+#pragma unroll
+        for (int j = 3; j >= 0; --j) {       // integer compares on the bf16 bit patterns (m is one of them)
+          if ((w[k][j] >> 16) == mbits) cand = (tid + k * 256) * 8 + 2 * j + 1;
+          if ((w[k][j] & 0xFFFFu) == mbits) cand = (tid + k * 256) * 8 + 2 * j;
+        }
+      }
+    }
+    // ---- sum of exponentials ----
+    const float ml2 = m * kLog2e;
+    float sum0 = 0.f, sum1 = 0.f;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        sum0 += ex2_fast(fmaf(bf16_lo_a(w[k][j]), kLog2e, -ml2));
+        sum1 += ex2_fast(fmaf(bf16_hi_a(w[k][j]), kLog2e, -ml2));
+      }
+    }
+    float sum = sum0 + sum1 + (tid < tail ? ex2_fast(fmaf(vt, kLog2e, -ml2)) : 0.f);
+    sum = warp_sum(sum);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) cand = min(cand, __shfl_xor_sync(0xffffffffu, cand, o));
+    if (lane == 0) { s_red[warp] = sum; s_idx[warp] = cand; }
+    __syncthreads();
+    if (warp == 0) {
+      float s2 = warp_sum(lane < 8 ? s_red[lane] : 0.f);
+      int a2 = lane < 8 ? s_idx[lane] : 0x7fffffff;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) a2 = min(a2, __shfl_xor_sync(0xffffffffu, a2, o));
+      if (lane == 0) { s_bc[1] = s2; s_bi = a2; }
+    }
+    __syncthreads();
+    const float ssum = s_bc[1];
+    if (tid == 0) {
+      const float l = m + __logf(ssum) - x_label;
+      if (row_loss != nullptr) row_loss[row] = l;
+      if (metrics != nullptr) {
+        atomicAdd(&metrics[0], l);
+        if (s_bi == label) atomicAdd(&metrics[1], 1.0f);
+      }
+    }
+    // ---- gradient: softmax * scale, minus scale at the label ----
+    const float c = lscale - ml2 - log2f(ssum);
+    const int lchunk = label >> 3, lj = label & 7;
+    uint4* xo = reinterpret_cast<uint4*>(x);
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const int i = tid + k * 256;
+      if (i < nvec) {
+        float g[8];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          g[2 * j] = ex2_fast(fmaf(bf16_lo_b(w[k][j]), kLog2e, c));
+          g[2 * j + 1] = ex2_fast(fmaf(bf16_hi_b(w[k][j]), kLog2e, c));
+        }
+        if (i == lchunk) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            if (j == lj) g[j] -= grad_scale;
+        }
+        uint4 o;
+        __nv_bfloat162 t;
+        t = __floats2bfloat162_rn(g[0], g[1]); o.x = *reinterpret_cast<uint32_t*>(&t);
+        t = __floats2bfloat162_rn(g[2], g[3]); o.y = *reinterpret_cast<uint32_t*>(&t);
+        t = __floats2bfloat162_rn(g[4], g[5]); o.z = *reinterpret_cast<uint32_t*>(&t);
+        t = __floats2bfloat162_rn(g[6], g[7]); o.w = *reinterpret_cast<uint32_t*>(&t);
+        xo[i] = o;
+      }
+    }
+    if (tid < tail) {
+      const int cidx = nvec * 8 + tid;
+      x[cidx] = __float2bfloat16_rn(ex2_fast(fmaf(vt, kLog2e, c)) - (cidx == label ? grad_scale : 0.f));
+    }
+    __syncthreads();     // s_red / s_bc are reused by the next row
+  }
+}
+
+// Large-vocabulary variant on bf16 logits, in place, any vocabulary size (fallback of the register-resident kernel above):
+// logits are replaced by dlogits.
 // One block per row; the row is read twice (max+sum online in pass 1, gradient in pass 2);
 // the second read hits L2 (a 50k-class bf16 row is 100 KB).
 __global__ void __launch_bounds__(512)
@@ -431,6 +580,14 @@ extern "C" int b200_softmax_xent_bf16_inplace(void* logits_bf16, int ld, const i
                                               int classes, float grad_scale, float* metrics, float* row_loss,
                                               void* stream) {
   B200_REQUIRE(rows > 0 && classes > 0, "xent: empty input");
+  const bool vec_ok = (ld % 8 == 0) && ((reinterpret_cast<uintptr_t>(logits_bf16) & 15) == 0) && grad_scale > 0.f;
+  if (vec_ok && classes >= 4096 && classes <= 256 * 8 * 25) {      // row fits the block's registers
+    int rblocks = rows < num_sms() * 2 ? rows : num_sms() * 2;
+    B200_CUDA(launch_k(xent_row_bf16_kernel<25>, dim3(rblocks), dim3(256), 0, static_cast<cudaStream_t>(stream),
+        static_cast<__nv_bfloat16*>(logits_bf16), ld, labels, rows, classes, grad_scale, metrics, row_loss));
+    B200_CUDA(cudaGetLastError());
+    return 0;
+  }
   int blocks = rows < num_sms() * 4 ? rows : num_sms() * 4;
   B200_CUDA(launch_k(xent_block_bf16_kernel, dim3(blocks), dim3(512), 0, static_cast<cudaStream_t>(stream), 
       static_cast<__nv_bfloat16*>(logits_bf16), ld, labels, rows, classes, grad_scale, metrics, row_loss));

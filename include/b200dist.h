@@ -16,13 +16,18 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 13
+#define B200_ABI_VERSION 14
 
 const char* b200_last_error(void);
 int b200_abi_version(void);
 /* Number of kernels launched by this library since the last reset (host-side counter). */
 long long b200_launch_count(void);
 void b200_reset_launch_count(void);
+/* Programmatic dependent launch for the launches that follow (it is a launch attribute, so inside a
+ * stream capture it is baked into the graph): 1 = on, 0 = off, -1 = default (on, unless the
+ * environment has B200DIST_NO_PDL=1, which always wins). Back-to-back short kernels gain from the
+ * overlapped prologue; long persistent kernels do not, and early-launched CTAs only tie up SMs. */
+void b200_set_pdl(int mode);
 
 /* ------------------------------------------------------------------------------------------
  * GEMM on tcgen05 tensor cores with TMEM accumulators and TMA-fed operand tiles.

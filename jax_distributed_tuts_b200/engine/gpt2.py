@@ -50,6 +50,7 @@ class GPT2Engine(FusedEngine):
         super().__init__(mesh, mode=mode, lr=lr, num_minibatches=num_minibatches,
                          data_axis_name=config.get("data_axis_name", "data"), **kw)
         self.cfg = config
+        self.pdl = tokens < 4096       # long persistent kernels: dependent launch only ties up SMs (see FusedEngine.pdl)
         self.L, self.Hh, self.C = config.n_layer, config.n_head, config.d_model
         self.T = seq_len or config.n_ctx
         assert self.T % 128 == 0 and self.T <= config.n_ctx

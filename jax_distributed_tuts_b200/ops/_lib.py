@@ -12,7 +12,7 @@ from typing import Optional
 
 from . import _build
 
-ABI_VERSION = 13
+ABI_VERSION = 14
 
 _lib: Optional[C.CDLL] = None
 
@@ -97,6 +97,8 @@ def _declare(lib: C.CDLL) -> None:
     lib.b200_abi_version.restype = C.c_int
     lib.b200_launch_count.restype = C.c_longlong
     lib.b200_reset_launch_count.restype = None
+    lib.b200_set_pdl.restype = None
+    lib.b200_set_pdl.argtypes = [C.c_int]
     if hasattr(lib, "b200_attention_bwd_scratch_bytes"):
         lib.b200_attention_bwd_scratch_bytes.restype = C.c_longlong
         lib.b200_attention_bwd_scratch_bytes.argtypes = [C.c_int, C.c_int, C.c_int]
@@ -177,3 +179,8 @@ def launch_count() -> int:
 
 def reset_launch_count() -> None:
     lib().b200_reset_launch_count()
+
+
+def set_pdl(mode: int) -> None:
+    """1 / 0 forces programmatic dependent launch on / off for later launches, -1 restores the default."""
+    lib().b200_set_pdl(int(mode))
