@@ -100,10 +100,25 @@ __device__ __forceinline__ TileCoord tile_coord(const GemmDev& p, int tile, int 
 
 __device__ __forceinline__ float bf16_bits_to_f(uint32_t v) { return __uint_as_float(v << 16); }
 
-template <int BN, int KIND>
+// Explicit shared-space accesses for the epilogue staging buffer: through a plain pointer the
+// compiler emits generic LD.E/ST.E (64-bit addresses, generic-path latency) because it cannot
+// prove the address space.
+__device__ __forceinline__ void sts_f32x4(uint32_t addr, float4 v) {
+  asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ float4 lds_f32x4(uint32_t addr) {
+  float4 v;
+  // volatile keeps it ordered after the staging stores / __syncwarp; no "memory" clobber, so kernel
+  // parameters are not re-read from the constant bank after every load
+  asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+  return v;
+}
+
+template <int BN, int KIND, bool DBIAS>
 __device__ __forceinline__ void epilogue_tile_fast(const GemmDev& p, int row_base, int col_base, int n_limit, uint32_t taddr,
                                                    float* stage, int lane) {
   constexpr int CHUNKS = BN / 64;
+  const uint32_t stage_s = smem_u32(stage);
   constexpr bool HAS_BIAS = KIND == EPI_BIAS || KIND == EPI_BIAS_RESID || KIND == EPI_BIAS_GELU_PRE;
   const int lrow = lane >> 3, lchunk = lane & 7;
   if (row_base >= p.M || col_base >= n_limit) return;   // warp-uniform
@@ -138,7 +153,7 @@ __device__ __forceinline__ void epilogue_tile_fast(const GemmDev& p, int row_bas
     for (int j = 0; j < 8; ++j) {
       float4 v4 = make_float4(__uint_as_float(r[j * 4 + 0]), __uint_as_float(r[j * 4 + 1]),
                               __uint_as_float(r[j * 4 + 2]), __uint_as_float(r[j * 4 + 3]));
-      *reinterpret_cast<float4*>(stage + lane * 32 + ((j ^ (lane & 7)) << 2)) = v4;
+      sts_f32x4(stage_s + ((lane * 32 + ((j ^ (lane & 7)) << 2)) << 2), v4);
     }
     __syncwarp();
     if (c + 1 < CHUNKS && col0 + 32 < n_limit) tmem_ld_32x32b_x32(taddr + (c + 1) * 32, r);
@@ -173,7 +188,7 @@ __device__ __forceinline__ void epilogue_tile_fast(const GemmDev& p, int row_bas
       if (i * 4 >= rows_left) break;        // warp-uniform
       if (lr < rows_left && col_ok) {
         const size_t row = row0 + i * 4;
-        const float4 a4 = *reinterpret_cast<const float4*>(stage + lr * 32 + ((lchunk ^ (lr & 7)) << 2));
+        const float4 a4 = lds_f32x4(stage_s + ((lr * 32 + ((lchunk ^ (lr & 7)) << 2)) << 2));
         float v0 = a4.x * alpha + b0, v1 = a4.y * alpha + b1, v2 = a4.z * alpha + b2, v3 = a4.w * alpha + b3;
         if (KIND == EPI_BIAS_GELU_PRE) {
           __nv_bfloat162 t0 = __floats2bfloat162_rn(v0, v1), t1 = __floats2bfloat162_rn(v2, v3);
@@ -208,12 +223,14 @@ __device__ __forceinline__ void epilogue_tile_fast(const GemmDev& p, int row_bas
           __nv_bfloat162 t0 = __floats2bfloat162_rn(v0, v1), t1 = __floats2bfloat162_rn(v2, v3);
           *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.d) + row * p.ldd + col) =
               make_uint2(*reinterpret_cast<uint32_t*>(&t0), *reinterpret_cast<uint32_t*>(&t1));
-          cs0 += __bfloat162float(t0.x); cs1 += __bfloat162float(t0.y);
-          cs2 += __bfloat162float(t1.x); cs3 += __bfloat162float(t1.y);
+          if (DBIAS) {
+            cs0 += __bfloat162float(t0.x); cs1 += __bfloat162float(t0.y);
+            cs2 += __bfloat162float(t1.x); cs3 += __bfloat162float(t1.y);
+          }
         }
       }
     }
-    if (KIND != EPI_PLAIN_F32 && p.dbias != nullptr) {   // warp-uniform
+    if (KIND != EPI_PLAIN_F32 && DBIAS) {
       // lanes l, l^8, l^16, l^24 hold the same four columns for different rows
       cs0 += __shfl_xor_sync(0xffffffffu, cs0, 8);  cs1 += __shfl_xor_sync(0xffffffffu, cs1, 8);
       cs2 += __shfl_xor_sync(0xffffffffu, cs2, 8);  cs3 += __shfl_xor_sync(0xffffffffu, cs3, 8);
@@ -396,13 +413,22 @@ __device__ __forceinline__ void epilogue_tile(const GemmDev& p, int row_base, in
 template <int BN>
 __device__ __forceinline__ void epilogue_dispatch(const GemmDev& p, int row_base, int col_base, int n_limit, uint32_t taddr,
                                                   float* stage, const uint64_t* seed_tab, uint64_t seed, int lane) {
+  // the column-sum (bias gradient) by-product is only wanted by the backward GEMMs: keep it out of
+  // the instruction stream of the forward ones (it is ~20% of a plain epilogue)
+  const bool db = p.dbias != nullptr;
   switch (p.epi_kind) {
-    case EPI_PLAIN: epilogue_tile_fast<BN, EPI_PLAIN>(p, row_base, col_base, n_limit, taddr, stage, lane); break;
-    case EPI_PLAIN_F32: epilogue_tile_fast<BN, EPI_PLAIN_F32>(p, row_base, col_base, n_limit, taddr, stage, lane); break;
-    case EPI_BIAS: epilogue_tile_fast<BN, EPI_BIAS>(p, row_base, col_base, n_limit, taddr, stage, lane); break;
-    case EPI_BIAS_RESID: epilogue_tile_fast<BN, EPI_BIAS_RESID>(p, row_base, col_base, n_limit, taddr, stage, lane); break;
-    case EPI_BIAS_GELU_PRE: epilogue_tile_fast<BN, EPI_BIAS_GELU_PRE>(p, row_base, col_base, n_limit, taddr, stage, lane); break;
-    case EPI_BWD_GELU: epilogue_tile_fast<BN, EPI_BWD_GELU>(p, row_base, col_base, n_limit, taddr, stage, lane); break;
+    case EPI_PLAIN:
+      if (db) epilogue_tile_fast<BN, EPI_PLAIN, true>(p, row_base, col_base, n_limit, taddr, stage, lane);
+      else epilogue_tile_fast<BN, EPI_PLAIN, false>(p, row_base, col_base, n_limit, taddr, stage, lane);
+      break;
+    case EPI_PLAIN_F32: epilogue_tile_fast<BN, EPI_PLAIN_F32, false>(p, row_base, col_base, n_limit, taddr, stage, lane); break;
+    case EPI_BIAS: epilogue_tile_fast<BN, EPI_BIAS, false>(p, row_base, col_base, n_limit, taddr, stage, lane); break;
+    case EPI_BIAS_RESID: epilogue_tile_fast<BN, EPI_BIAS_RESID, false>(p, row_base, col_base, n_limit, taddr, stage, lane); break;
+    case EPI_BIAS_GELU_PRE: epilogue_tile_fast<BN, EPI_BIAS_GELU_PRE, false>(p, row_base, col_base, n_limit, taddr, stage, lane); break;
+    case EPI_BWD_GELU:
+      if (db) epilogue_tile_fast<BN, EPI_BWD_GELU, true>(p, row_base, col_base, n_limit, taddr, stage, lane);
+      else epilogue_tile_fast<BN, EPI_BWD_GELU, false>(p, row_base, col_base, n_limit, taddr, stage, lane);
+      break;
     default: epilogue_tile<BN>(p, row_base, col_base, n_limit, taddr, stage, seed_tab, seed, lane); break;
   }
 }
@@ -1011,6 +1037,9 @@ extern "C" int b200_gemm_bf16(const b200_gemm_args* args, void* stream) {
         kind = EPI_BIAS_GELU_PRE;
       }
     }
+    // the specialised epilogues produce the bias-gradient column sums only where a backward pass asks
+    // for them (plain and GELU' dgrad); any other combination goes through the generic epilogue
+    if (a.dbias != nullptr && kind != EPI_PLAIN && kind != EPI_BWD_GELU) kind = EPI_GENERIC;
     dev.epi_kind = kind;
   }
   int bn = a.block_n;
