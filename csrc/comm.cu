@@ -99,7 +99,7 @@ fused_reduce_adamw_kernel(const CommDev c, const b200_seg* __restrict__ segs, in
                           float* __restrict__ p_local, __nv_bfloat16* __restrict__ bf16_local,
                           float* __restrict__ m, float* __restrict__ v, const b200_adamw_hparams hp,
                           const int32_t* __restrict__ step_count, const float* __restrict__ step_metrics,
-                          float* __restrict__ metrics_acc, int nmetrics) {
+                          float* __restrict__ metrics_acc, int nmetrics, const b200_step_end end) {
   pdl_sync();
   // metrics: every rank drops its partial sums into every peer's signal buffer before the barrier
   if (blockIdx.x == 0 && step_metrics != nullptr && c.world > 1) {
@@ -242,6 +242,17 @@ fused_reduce_adamw_kernel(const CommDev c, const b200_seg* __restrict__ segs, in
   }
   __threadfence_system();
   cross_rank_barrier(c, 1);
+  // End-of-step bookkeeping folded into the last update of the step: the block that finishes last
+  // (self-resetting counter) advances the RNG key and the step counter. Every block read the step
+  // counter long before it got here, and nothing in this kernel reads the key.
+  if (end.done_word != nullptr && threadIdx.x == 0) {
+    __threadfence();
+    if (atomicInc(end.done_word, gridDim.x - 1) == gridDim.x - 1) {
+      const uint64_t k = *end.rng_key;
+      *end.rng_key = mix64(k ^ end.salt_next);
+      *end.step_count += 1;
+    }
+  }
 }
 
 // All-gather by peer loads: for every segment and every rank p, `rows` rows of `row_bytes` bytes are
@@ -334,6 +345,23 @@ extern "C" int b200_fused_reduce_adamw(const b200_comm_ctx* ctx, const b200_seg*
                                        const b200_adamw_hparams* hp, int32_t* step_count, int bump_step,
                                        const float* step_metrics, float* metrics_acc, int nmetrics,
                                        int blocks, void* stream) {
+  return b200_fused_reduce_adamw_end(ctx, segs_dev, nseg, broadcast, p_local, bf16_local, m, v, hp, step_count, bump_step,
+                                     step_metrics, metrics_acc, nmetrics, blocks, nullptr, stream);
+}
+
+extern "C" int b200_fused_reduce_adamw_end(const b200_comm_ctx* ctx, const b200_seg* segs_dev, int nseg,
+                                           int broadcast, float* p_local, void* bf16_local, float* m, float* v,
+                                           const b200_adamw_hparams* hp, int32_t* step_count, int bump_step,
+                                           const float* step_metrics, float* metrics_acc, int nmetrics,
+                                           int blocks, const b200_step_end* end, void* stream) {
+  b200_step_end e;
+  memset(&e, 0, sizeof(e));
+  if (end != nullptr) {
+    e = *end;
+    B200_REQUIRE(e.rng_key != nullptr && e.step_count != nullptr && e.done_word != nullptr,
+                 "comm: step_end needs rng_key, step_count and a zero-initialised done_word");
+    B200_REQUIRE(!bump_step, "comm: bump_step and step_end both advance the step counter");
+  }
   CommDev d;
   int rc = fill_ctx(ctx, &d);
   if (rc) return rc;
@@ -354,7 +382,7 @@ extern "C" int b200_fused_reduce_adamw(const b200_comm_ctx* ctx, const b200_seg*
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   B200_CUDA(launch_k(fused_reduce_adamw_kernel, dim3(blocks), dim3(256), 0, s, d, segs_dev, nseg, broadcast, p_local,
                                                    static_cast<__nv_bfloat16*>(bf16_local), m, v, *hp,
-                                                   step_count, step_metrics, metrics_acc, nmetrics));
+                                                   step_count, step_metrics, metrics_acc, nmetrics, e));
   if (bump_step) {
     B200_CUDA(launch_k(bump_step_kernel2, dim3(1), dim3(1), 0, s, step_count));
   }

@@ -16,7 +16,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 14
+#define B200_ABI_VERSION 15
 
 const char* b200_last_error(void);
 int b200_abi_version(void);
@@ -282,6 +282,21 @@ int b200_fused_reduce_adamw(const b200_comm_ctx* ctx, const b200_seg* segs_dev, 
                             const b200_adamw_hparams* hp, int32_t* step_count, int bump_step,
                             const float* step_metrics, float* metrics_acc, int nmetrics,
                             int blocks, void* stream);
+/* Same, with the end-of-step bookkeeping folded in (one launch less per step): the thread block
+ * that finishes last sets *rng_key = mix64(*rng_key ^ salt_next) (what b200_rng_split_bump does)
+ * and increments *step_count. done_word: a device uint32 that is 0 before the first call; the
+ * kernel leaves it at 0. end == NULL behaves like b200_fused_reduce_adamw. */
+typedef struct b200_step_end {
+  uint64_t* rng_key;
+  uint64_t salt_next;
+  int32_t* step_count;
+  uint32_t* done_word;
+} b200_step_end;
+int b200_fused_reduce_adamw_end(const b200_comm_ctx* ctx, const b200_seg* segs_dev, int nseg,
+                                int broadcast, float* p_local, void* bf16_local, float* m, float* v,
+                                const b200_adamw_hparams* hp, int32_t* step_count, int bump_step,
+                                const float* step_metrics, float* metrics_acc, int nmetrics,
+                                int blocks, const b200_step_end* end, void* stream);
 /* All-gather through peer loads (no collective launch): for every segment and every rank p, `rows`
  * rows of `row_bytes` bytes are read from peer_base[p] + src_off (row pitch src_pitch) and written
  * to dst + dst_off + p*peer_stride (row pitch dst_pitch). Row shards: rows = 1 and peer_stride =

@@ -513,9 +513,24 @@ class FusedEngine:
 
     def _end_step(self, next_rng) -> None:
         """state.rng <- rebase(next_rng) (the salt folds into the device-resident key in place) and
-        step counter += 1, one launch."""
-        K.rng_split_bump_(self.rng_base, _rng.salt_word(next_rng), self.step_count)
+        step counter += 1. Normally this rides on the step's last fused update (``_fold_end``); if no
+        update consumed it, it is one small launch."""
+        if self._end_folded:
+            self._end_folded = False
+        else:
+            K.rng_split_bump_(self.rng_base, _rng.salt_word(next_rng), self.step_count)
+        self._end_salt = None
         self.release_gathered()
+
+    _end_salt = None
+    _end_folded = False
+
+    def _fold_end(self, next_rng) -> None:
+        """Call before the step's last ``_sync_bucket(..., last=True)``: that launch then also advances
+        the RNG key and the step counter (the block that finishes last does it)."""
+        if not hasattr(self, "_done_word"):
+            self._done_word = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self._end_salt = _rng.salt_word(next_rng)
 
     def _sync_bucket(self, b: int, last: bool) -> None:
         """Fused reduce + mean + AdamW + publish of one gradient bucket (one launch)."""
@@ -524,12 +539,17 @@ class FusedEngine:
                           self.hp["weight_decay"], 1.0 / (self.num_minibatches * self.world))
         nmet = len(self.metric_names)
         dp = self.mode == "dp"
-        _lib.check(_lib.lib().b200_fused_reduce_adamw(
+        end = None
+        if last and self._end_salt is not None:
+            end = _lib.StepEnd(self.rng_base.data_ptr(), self._end_salt, self.step_count.data_ptr(), self._done_word.data_ptr())
+            self._end_folded = True
+        _lib.check(_lib.lib().b200_fused_reduce_adamw_end(
             C.byref(self.ctx), segs.data_ptr(), nseg, int(dp),
             None if dp else self.p_loc.data_ptr(), None if dp else self.pb.data_ptr(),
-            self.m.data_ptr(), self.v.data_ptr(), C.byref(hp), self.step_count.data_ptr(), 0,   # bumped by _end_step
+            self.m.data_ptr(), self.v.data_ptr(), C.byref(hp), self.step_count.data_ptr(), 0,   # bumped by the end record / _end_step
             self.step_metrics.data_ptr() if last else None, self.metrics_acc.data_ptr() if last else None,
-            nmet if last else 0, self.comm_blocks, torch.cuda.current_stream().cuda_stream))
+            nmet if last else 0, self.comm_blocks, C.byref(end) if end is not None else None,
+            torch.cuda.current_stream().cuda_stream))
 
     def _sync_bucket_async(self, b: int) -> None:
         """Launches bucket ``b``'s fused update on the side stream, after everything already

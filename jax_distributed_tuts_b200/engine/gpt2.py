@@ -157,6 +157,7 @@ class GPT2Engine(FusedEngine):
             sl = slice(i * self.mbB, (i + 1) * self.mbB)
             self._forward(self.tokens[sl])
             self._backward(self.tokens[sl], self.targets[sl], accumulate=i > 0, last=i == nmb - 1)
+        self._fold_end(next_rng)
         if self.overlap:
             torch.cuda.current_stream().wait_stream(self.side_stream)
             self._sync_bucket(self.L, last=True)

@@ -68,6 +68,7 @@ class MLPEngine(FusedEngine):
         # a sub-megabyte model: one fused reduce+update launch (two cross-GPU barriers) beats two
         # overlapped launches (four barriers); bucket-level overlap pays off from a few MB per bucket
         self.overlap = self.overlap and self.layout.total * 4 > (8 << 20)
+        self.fork_wgrad = (not self.overlap) and self.fuse_minibatches
         b1, b2 = self.layout.leaves["input_dense/bias"], self.layout.leaves["output_dense/bias"]
         self._vec_grads = self.g32[b1.offset: b2.offset + b2.ld]
         d = self.device
@@ -119,10 +120,13 @@ class MLPEngine(FusedEngine):
             for i in range(nmb):
                 self._fwd_bwd(xb[i * mb:(i + 1) * mb], self.labels[i * mb:(i + 1) * mb], [salts[i]], mb,
                               accumulate=i > 0, last=i == nmb - 1)
+        self._fold_end(next_rng)
         if self.overlap:
             torch.cuda.current_stream().wait_stream(self.side_stream)
             self._sync_bucket(1, last=True)
         else:
+            if self.fork_wgrad:
+                torch.cuda.current_stream().wait_stream(self.side_stream)     # join: output layer's weight gradient
             self._sync_all_buckets()
         self._end_step(next_rng)
 
@@ -135,7 +139,15 @@ class MLPEngine(FusedEngine):
         self.gemm_w(self.h, "output_dense/kernel", logits, bias=self.vec("output_dense/bias"))
         K.softmax_xent(logits, lab, grad_scale=1.0 / self.mb, dlogits=dlogits, metrics=self.step_metrics,
                        dbias=self.grad1d("output_dense/bias"))
-        K.gemm(self.h, dlogits, self.grad2d("output_dense/kernel"), a_mn=True, b_mn=True, accumulate=accumulate)
+        if self.fork_wgrad:
+            # dW2 only depends on h and dlogits: in a latency-bound step it runs as a parallel branch of
+            # the graph next to the dgrad -> dW1 chain instead of in front of it
+            main = torch.cuda.current_stream()
+            self.side_stream.wait_stream(main)
+            with torch.cuda.stream(self.side_stream):
+                K.gemm(self.h, dlogits, self.grad2d("output_dense/kernel"), a_mn=True, b_mn=True, accumulate=accumulate)
+        else:
+            K.gemm(self.h, dlogits, self.grad2d("output_dense/kernel"), a_mn=True, b_mn=True, accumulate=accumulate)
         if last and self.overlap:
             self._sync_bucket_async(0)   # output layer's matrix: reduce + update under the rest of the backward
         self.gemm_wT(dlogits, "output_dense/kernel", self.dpre, bwd=True, aux=self.pre, act="silu",

@@ -12,7 +12,7 @@ from typing import Optional
 
 from . import _build
 
-ABI_VERSION = 14
+ABI_VERSION = 15
 
 _lib: Optional[C.CDLL] = None
 
@@ -55,6 +55,13 @@ class AdamWHParams(C.Structure):
     _fields_ = [
         ("lr", C.c_float), ("beta1", C.c_float), ("beta2", C.c_float),
         ("eps", C.c_float), ("weight_decay", C.c_float), ("grad_scale", C.c_float),
+    ]
+
+
+class StepEnd(C.Structure):
+    _fields_ = [
+        ("rng_key", C.c_void_p), ("salt_next", C.c_uint64),
+        ("step_count", C.c_void_p), ("done_word", C.c_void_p),
     ]
 
 
@@ -128,6 +135,8 @@ def _declare(lib: C.CDLL) -> None:
         "b200_attention_bwd": [vp, vp, vp, vp, vp, vp, i32, i32, i32, vp],
         "b200_fused_reduce_adamw": [C.POINTER(CommCtx), vp, i32, i32, vp, vp, vp, vp,
                                     C.POINTER(AdamWHParams), vp, i32, vp, vp, i32, i32, vp],
+        "b200_fused_reduce_adamw_end": [C.POINTER(CommCtx), vp, i32, i32, vp, vp, vp, vp,
+                                        C.POINTER(AdamWHParams), vp, i32, vp, vp, i32, i32, C.POINTER(StepEnd), vp],
         "b200_signal_barrier": [C.POINTER(CommCtx), vp],
         "b200_peer_gather": [C.POINTER(C.c_void_p), i32, vp, i32, vp, i32, vp],
     }
