@@ -51,12 +51,15 @@ struct GemmDev {
   int epi_kind;                          // EPI_*: compile-time specialised epilogue, or EPI_GENERIC
   int k_splits, atomic_out;              // split-K: tile index also selects a K range; partials are red.add-ed
   float* dbias;                          // column sums of the stored output, added atomically (or null)
+  const int64_t* xent_labels;            // EPI_XENT: integer labels, metrics {loss sum, #correct}, gradient scale
+  float* xent_metrics;
+  float xent_scale;
 };
 
 // Specialised epilogues (fully vectorised, no run-time feature tests in the inner loop). Anything
 // else - dropout, SiLU, odd alignments, partial 4-column groups - takes EPI_GENERIC.
 enum { EPI_GENERIC = 0, EPI_PLAIN = 1, EPI_PLAIN_F32 = 2, EPI_BIAS = 3, EPI_BIAS_RESID = 4, EPI_BIAS_GELU_PRE = 5,
-       EPI_BWD_GELU = 6 };
+       EPI_BWD_GELU = 6, EPI_XENT = 7 };
 
 template <int BN>
 struct GemmCfg {
@@ -244,6 +247,57 @@ __device__ __forceinline__ void epilogue_tile_fast(const GemmDev& p, int row_bas
   tmem_ld_wait();
 }
 
+// Classifier head with at most 32 classes: the accumulator row of a sample sits in one thread
+// (TMEM lane = row), so softmax, loss, accuracy and dlogits are computed in registers right here and
+// the logits never go to memory. Only the warps that hold columns [0, 32) take part.
+__device__ __noinline__ void epilogue_tile_xent(const GemmDev& p, int row_base, int col_base, uint32_t taddr, float* stage,
+                                                int lane) {
+  if (col_base != 0 || row_base >= p.M) return;   // warp-uniform
+  // Deliberately compact code (rolled loops over the classes, row parked in the warp's staging
+  // buffer): this runs once per step in a launch-latency-bound chain, where instruction fetch of a
+  // fully unrolled 32-class version from a cold cache costs more than the arithmetic.
+  uint32_t r[32];
+  tmem_ld_32x32b_x32(taddr, r);
+  tmem_ld_wait();
+  float* mine = stage + lane * 32;                // element j of this lane's row lives at (j ^ lane): conflict-free
+#pragma unroll
+  for (int j = 0; j < 32; ++j) mine[j ^ lane] = __uint_as_float(r[j]);
+  __syncwarp();
+  const int row = row_base + lane;
+  const bool live = row < p.M;
+  const int nc = p.N;
+  const int label = live ? static_cast<int>(p.xent_labels[row]) : 0;
+  float m = -INFINITY, l_label = 0.f;
+  int amax = 0;
+#pragma unroll 1
+  for (int j = 0; j < nc; ++j) {
+    const float v = mine[j ^ lane] * p.alpha + (p.bias != nullptr ? __bfloat162float(p.bias[j]) : 0.f);
+    mine[j ^ lane] = v;
+    if (v > m) { m = v; amax = j; }               // strict: the first maximum wins
+    if (j == label) l_label = v;
+  }
+  float ssum = 0.f;
+#pragma unroll 1
+  for (int j = 0; j < nc; ++j) ssum += __expf(mine[j ^ lane] - m);
+  const float inv = 1.0f / ssum;
+  __nv_bfloat16* drow = reinterpret_cast<__nv_bfloat16*>(p.d) + static_cast<size_t>(row) * p.ldd;
+#pragma unroll 1
+  for (int j = 0; j < nc; ++j) {
+    const __nv_bfloat16 g = __float2bfloat16_rn((__expf(mine[j ^ lane] - m) * inv - (j == label ? 1.0f : 0.f)) * p.xent_scale);
+    if (live) drow[j] = g;
+    if (p.dbias != nullptr) {
+      const float cs = warp_sum(live ? __bfloat162float(g) : 0.f);
+      if (lane == 0) atomicAdd(&p.dbias[j], cs);
+    }
+  }
+  const float loss = warp_sum(live ? (m + __logf(ssum) - l_label) : 0.f);
+  const float corr = warp_sum((live && amax == label) ? 1.0f : 0.f);
+  if (lane == 0 && p.xent_metrics != nullptr) {
+    atomicAdd(&p.xent_metrics[0], loss);
+    atomicAdd(&p.xent_metrics[1], corr);
+  }
+}
+
 // Dispatch once per tile on the epilogue kind (uniform across the kernel).
 template <int BN>
 __device__ __forceinline__ void epilogue_dispatch(const GemmDev& p, int row_base, int col_base, int n_limit, uint32_t taddr,
@@ -429,6 +483,7 @@ __device__ __forceinline__ void epilogue_dispatch(const GemmDev& p, int row_base
       if (db) epilogue_tile_fast<BN, EPI_BWD_GELU, true>(p, row_base, col_base, n_limit, taddr, stage, lane);
       else epilogue_tile_fast<BN, EPI_BWD_GELU, false>(p, row_base, col_base, n_limit, taddr, stage, lane);
       break;
+    case EPI_XENT: epilogue_tile_xent(p, row_base, col_base, taddr, stage, lane); break;
     default: epilogue_tile<BN>(p, row_base, col_base, n_limit, taddr, stage, seed_tab, seed, lane); break;
   }
 }
@@ -1040,6 +1095,12 @@ extern "C" int b200_gemm_bf16(const b200_gemm_args* args, void* stream) {
     // the specialised epilogues produce the bias-gradient column sums only where a backward pass asks
     // for them (plain and GELU' dgrad); any other combination goes through the generic epilogue
     if (a.dbias != nullptr && kind != EPI_PLAIN && kind != EPI_BWD_GELU) kind = EPI_GENERIC;
+    if (a.xent_labels != nullptr) {
+      B200_REQUIRE(a.n <= 32 && !a.bwd && !a.d_fp32 && a.act == B200_ACT_NONE && a.pre == nullptr && a.resid == nullptr &&
+                       dev.drop_key == nullptr && a.b_shard_mode != 2 && !a.accumulate,
+                   "gemm: the fused cross-entropy epilogue needs n <= 32, a bf16 output and a plain forward product");
+      kind = EPI_XENT;
+    }
     dev.epi_kind = kind;
   }
   int bn = a.block_n;
@@ -1081,6 +1142,9 @@ extern "C" int b200_gemm_bf16(const b200_gemm_args* args, void* stream) {
   dev.k_splits = 1;
   dev.atomic_out = 0;
   dev.dbias = a.dbias;
+  dev.xent_labels = a.xent_labels;
+  dev.xent_metrics = a.xent_metrics;
+  dev.xent_scale = a.xent_scale;
   B200_REQUIRE(a.dbias == nullptr || (!a.d_fp32 && (reinterpret_cast<uintptr_t>(a.dbias) & 15) == 0),
                "gemm: dbias needs a bf16 output and a 16-byte aligned fp32 vector");
   if (dev.epi_kind == EPI_PLAIN_F32 && a.b_shard_mode != 1 && a.split_k != 1) {

@@ -16,7 +16,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 15
+#define B200_ABI_VERSION 16
 
 const char* b200_last_error(void);
 int b200_abi_version(void);
@@ -99,6 +99,15 @@ typedef struct b200_gemm_args {
    * aligned, caller zeroes it). Lets a dgrad GEMM emit the bias gradient of the layer it feeds
    * without a separate pass over D. NULL = off. */
   float* dbias;
+  /* Softmax cross-entropy fused into the epilogue of a classifier head with n <= 32 classes (the
+   * reference's Dense(num_classes) -> optax.softmax_cross_entropy_with_integer_labels,
+   * data_paral.py:150-167): D receives dlogits = (softmax(A*B + bias) - onehot(label)) * xent_scale
+   * as bf16 instead of the logits, xent_metrics[0] += sum of the row losses, xent_metrics[1] +=
+   * number of rows whose argmax is the label, and dbias (if given) the column sums of the stored
+   * dlogits. Forward only, no activation / dropout / residual. NULL labels = off. */
+  const int64_t* xent_labels;
+  float* xent_metrics;
+  float xent_scale;
 } b200_gemm_args;
 
 int b200_gemm_bf16(const b200_gemm_args* args, void* stream);

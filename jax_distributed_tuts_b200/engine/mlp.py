@@ -1,26 +1,27 @@
 """Fused engine for the reference's MLP classifier in data-parallel and FSDP modes.
 
-The schedule per row block (a minibatch, or all minibatches of the step folded together) is
-eight launches, all ours (reference: util.py:58-75 around data_paral.py:171-189):
+One step (all minibatches folded into the row dimension, reference: util.py:58-75 around
+data_paral.py:171-189) is seven launches, all ours, replayed as one CUDA graph:
 
+    cast  x -> bf16, zero the step metrics and the bias-gradient vectors
     GEMM  h = dropout(silu(x W1 + b1))        bias+SiLU+dropout in the epilogue, pre-act saved
-    GEMM  logits = h W2 + b2                  fp32 out
-    xent  loss sum, #correct, dlogits         one pass
-    GEMM  dW2 (+)= h^T dlogits                accumulates straight into the flat gradient buffer
-    colsum db2 (+)= sum dlogits
-    GEMM  dpre = (dlogits W2^T) * mask/keep * silu'(pre)     backward epilogue
-    GEMM  dW1 (+)= x^T dpre
-    colsum db1 (+)= sum dpre
-
-then one fused collective+optimizer launch per gradient bucket:
+    GEMM  dlogits = xent'(h W2 + b2)          softmax cross-entropy in the epilogue (N <= 32): loss sum,
+                                              #correct, dlogits and db2 leave the kernel, logits do not
+    GEMM  dW2 = h^T dlogits                   parallel graph branch (side stream)
+    GEMM  dpre = (dlogits W2^T) * mask/keep * silu'(pre)     backward epilogue, db1 as column sums
+    GEMM  dW1 = x^T dpre
+    fused collective + optimizer + end-of-step bookkeeping (RNG key, step counter)
 
     DP   (data_paral.py:210-217)        NVLS all-reduce-mean + AdamW on the rank's slice +
-                                        multicast publish of fp32/bf16 params; bucket 0
-                                        (output layer) runs on a side stream under the rest of
-                                        the backward.
+                                        multicast publish of fp32/bf16 params. Models above 8 MB
+                                        use one launch per bucket, the output layer's on a side
+                                        stream under the rest of the backward.
     FSDP (param_sharding.py:134-140,353) the weight GEMMs read the peers' bf16 shards in place
                                         through TMA (all-gather fused into the GEMM); the
                                         reduce-scatter-mean + sharded AdamW is one launch.
+
+With more than 32 classes the head and the cross-entropy are separate launches; without
+``fuse_minibatches`` the GEMM block runs once per minibatch and accumulates.
 """
 from __future__ import annotations
 
@@ -41,7 +42,7 @@ _ORDER = ("input_dense/kernel", "input_dense/bias", "output_dense/kernel", "outp
 class MLPEngine(FusedEngine):
     def __init__(self, config, mesh: Mesh, *, mode: str = "dp", batch_per_rank: int, lr: float,
                  num_minibatches: int = 4, min_weight_size: int = 2 ** 18, init_params: Optional[Dict] = None,
-                 input_size: int = 784, fuse_minibatches: bool = True, **kw):
+                 input_size: int = 784, fuse_minibatches: bool = True, fuse_xent: bool = True, **kw):
         if kw.get("fsdp_weights", "auto") == "auto":   # few row tiles per GEMM: read the peers' shards from inside the GEMM
             kw["fsdp_weights"] = "fused" if batch_per_rank <= 1024 else "gather"
         super().__init__(mesh, mode=mode, lr=lr, num_minibatches=num_minibatches,
@@ -69,6 +70,7 @@ class MLPEngine(FusedEngine):
         # overlapped launches (four barriers); bucket-level overlap pays off from a few MB per bucket
         self.overlap = self.overlap and self.layout.total * 4 > (8 << 20)
         self.fork_wgrad = (not self.overlap) and self.fuse_minibatches
+        self.fuse_xent = fuse_xent
         b1, b2 = self.layout.leaves["input_dense/bias"], self.layout.leaves["output_dense/bias"]
         self._vec_grads = self.g32[b1.offset: b2.offset + b2.ld]
         d = self.device
@@ -136,9 +138,15 @@ class MLPEngine(FusedEngine):
         dlogits = self.dlogits[:, : self.Cn]
         drop = dict(drop_key=self.rng_base, drop_rate=self.rate, drop_salts=salts, drop_rows_per_salt=rows_per_salt)
         self.gemm_w(xs, "input_dense/kernel", self.h, bias=self.vec("input_dense/bias"), act="silu", pre=self.pre, **drop)
-        self.gemm_w(self.h, "output_dense/kernel", logits, bias=self.vec("output_dense/bias"))
-        K.softmax_xent(logits, lab, grad_scale=1.0 / self.mb, dlogits=dlogits, metrics=self.step_metrics,
-                       dbias=self.grad1d("output_dense/bias"))
+        w2_shard = self._weight("output_dense/kernel")[2]
+        if self.fuse_xent and self.Cn <= 32 and not (w2_shard is not None and w2_shard[0]):     # not for a class-sharded head
+            # head + softmax cross-entropy + its bias gradient in one launch: the logits stay in TMEM
+            self.gemm_w(self.h, "output_dense/kernel", dlogits, bias=self.vec("output_dense/bias"), xent_labels=lab,
+                        xent_metrics=self.step_metrics, xent_scale=1.0 / self.mb, dbias=self.grad1d("output_dense/bias"))
+        else:
+            self.gemm_w(self.h, "output_dense/kernel", logits, bias=self.vec("output_dense/bias"))
+            K.softmax_xent(logits, lab, grad_scale=1.0 / self.mb, dlogits=dlogits, metrics=self.step_metrics,
+                           dbias=self.grad1d("output_dense/bias"))
         if self.fork_wgrad:
             # dW2 only depends on h and dlogits: in a latency-bound step it runs as a parallel branch of
             # the graph next to the dgrad -> dW1 chain instead of in front of it

@@ -12,7 +12,7 @@ from typing import Optional
 
 from . import _build
 
-ABI_VERSION = 15
+ABI_VERSION = 16
 
 _lib: Optional[C.CDLL] = None
 
@@ -48,6 +48,9 @@ class GemmArgs(C.Structure):
         ("pair_mode", C.c_int32),
         ("split_k", C.c_int32),
         ("dbias", C.c_void_p),
+        ("xent_labels", C.c_void_p),
+        ("xent_metrics", C.c_void_p),
+        ("xent_scale", C.c_float),
     ]
 
 

@@ -59,6 +59,9 @@ def gemm(
     pair_mode: int = 0,
     split_k: int = 0,
     dbias: Optional[torch.Tensor] = None,
+    xent_labels: Optional[torch.Tensor] = None,
+    xent_metrics: Optional[torch.Tensor] = None,
+    xent_scale: float = 1.0,
 ) -> torch.Tensor:
     """``out (+)= epilogue(A @ B)`` on tcgen05 (see ``include/b200dist.h`` for the layouts).
 
@@ -66,6 +69,10 @@ def gemm(
     [K,N] (``b_mn=True``). ``b`` may be a list of shard tensors or raw device pointers (peer
     memory); then ``b_shape`` is the logical (rows, cols) of the *whole* B in its storage
     orientation and ``ldb`` its row pitch.
+
+    ``xent_labels`` (int64 [M]) turns a classifier head with N <= 32 classes into head + softmax
+    cross-entropy in one launch: ``out`` (bf16) receives ``dlogits`` scaled by ``xent_scale``,
+    ``xent_metrics[0:2]`` accumulates (loss sum, #correct), ``dbias`` the column sums of ``dlogits``.
     """
     args = GemmArgs()
     assert a.dtype == torch.bfloat16 and a.is_cuda
@@ -125,6 +132,11 @@ def gemm(
     if dbias is not None:
         assert dbias.dtype == torch.float32 and dbias.numel() >= n
         args.dbias = dbias.data_ptr()
+    if xent_labels is not None:
+        assert xent_labels.dtype == torch.int64 and xent_labels.numel() >= m and out.dtype == torch.bfloat16
+        args.xent_labels = xent_labels.data_ptr()
+        args.xent_metrics = _ptr(xent_metrics)
+        args.xent_scale = float(xent_scale)
     _lib.check(_lib.lib().b200_gemm_bf16(C.byref(args), _stream()))
     return out
 

@@ -7,7 +7,7 @@ from tools import gpu_check_kernels as G
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("group", ["gemm_kmajor", "gemm_mnmajor", "gemm_epilogue", "gemm_sharded", "elementwise", "transformer", "attention"])
+@pytest.mark.parametrize("group", ["gemm_kmajor", "gemm_mnmajor", "gemm_epilogue", "gemm_xent", "gemm_sharded", "elementwise", "transformer", "attention"])
 def test_kernel_group(group):
     import torch
     assert getattr(G, "group_" + group)()

@@ -15,7 +15,7 @@ import time
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
-GROUPS = ["gemm_kmajor", "gemm_mnmajor", "gemm_epilogue", "gemm_sharded", "elementwise", "transformer",
+GROUPS = ["gemm_kmajor", "gemm_mnmajor", "gemm_epilogue", "gemm_xent", "gemm_sharded", "elementwise", "transformer",
           "attention", "gemm_perf", "gemm_epi_perf"]
 
 
@@ -206,6 +206,34 @@ def group_gemm_epilogue():
     same = ((out2 != 0) == kept).float().mean().item()
     print(f"  masks with different salt agree on {same:.3f} of elements (want ~0.82)")
     ok &= same < 0.9
+    return ok
+
+
+def group_gemm_xent():
+    """Classifier head + softmax cross-entropy in one GEMM launch vs. PyTorch fp32."""
+    import torch
+    import torch.nn.functional as F
+    from jax_distributed_tuts_b200.ops import kernels as K
+    ok = True
+    torch.manual_seed(9)
+    for (m, k, n) in [(16, 512, 10), (200, 784, 32), (130, 64, 3)]:
+        x = torch.randn(m, k, device="cuda").bfloat16()
+        ld = (n + 7) // 8 * 8
+        w = (torch.randn(k, ld, device="cuda") / k ** 0.5).bfloat16()[:, :n]
+        bias = torch.randn(n, device="cuda").bfloat16()
+        labels = torch.randint(0, n, (m,), device="cuda")
+        dl = torch.zeros(m, ld, device="cuda", dtype=torch.bfloat16)[:, :n]
+        metrics = torch.zeros(2, device="cuda")
+        db = torch.zeros(64, device="cuda")
+        scale = 1.0 / m
+        K.gemm(x, w, dl, b_mn=True, bias=bias, xent_labels=labels, xent_metrics=metrics, xent_scale=scale, dbias=db)
+        logits = (x.float() @ w.float() + bias.float()).requires_grad_(True)
+        loss = F.cross_entropy(logits, labels, reduction="sum")
+        (loss * scale).backward()
+        ok &= _report(f"xent head {m}x{k}x{n} loss sum", abs(metrics[0].item() - loss.item()) / max(1.0, loss.item()), 2e-3)
+        ok &= _report("xent head correct", abs(metrics[1].item() - (logits.argmax(-1) == labels).sum().item()), 1.0)
+        ok &= _report("xent head dlogits", _rel_err(dl, logits.grad), 1.5e-2)
+        ok &= _report("xent head dbias", _rel_err(db[:n], logits.grad.sum(0)), 1.5e-2)
     return ok
 
 
