@@ -251,7 +251,7 @@ __device__ __forceinline__ void epilogue_tile_fast(const GemmDev& p, int row_bas
 // (TMEM lane = row), so softmax, loss, accuracy and dlogits are computed in registers right here and
 // the logits never go to memory. Only the warps that hold columns [0, 32) take part.
 __device__ __noinline__ void epilogue_tile_xent(const GemmDev& p, int row_base, int col_base, uint32_t taddr, float* stage,
-                                                int lane) {
+                                                int lane, int label_pre, float bias_pre) {
   if (col_base != 0 || row_base >= p.M) return;   // warp-uniform
   // Deliberately compact code (rolled loops over the classes, row parked in the warp's staging
   // buffer): this runs once per step in a launch-latency-bound chain, where instruction fetch of a
@@ -266,12 +266,12 @@ __device__ __noinline__ void epilogue_tile_xent(const GemmDev& p, int row_base, 
   const int row = row_base + lane;
   const bool live = row < p.M;
   const int nc = p.N;
-  const int label = live ? static_cast<int>(p.xent_labels[row]) : 0;
-  float m = -INFINITY, l_label = 0.f;
+  const int label = live ? label_pre : 0;         // label of this lane's row and bias[lane]: loaded before the
+  float m = -INFINITY, l_label = 0.f;             // accumulator wait, i.e. under the main loop
   int amax = 0;
 #pragma unroll 1
   for (int j = 0; j < nc; ++j) {
-    const float v = mine[j ^ lane] * p.alpha + (p.bias != nullptr ? __bfloat162float(p.bias[j]) : 0.f);
+    const float v = mine[j ^ lane] * p.alpha + __shfl_sync(0xffffffffu, bias_pre, j);
     mine[j ^ lane] = v;
     if (v > m) { m = v; amax = j; }               // strict: the first maximum wins
     if (j == label) l_label = v;
@@ -298,10 +298,23 @@ __device__ __noinline__ void epilogue_tile_xent(const GemmDev& p, int row_base, 
   }
 }
 
+// Operands of the cross-entropy epilogue that do not depend on the accumulator: fetched before
+// the wait on the accumulator so that their (cold-cache) latency hides under the main loop.
+__device__ __forceinline__ void xent_prefetch(const GemmDev& p, int row_base, int col_base, int lane, int& label_pre,
+                                              float& bias_pre) {
+  label_pre = 0;
+  bias_pre = 0.f;
+  if (p.epi_kind != EPI_XENT || col_base != 0) return;
+  const int row = row_base + lane;
+  if (row < p.M) label_pre = static_cast<int>(p.xent_labels[row]);
+  if (lane < p.N && p.bias != nullptr) bias_pre = __bfloat162float(p.bias[lane]);
+}
+
 // Dispatch once per tile on the epilogue kind (uniform across the kernel).
 template <int BN>
 __device__ __forceinline__ void epilogue_dispatch(const GemmDev& p, int row_base, int col_base, int n_limit, uint32_t taddr,
-                                                  float* stage, const uint64_t* seed_tab, uint64_t seed, int lane);
+                                                  float* stage, const uint64_t* seed_tab, uint64_t seed, int lane,
+                                                  int label_pre, float bias_pre);
 
 // Epilogue of one warp for one tile: rows [row_base, row_base+32) x columns [col_base, col_base+BN/2)
 // of the output, accumulator at TMEM address `taddr` (lane quadrant, stage and column half already
@@ -466,7 +479,8 @@ __device__ __forceinline__ void epilogue_tile(const GemmDev& p, int row_base, in
 
 template <int BN>
 __device__ __forceinline__ void epilogue_dispatch(const GemmDev& p, int row_base, int col_base, int n_limit, uint32_t taddr,
-                                                  float* stage, const uint64_t* seed_tab, uint64_t seed, int lane) {
+                                                  float* stage, const uint64_t* seed_tab, uint64_t seed, int lane,
+                                                  int label_pre, float bias_pre) {
   // the column-sum (bias gradient) by-product is only wanted by the backward GEMMs: keep it out of
   // the instruction stream of the forward ones (it is ~20% of a plain epilogue)
   const bool db = p.dbias != nullptr;
@@ -483,7 +497,7 @@ __device__ __forceinline__ void epilogue_dispatch(const GemmDev& p, int row_base
       if (db) epilogue_tile_fast<BN, EPI_BWD_GELU, true>(p, row_base, col_base, n_limit, taddr, stage, lane);
       else epilogue_tile_fast<BN, EPI_BWD_GELU, false>(p, row_base, col_base, n_limit, taddr, stage, lane);
       break;
-    case EPI_XENT: epilogue_tile_xent(p, row_base, col_base, taddr, stage, lane); break;
+    case EPI_XENT: epilogue_tile_xent(p, row_base, col_base, taddr, stage, lane, label_pre, bias_pre); break;
     default: epilogue_tile<BN>(p, row_base, col_base, n_limit, taddr, stage, seed_tab, seed, lane); break;
   }
 }
@@ -663,11 +677,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
       const int as = local & 1;
       const uint32_t aphase = (local >> 1) & 1;
       TileCoord tc = tile_coord(p, tile % mn_tiles, m_tiles, BN);
+      int label_pre;
+      float bias_pre;
+      xent_prefetch(p, tc.m0 + quad * 32, tc.n0 + half * (BN / 2), lane, label_pre, bias_pre);
       mbar_wait(&tmem_full[as], aphase);
       tc_fence_after();
       epilogue_dispatch<BN>(p, tc.m0 + quad * 32, tc.n0 + half * (BN / 2), tc.n_limit,
                         tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + as * BN + half * (BN / 2), stage, seed_tab,
-                        seed, lane);
+                        seed, lane, label_pre, bias_pre);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tmem_empty[as]);
@@ -903,11 +920,14 @@ gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
       const int as = local & 1;
       const uint32_t aphase = (local >> 1) & 1;
       TileCoord tc = coord(tile % mn_tiles);
+      int label_pre;
+      float bias_pre;
+      xent_prefetch(p, tc.m0 + static_cast<int>(rank) * BM + quad * 32, tc.n0 + half * (BN / 2), lane, label_pre, bias_pre);
       mbar_wait(&tmem_full[as], aphase);
       tc_fence_after();
       epilogue_dispatch<BN>(p, tc.m0 + static_cast<int>(rank) * BM + quad * 32, tc.n0 + half * (BN / 2), tc.n_limit,
                         tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + as * BN + half * (BN / 2), stage, seed_tab,
-                        seed, lane);
+                        seed, lane, label_pre, bias_pre);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(mapa_cluster(smem_u32(&tmem_empty[as]), 0));
