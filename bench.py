@@ -114,7 +114,7 @@ class ClockSampler:
 
 
 def run_secondary(args, rank, world, device) -> dict:
-    """DP GPT-2 small (124M), 16 x 1024 tokens per GPU, 10 timed steps, same timing rules."""
+    """DP GPT-2 small (124M), 16 x 1024 tokens per GPU, 20 timed steps, same timing rules."""
     import torch
     import torch.distributed as dist
 
@@ -124,7 +124,7 @@ def run_secondary(args, rank, world, device) -> dict:
     from jax_distributed_tuts_b200.models.gpt2 import GPT2, gpt2_config
     from jax_distributed_tuts_b200.state import Batch
 
-    steps, warm, B, T = 10, 3, 16, 1024
+    steps, warm, B, T = 20, 4, 16, 1024
     gcfg = gpt2_config("small")
     model = GPT2(gcfg)
     mesh = Mesh((world,), ("data",))
