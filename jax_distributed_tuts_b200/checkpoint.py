@@ -73,9 +73,11 @@ def state_dict(state, *, mesh: Optional[Mesh] = None) -> Dict[str, Any]:
     from .parallel.fsdp import unshard_params
     eng = getattr(state, "engine", None)
     if eng is not None:
+        # same container as the generic tiers: mu / nu shaped like the parameters, global layout
         params = eng.params_tree(gather=True)
-        opt = {"0": {"count": _to_numpy(eng.step_count).reshape(()),
-                     "mu": {"flat_slice": _to_numpy(eng.m)}, "nu": {"flat_slice": _to_numpy(eng.v)}}, "1": {}, "2": {}}
+        og = eng.opt_state_global()
+        opt = {"0": {"count": _to_numpy(og["count"]).reshape(()), "mu": _plain(og["mu"]), "nu": _plain(og["nu"])},
+               "1": {}, "2": {}}
         rng_arr = _to_numpy(eng.rng_base)
     else:
         needs_mesh = any(is_partitioned(v) for _, v in tree_leaves_with_path(state.params, is_leaf=is_partitioned))
@@ -211,3 +213,15 @@ def restore_params(template: Pytree, loaded: Dict[str, Any], *, mesh: Optional[M
 
     paths = iter([p for p, _ in tree_leaves_with_path(template, is_leaf=is_partitioned)])
     return tree_map(lambda leaf: put(next(paths), leaf), template, is_leaf=is_partitioned)
+
+
+def restore_engine(engine, loaded: Dict[str, Any]) -> None:
+    """Puts a loaded global checkpoint (``load_checkpoint``) into a fused engine: parameters,
+    Adam moments and step count (each rank keeps its slice / shard), and the RNG key. The file may
+    come from a generic-tier TrainState or from an engine of another mode or world size."""
+    import torch
+    engine.load_params(loaded["params"])
+    adam = loaded["opt_state"]["0"]
+    engine.load_opt_state_global(adam["mu"], adam["nu"], int(np.asarray(adam["count"]).reshape(-1)[0]))
+    engine.rng_base.copy_(torch.from_numpy(np.asarray(loaded["rng"]).astype(np.int64).reshape(-1)[:1]).to(engine.rng_base.device))
+    engine.steps_done = int(np.asarray(loaded["step"]).reshape(-1)[0])

@@ -388,7 +388,7 @@ class FusedEngine:
         its slice, param_sharding.py:227-241)."""
         for path, sp in self.layout.leaves.items():
             v = flat[path]
-            v = (v.value if isinstance(v, Partitioned) else v).to(self.device, dtype=torch.float32)
+            v = torch.as_tensor(v.value if isinstance(v, Partitioned) else v).to(self.device, dtype=torch.float32)   # tensors or numpy (checkpoints)
             v2 = v.reshape(sp.rows, sp.cols)
             if self.mode == "dp":
                 self.layout.view2d(self.p32, path).copy_(v2)
@@ -428,6 +428,81 @@ class FusedEngine:
                 names = tuple(self.shard_axis if i == dim else None for i in range(len(sp.shape)))
                 out[path] = Partitioned(loc, names)
         return out
+
+    # ---- optimizer state in the reference's (global, per-leaf) layout: checkpoints, inspection ----
+    def _moment_flat(self, buf: torch.Tensor) -> Dict[str, torch.Tensor]:
+        """path -> full fp32 array of an Adam moment (``buf`` is ``self.m`` or ``self.v``). DP keeps a
+        moment only for the rank's 1/world slice of every bucket (owner-update): the slices are
+        all-gathered and put back at their flat offsets. FSDP keeps it per local shard: sharded
+        leaves are all-gathered over the shard axis like the parameters. Collective: every rank calls."""
+        out: Dict[str, torch.Tensor] = {}
+        if self.mode == "dp":
+            W = self.world
+            if W == 1:
+                full = buf
+            else:
+                g = torch.empty(W, buf.numel(), dtype=buf.dtype, device=buf.device)
+                dist.all_gather_into_tensor(g.view(-1), buf.contiguous().view(-1))
+                full = torch.empty(self.layout.total, dtype=buf.dtype, device=buf.device)
+                for (b0, b1) in self.layout.bucket_ranges:
+                    sl = (b1 - b0) // W
+                    full[b0:b1].view(W, sl).copy_(g[:, b0 // W: b0 // W + sl])
+            for path in self.layout.leaves:
+                out[path] = self.layout.view(full, path).clone()
+            return out
+        from ..comm import collectives as Cc
+        for path, sp in self.layout.leaves.items():
+            loc = self._local_view(buf, path)
+            dim = self.shard_dim[path]
+            if len(sp.shape) == 1:
+                loc = loc.reshape(-1)
+            if dim is not None and self.S > 1:
+                loc = Cc.all_gather(loc.contiguous(), self.shard_axis, axis=dim, mesh=self.mesh)
+            out[path] = loc.reshape(sp.shape).clone()
+        return out
+
+    def opt_state_global(self) -> Dict[str, object]:
+        """``{"count", "mu", "nu"}`` with ``mu`` / ``nu`` shaped like the parameter tree (what
+        ``optax.adamw``'s ScaleByAdamState holds in the reference, data_paral.py:106-108), whatever
+        the engine's mode and world size. Collective."""
+        return {"count": self.step_count.clone(), "mu": self._nest(self._moment_flat(self.m)),
+                "nu": self._nest(self._moment_flat(self.v))}
+
+    def _load_moment(self, buf: torch.Tensor, flat: Dict[str, object]) -> None:
+        if self.mode == "dp":
+            full = torch.zeros(self.layout.total, dtype=torch.float32, device=self.device)
+            for path, sp in self.layout.leaves.items():
+                v = torch.as_tensor(flat[path]).to(self.device, dtype=torch.float32)
+                self.layout.view2d(full, path).copy_(v.reshape(sp.rows, sp.cols))
+            W, r = self.world, self.rank
+            for (b0, b1) in self.layout.bucket_ranges:
+                sl = (b1 - b0) // W
+                buf[b0 // W: b0 // W + sl].copy_(full[b0 + r * sl: b0 + (r + 1) * sl])
+            return
+        for path, sp in self.layout.leaves.items():
+            v2 = torch.as_tensor(flat[path]).to(self.device, dtype=torch.float32).reshape(sp.rows, sp.cols)
+            dim = self.shard_dim[path]
+            rws, c, ld = self._local_shape2d(path)
+            if dim is not None:
+                v2 = v2[:, self.sidx * c:(self.sidx + 1) * c] if c != sp.cols else v2[self.sidx * rws:(self.sidx + 1) * rws]
+            self._local_view(buf, path).copy_(v2)
+
+    def load_opt_state_global(self, mu: Dict, nu: Dict, count: int) -> None:
+        """Inverse of ``opt_state_global``: every rank passes the same global trees and keeps its part."""
+        def flatten(tree, prefix=""):
+            out = {}
+            for k, v in tree.items():
+                if isinstance(v, dict):
+                    out.update(flatten(v, prefix + k + "/"))
+                else:
+                    out[prefix + k] = v
+            return out
+        self._load_moment(self.m, flatten(mu))
+        self._load_moment(self.v, flatten(nu))
+        self.step_count.fill_(int(count))
+        torch.cuda.synchronize()
+        if self.world > 1:
+            dist.barrier()
 
     @staticmethod
     def _nest(flat: Dict[str, object], order: Optional[Sequence[str]] = None) -> Dict:

@@ -189,3 +189,41 @@ def test_gpt2_engine_matches_generic_path(nmb):
         # attention has an exactly zero gradient (softmax is shift invariant), so bound biases loosely
         mean_tol = (0.6 if pa.endswith("bias") else 0.06) * lr * steps
         assert d.max() <= 2.2 * lr * steps and d.mean() <= mean_tol, (pa, d.max(), d.mean())
+
+
+@pytest.mark.parametrize("ext", ["msgpack", "safetensors"])
+def test_engine_checkpoint_has_the_generic_layout_and_resumes(tmp_path, ext):
+    """An engine checkpoint uses the same container as a generic-tier TrainState (mu / nu shaped like
+    the parameters, global layout), and a fresh engine restored from it continues like the original."""
+    from jax_distributed_tuts_b200 import checkpoint as ckpt
+    from jax_distributed_tuts_b200.engine import MLPEngine
+    cfg, _, model, state, batch = _setup("cpu")
+    mesh = Mesh((1,), ("data",), device=torch.device("cuda"))
+    lr = cfg.optimizer.learning_rate
+    pinned = Batch(batch.inputs.pin_memory(), batch.labels.pin_memory())
+    with mesh:
+        eng = MLPEngine(cfg.model, mesh, mode="dp", batch_per_rank=batch.inputs.shape[0], lr=lr, num_minibatches=4,
+                        init_params=state.params, use_graph=True)
+        st = eng.make_state(model, state.rng)
+        for _ in range(3):
+            st, _m = eng.train_step(st, None, pinned)
+        path = str(tmp_path / f"ckpt.{ext}")
+        ckpt.save_checkpoint(path, st, mesh=mesh)
+        loaded = ckpt.load_checkpoint(path)
+        # container: identical key structure to the generic tier's
+        generic = ckpt.state_dict(_to(state, "cuda"), mesh=mesh)
+        def keys(t, p=""):
+            return sorted(k2 for k, v in t.items() for k2 in (keys(v, p + k + "/") if isinstance(v, dict) else [p + k]))
+        assert keys(loaded["params"]) == keys(generic["params"])
+        assert keys(loaded["opt_state"]["0"]) == keys(generic["opt_state"]["0"])
+        assert int(loaded["opt_state"]["0"]["count"]) == 3
+        eng2 = MLPEngine(cfg.model, mesh, mode="dp", batch_per_rank=batch.inputs.shape[0], lr=lr, num_minibatches=4,
+                         init_params=tree_map(torch.zeros_like, state.params), use_graph=False)
+        st2 = eng2.make_state(model, state.rng)
+        ckpt.restore_engine(eng2, loaded)
+        st, m1 = eng.train_step(st, None, pinned)
+        st2, m2 = eng2.train_step(st2, None, pinned)
+        torch.cuda.synchronize()
+        for a, b in zip(tree_leaves(eng.params_tree()), tree_leaves(eng2.params_tree())):
+            assert (a.float() - b.float()).abs().max().item() <= 2e-5
+        assert abs(float(m1["loss"][0]) - float(m2["loss"][0])) <= 1e-2 * max(1.0, abs(float(m1["loss"][0])))

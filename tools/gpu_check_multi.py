@@ -97,6 +97,42 @@ def main():
                 loss = float(m["loss"][0]) / m["loss"][1]
                 lg = float(m_gen["loss"][0]) / m_gen["loss"][1]
                 good &= abs(loss - lg) < 2e-2 and m["loss"][1] == m_gen["loss"][1]
+                # Adam moments exported in the global per-leaf layout == the generic path's optimizer state
+                og = eng.opt_state_global()
+                adam = gen.opt_state[0]
+                for nm, mine, ref_t in (("mu", og["mu"], adam.mu), ("nu", og["nu"], adam.nu)):
+                    for k in ("input_dense", "output_dense"):
+                        for kk in ("kernel", "bias"):
+                            a, b_ = mine[k][kk].float(), ref_t[k][kk].float().reshape(mine[k][kk].shape)
+                            err = ((a - b_).norm() / b_.norm().clamp_min(1e-12)).item()
+                            if not err < 8e-2:
+                                good = False
+                                log(f"  [{name}] {nm} {k}/{kk} rel err {err:.3e}")
+                good &= int(og["count"].item()) == steps
+                # checkpoint round trip: a fresh engine restored from the file continues like the original
+                import tempfile
+                from jax_distributed_tuts_b200 import checkpoint as ckpt
+                path = os.path.join(tempfile.gettempdir(), f"b200_ckpt_{name.replace('/', '_')}.msgpack")
+                ckpt.save_checkpoint(path, st, mesh=mesh)
+                dist.barrier()
+                eng2 = MLPEngine(cfg.model, mesh, mode=mode, batch_per_rank=per_rank, lr=lr, num_minibatches=4,
+                                 init_params=tree_map(torch.zeros_like, init.params), min_weight_size=16, use_graph=False)
+                st2 = eng2.make_state(model, init.rng)
+                ckpt.restore_engine(eng2, ckpt.load_checkpoint(path))
+                st, m = eng.train_step(st, None, pinned)
+                st2, m2 = eng2.train_step(st2, None, pinned)
+                torch.cuda.synchronize()
+                t1, t2 = eng.params_tree(), eng2.params_tree()
+                for k in ("input_dense", "output_dense"):
+                    for kk in ("kernel", "bias"):
+                        d = (t1[k][kk].float() - t2[k][kk].float()).abs().max().item()
+                        if not d <= 2e-5:
+                            good = False
+                            log(f"  [{name}] resume mismatch {k}/{kk}: {d:.3e}")
+                if abs(float(m["loss"][0]) - float(m2["loss"][0])) > 1e-2 * max(1.0, abs(float(m["loss"][0]))):
+                    good = False
+                    log(f"  [{name}] resume loss {float(m2['loss'][0])} vs {float(m['loss'][0])}")
+                del eng2
                 # timing
                 evs = []
                 for _ in range(30):
