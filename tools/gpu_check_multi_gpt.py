@@ -75,6 +75,24 @@ def main():
                         good = False
                     if d.mean().item() > worst[1]:
                         worst = (k, d.mean().item())
+                # Adam second moments, reassembled from the owner-update slices (DP) or the row / column
+                # shards (FSDP) into the global per-leaf layout, against the generic path's state
+                # (nu = EMA of g^2 is insensitive to the sign noise that makes mu of tiny gradients jitter)
+                og = eng.opt_state_global()
+                nu_ref = dict(tree_leaves_with_path(st.opt_state[0].nu))
+                nu_got = dict(tree_leaves_with_path(og["nu"]))
+                worst_nu = ("", 0.0)
+                for k, a in nu_ref.items():
+                    b = nu_got[k]
+                    b = b[: a.shape[0]] if b.shape != a.shape else b
+                    if a.float().norm().item() < 1e-9 and b.float().norm().item() < 1e-9:
+                        continue          # exactly-zero gradients (attention key bias): only rounding noise
+                    err = ((a.float() - b.float()).norm() / a.float().norm().clamp_min(1e-20)).item()
+                    if err > worst_nu[1]:
+                        worst_nu = (k, err)
+                if not worst_nu[1] < 0.15 or int(og["count"].item()) != steps:
+                    good = False
+                    log(f"  [{name}] optimizer state mismatch: nu {worst_nu[0]} rel err {worst_nu[1]:.3e}, count {int(og['count'].item())}")
                 flat = torch.cat([t.reshape(-1).float() for t in got.values()])
                 ref0 = flat.clone()
                 dist.broadcast(ref0, 0)
