@@ -182,7 +182,6 @@ def main() -> None:
                     help="after the timed regions, profile 3 more steps with CUPTI and print per-kernel device time to stderr")
     ap.add_argument("--no-extra", action="store_true",
                     help="skip the secondary GPT-2 small measurement that the default config appends as `extra`")
-    ap.add_argument("--extra-child", action="store_true", help=argparse.SUPPRESS)
     args = ap.parse_args()
     if args.impl == "reference":
         if int(os.environ.get("RANK", "0")) == 0:
@@ -420,9 +419,7 @@ def main() -> None:
             n_params = 124.4e6 if c["gpt"] == "small" else 354.8e6 if c["gpt"] == "medium" else 1e6
             flops = 6.0 * n_params * toks + 12.0 * gcfg.n_layer * gcfg.d_model * c["seq"] * toks * 0.5
             out["model_tflops_per_gpu"] = flops / (ms_per_step * 1e-3) / 1e12 / world
-        if args.extra_child:
-            print("EXTRA_JSON " + json.dumps(out), flush=True)
-    want_extra = (args.config == "mlp_dp" and args.impl == "ours" and not args.no_extra and not args.extra_child)
+    want_extra = (args.config == "mlp_dp" and args.impl == "ours" and not args.no_extra)
     extra = None
     if want_extra:
         # secondary measurement, same protocol, transformer configuration of BASELINE.json (DP GPT-2 small):
@@ -435,7 +432,7 @@ def main() -> None:
             extra = run_secondary(args, rank, world, device)
         except Exception as e:  # noqa: BLE001  (never lose the headline line because of the extra)
             extra = {"error": f"{type(e).__name__}: {e}"[:200]}
-    if rank == 0 and not args.extra_child:
+    if rank == 0:
         if extra is not None:
             out["extra"] = {"gpt2s_dp": extra}
         print(json.dumps(out), flush=True)
