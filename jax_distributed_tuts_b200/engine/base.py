@@ -89,6 +89,27 @@ class FlatLayout:
         sp = self.leaves[path]
         return buf[sp.offset: sp.offset + sp.rows * sp.ld].view(sp.rows, sp.ld)[:, : sp.cols]
 
+    # Owner-update data parallelism keeps per-rank state (Adam moments) only for the rank's 1/world
+    # slice of every bucket; a rank's local buffer is the concatenation of its slices, bucket by bucket.
+    def owner_slices_to_flat(self, slices: torch.Tensor) -> torch.Tensor:
+        """``slices`` [world, total/world] (row r = rank r's local buffer) -> the flat [total] buffer."""
+        W = self.world
+        assert slices.shape == (W, self.total // W), (tuple(slices.shape), W, self.total)
+        full = torch.empty(self.total, dtype=slices.dtype, device=slices.device)
+        for (b0, b1) in self.bucket_ranges:
+            sl = (b1 - b0) // W
+            full[b0:b1].view(W, sl).copy_(slices[:, b0 // W: b0 // W + sl])
+        return full
+
+    def flat_to_owner_slice(self, full: torch.Tensor, rank: int) -> torch.Tensor:
+        """Inverse of ``owner_slices_to_flat`` for one rank: flat [total] -> local [total/world]."""
+        W = self.world
+        out = torch.empty(self.total // W, dtype=full.dtype, device=full.device)
+        for (b0, b1) in self.bucket_ranges:
+            sl = (b1 - b0) // W
+            out[b0 // W: b0 // W + sl].copy_(full[b0 + rank * sl: b0 + (rank + 1) * sl])
+        return out
+
     def tree(self, buf: torch.Tensor) -> Dict:
         out: Dict = {}
         for path in self.leaves:
@@ -443,12 +464,9 @@ class FusedEngine:
             else:
                 g = torch.empty(W, buf.numel(), dtype=buf.dtype, device=buf.device)
                 dist.all_gather_into_tensor(g.view(-1), buf.contiguous().view(-1))
-                full = torch.empty(self.layout.total, dtype=buf.dtype, device=buf.device)
-                for (b0, b1) in self.layout.bucket_ranges:
-                    sl = (b1 - b0) // W
-                    full[b0:b1].view(W, sl).copy_(g[:, b0 // W: b0 // W + sl])
-            for path in self.layout.leaves:
-                out[path] = self.layout.view(full, path).clone()
+                full = self.layout.owner_slices_to_flat(g)
+            for path, sp in self.layout.leaves.items():
+                out[path] = self.layout.view(full, path).clone().reshape(sp.shape)
             return out
         from ..comm import collectives as Cc
         for path, sp in self.layout.leaves.items():
@@ -474,10 +492,7 @@ class FusedEngine:
             for path, sp in self.layout.leaves.items():
                 v = torch.as_tensor(flat[path]).to(self.device, dtype=torch.float32)
                 self.layout.view2d(full, path).copy_(v.reshape(sp.rows, sp.cols))
-            W, r = self.world, self.rank
-            for (b0, b1) in self.layout.bucket_ranges:
-                sl = (b1 - b0) // W
-                buf[b0 // W: b0 // W + sl].copy_(full[b0 + r * sl: b0 + (r + 1) * sl])
+            buf.copy_(self.layout.flat_to_owner_slice(full, self.rank))
             return
         for path, sp in self.layout.leaves.items():
             v2 = torch.as_tensor(flat[path]).to(self.device, dtype=torch.float32).reshape(sp.rows, sp.cols)

@@ -140,3 +140,31 @@ def test_train_step_dp_overfits_single_batch(capsys):
     assert state.step == 11
     s = format_metrics(m, "dp")
     assert s.splitlines()[0].strip("=") == " dp " and "loss: " in s and "accuracy: " in s
+
+
+def test_flat_layout_views_and_owner_slices_round_trip():
+    """The engines' flat padded layout (host-side index math only, no GPU): leaf views address the
+    right elements, pads stay out of them, and the owner-update slicing of data parallelism
+    (each rank keeps 1/world of every bucket) reassembles to the flat buffer for any world size."""
+    from jax_distributed_tuts_b200.engine.base import FlatLayout
+    leaves = [("out/kernel", (512, 10), 0), ("in/kernel", (784, 512), 1), ("in/bias", (512,), 1), ("out/bias", (10,), 1)]
+    for world in (1, 2, 4, 8):
+        lay = FlatLayout(leaves, world)
+        assert lay.total % (world * 64) == 0 and all((b1 - b0) % world == 0 for b0, b1 in lay.bucket_ranges)
+        flat = torch.arange(lay.total, dtype=torch.float32)
+        # leaf views: shapes, and the 10-wide leaf is stored with a pitch of 16 (TMA / vector alignment)
+        assert lay.view(flat, "out/kernel").shape == (512, 10) and lay.leaves["out/kernel"].ld == 16
+        assert lay.view(flat, "in/bias").shape == (512,)
+        v = lay.view2d(flat, "out/kernel")
+        assert v[1, 0] - v[0, 0] == 16 and v[0, 9] - v[0, 0] == 9
+        # no two leaves overlap
+        seen = torch.zeros(lay.total, dtype=torch.int32)
+        for path, sp in lay.leaves.items():
+            seen[sp.offset: sp.offset + sp.rows * sp.ld] += 1
+        assert int(seen.max()) == 1
+        # owner slices <-> flat
+        slices = torch.stack([lay.flat_to_owner_slice(flat, r) for r in range(world)])
+        assert slices.shape == (world, lay.total // world)
+        assert torch.equal(lay.owner_slices_to_flat(slices), flat)
+        # every flat element is owned by exactly one rank
+        assert torch.equal(torch.sort(slices.reshape(-1)).values, flat)
