@@ -433,19 +433,6 @@ def group_attention():
             torch.cuda.synchronize()
             ms = e0.elapsed_time(e1) / 20
             print(f"  attention {name} b={b}: {ms * 1e3:.1f} us  {flops * mult / ms / 1e9:.0f} TFLOP/s (causal flops)")
-    # per-kernel device times (CUPTI through torch.profiler), b=16
-    try:
-        from torch.profiler import ProfilerActivity, profile
-        with profile(activities=[ProfilerActivity.CUDA]) as prof:
-            for _ in range(5):
-                K.attention_fwd(qkv, out, lse, b, t, h)
-                K.attention_bwd(qkv, out, dout, lse, dqkv, scratch, b, t, h)
-            torch.cuda.synchronize()
-        for ev in prof.key_averages():
-            if "attention" in ev.key:
-                print(f"    {ev.key[:60]:60s} {ev.device_time_total / max(ev.count, 1):8.1f} us x{ev.count}")
-    except Exception as e:     # profiler availability is not part of the check
-        print("  (torch.profiler unavailable:", e, ")")
     return ok
 
 
