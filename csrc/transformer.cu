@@ -6,7 +6,8 @@
 
 namespace b200 {
 
-constexpr int LN_MAX_CHUNKS = 8;  // 8 chunks x 32 lanes x 8 elements = 2048 columns max
+// LayerNorm rows are processed as 16-byte chunks, one per lane: NCH chunks per lane cover NCH * 256 columns
+// (instantiated for 256 ... 2048 columns).
 
 __device__ __forceinline__ void unpack8(const uint4& w, float (&f)[8]) {
   f[0] = __uint_as_float(w.x << 16); f[1] = __uint_as_float(w.x & 0xFFFF0000u);
