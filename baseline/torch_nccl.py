@@ -10,7 +10,6 @@ FSDP : each parameter stored as a 1/N flat shard; before the forward every layer
 """
 from __future__ import annotations
 
-import math
 from typing import List
 
 import torch

@@ -5,7 +5,7 @@ Leaves may be ``Partitioned`` boxes; the gradient tree has the same structure an
 """
 from __future__ import annotations
 
-from typing import Callable, Tuple
+from typing import Callable
 
 import torch
 

@@ -26,7 +26,7 @@ import torch
 
 from .mesh import Mesh
 from .rng import Key
-from .tree import Partitioned, Pytree, is_partitioned, tree_leaves_with_path, tree_map
+from .tree import Pytree, is_partitioned, tree_leaves_with_path, tree_map
 
 _EXT_NDARRAY = 1
 _EXT_NPSCALAR = 3

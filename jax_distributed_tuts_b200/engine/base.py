@@ -24,7 +24,7 @@ from ..ops import kernels as K
 from ..ops._lib import AdamWHParams, CommCtx, Seg
 from ..state import Batch, Metrics, TrainState
 from ..parallel.fsdp import choose_shard_dim
-from ..tree import Partitioned, Pytree
+from ..tree import Partitioned
 
 
 def _round_up(x: int, m: int) -> int:

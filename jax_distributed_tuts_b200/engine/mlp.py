@@ -33,7 +33,6 @@ from .. import rng as _rng
 from ..mesh import Mesh
 from ..ops import kernels as K
 from ..state import Batch
-from ..tree import Partitioned
 from .base import FlatLayout, FusedEngine, _round_up
 
 _ORDER = ("input_dense/kernel", "input_dense/bias", "output_dense/kernel", "output_dense/bias")

@@ -16,7 +16,7 @@ ride in the GEMM epilogues.
 from __future__ import annotations
 
 import math
-from typing import Dict, Optional
+from typing import Dict
 
 import torch
 

@@ -15,11 +15,11 @@ This module is the generic pytree implementation (any device, any leaf). The fus
 from __future__ import annotations
 
 import dataclasses
-from typing import Any, NamedTuple, Tuple
+from typing import Any, Tuple
 
 import torch
 
-from ..tree import Partitioned, Pytree, is_partitioned, register_dataclass, tree_map
+from ..tree import Pytree, is_partitioned, register_dataclass, tree_map
 
 
 @register_dataclass

@@ -25,7 +25,7 @@ from ..mesh import Mesh, current_mesh
 from ..models.mlp import Module
 from ..optim import adamw
 from ..state import Batch, Metrics, TrainState
-from ..tree import Partitioned, Pytree, is_partitioned, tree_leaves, tree_map
+from ..tree import Partitioned, Pytree, is_partitioned, tree_map
 from ..utils.profiling import named_scope
 from .dp import make_loss_fn
 

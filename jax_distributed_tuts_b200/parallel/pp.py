@@ -16,11 +16,9 @@ mesh has one, averages gradients with ``sync_gradients`` semantics.
 """
 from __future__ import annotations
 
-import dataclasses
-from typing import Callable, Dict, List, Optional, Sequence, Tuple
+from typing import Callable, Dict, List, Optional, Tuple
 
 import torch
-import torch.distributed as dist
 
 from .. import rng as _rng
 from ..comm import collectives as C
@@ -30,7 +28,7 @@ from ..models.mlp import Module
 from ..ops import functional as Fn
 from ..optim import adamw
 from ..state import Batch, Metrics, TrainState
-from ..tree import Pytree, tree_leaves, tree_map
+from ..tree import tree_leaves, tree_map
 from ..utils.profiling import named_scope
 from .dp import fold_rng_over_axis
 from .fsdp import sync_gradients

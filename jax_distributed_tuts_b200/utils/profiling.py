@@ -5,7 +5,6 @@ region timers (the reference has no timing code at all)."""
 from __future__ import annotations
 
 import contextlib
-import functools
 from collections import defaultdict
 from typing import Dict, List
 

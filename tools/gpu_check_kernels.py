@@ -495,8 +495,6 @@ def group_gemm_epi_perf():
         "bwd aux silu'": lambda: K.gemm(a, bt, out, bwd=True, aux=pre, act="silu"),
     }
     for name, fn in cases.items():
-        for bn in (128, 256):
-            import functools
         t = _time(fn)
         print(f"  {name:24s} {t * 1e3:8.1f} us  {fl / t / 1e9:7.1f} TFLOP/s", flush=True)
     return True

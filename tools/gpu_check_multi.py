@@ -11,7 +11,6 @@ from __future__ import annotations
 
 import os
 import sys
-import time
 import traceback
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -27,7 +26,7 @@ from jax_distributed_tuts_b200.mesh import Mesh
 from jax_distributed_tuts_b200.models.mlp import Classifier
 from jax_distributed_tuts_b200.parallel import dp
 from jax_distributed_tuts_b200.state import Batch
-from jax_distributed_tuts_b200.tree import tree_leaves, tree_map
+from jax_distributed_tuts_b200.tree import tree_map
 
 
 def log(*a):
