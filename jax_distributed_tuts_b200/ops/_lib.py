@@ -136,6 +136,7 @@ def _declare(lib: C.CDLL) -> None:
                                        i32, i32, i32, vp],
         "b200_attention_fwd": [vp, vp, vp, i32, i32, i32, vp],
         "b200_attention_bwd": [vp, vp, vp, vp, vp, vp, i32, i32, i32, vp],
+        "b200_attention_bwd_noalloc": [vp, vp, vp, vp, vp, i32, i32, i32, vp],
         "b200_fused_reduce_adamw": [C.POINTER(CommCtx), vp, i32, i32, vp, vp, vp, vp,
                                     C.POINTER(AdamWHParams), vp, i32, vp, vp, i32, i32, vp],
         "b200_fused_reduce_adamw_end": [C.POINTER(CommCtx), vp, i32, i32, vp, vp, vp, vp,
