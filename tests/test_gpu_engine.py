@@ -227,3 +227,42 @@ def test_engine_checkpoint_has_the_generic_layout_and_resumes(tmp_path, ext):
         for a, b in zip(tree_leaves(eng.params_tree()), tree_leaves(eng2.params_tree())):
             assert (a.float() - b.float()).abs().max().item() <= 2e-5
         assert abs(float(m1["loss"][0]) - float(m2["loss"][0])) <= 1e-2 * max(1.0, abs(float(m1["loss"][0])))
+
+
+@pytest.mark.parametrize("num_classes,fuse_xent", [(10, False), (40, True)])
+def test_engine_head_variants_match_each_other(num_classes, fuse_xent):
+    """The classifier head runs either with the cross-entropy fused into the GEMM epilogue (<= 32
+    classes) or as GEMM + cross-entropy kernel (more classes, or fuse_xent=False): both must follow
+    the generic path."""
+    from jax_distributed_tuts_b200.engine import MLPEngine
+    cfg = dp_config()
+    cfg.model.num_classes = num_classes
+    mesh_g = Mesh((1,), ("data",), device=torch.device("cuda"))
+    model = Classifier(cfg.model)
+    key = rng.PRNGKey(cfg.seed)
+    model_rng, data_rng, label_rng = rng.split(key, 3)
+    x = torch.randn(64, 784, generator=rng.uniform_generator(data_rng))
+    y = torch.randint(0, num_classes, (64,), generator=rng.uniform_generator(label_rng))
+    batch = Batch(x, y)
+    with Mesh((1,), ("data",), device=torch.device("cpu")):
+        state = dp.init_dp(model_rng, x, model)
+    steps, lr = 3, cfg.optimizer.learning_rate
+    step = dp.make_train_step_dp(mesh_g, num_minibatches=4)
+    s_gen, m_gen = _to(state, "cuda"), None
+    bg = batch.to("cuda")
+    for _ in range(steps):
+        s_gen, m_gen = step(s_gen, m_gen, bg)
+    with mesh_g:
+        eng = MLPEngine(cfg.model, mesh_g, mode="dp", batch_per_rank=64, lr=lr, num_minibatches=4,
+                        init_params=state.params, use_graph=False, fuse_xent=fuse_xent)
+        s_eng, m_eng = eng.make_state(model, state.rng), None
+        for _ in range(steps):
+            s_eng, m_eng = eng.train_step(s_eng, m_eng, batch)
+    torch.cuda.synchronize()
+    assert eng.launches_per_step == 8        # neither variant takes the 7-launch fused-head path
+    p_eng = eng.params_tree()
+    for k in ("input_dense", "output_dense"):
+        for kk in ("kernel", "bias"):
+            assert _mean_close(p_eng[k][kk], s_gen.params[k][kk], lr, steps), (k, kk)
+    assert abs(float(m_gen["loss"][0]) / m_gen["loss"][1] - float(m_eng["loss"][0]) / m_eng["loss"][1]) < 2e-2
+    assert float(m_gen["accuracy"][0]) == pytest.approx(float(m_eng["accuracy"][0]), abs=3)
