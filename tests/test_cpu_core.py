@@ -168,3 +168,13 @@ def test_flat_layout_views_and_owner_slices_round_trip():
         assert torch.equal(lay.owner_slices_to_flat(slices), flat)
         # every flat element is owned by exactly one rank
         assert torch.equal(torch.sort(slices.reshape(-1)).values, flat)
+
+
+def test_print_exception_names_the_class(capsys):
+    from jax_distributed_tuts_b200.utils import print_exception
+    try:
+        raise ValueError("bad shape (3, 5)")
+    except ValueError as e:
+        print_exception(e)
+    out = capsys.readouterr().out
+    assert "ValueError" in out and "bad shape" in out
