@@ -50,7 +50,7 @@ def worker(rank, world):
             state_dp, metrics_dp = train_step_dp_fn(state_dp, metrics_dp, local)
         state_dp, final_metrics_dp = train_step_dp_fn(state_dp, None, local)
         if rank == 0:
-            print(f"devices: {world}, parameters: {get_num_params(state_dp) if state_dp.engine is None else 407050}")
+            print(f"devices: {world}, parameters: {get_num_params(state_dp)}")
             print_metrics(final_metrics_dp, title="dp")
 
 

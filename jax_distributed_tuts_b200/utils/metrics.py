@@ -34,7 +34,17 @@ def print_metrics(metrics, title: str = "") -> None:
 
 def get_num_params(state) -> int:
     """Total element count of ``state.params`` (util.py:184-185). For sharded states this counts
-    the local slices, exactly as the reference would inside ``shard_map``."""
+    the local slices, exactly as the reference would inside ``shard_map``. States owned by a fused
+    engine are counted from the engine's layout (logical shapes, pads excluded)."""
+    eng = getattr(state, "engine", None)
+    if eng is not None:
+        total = 0
+        for sp in eng.layout.leaves.values():
+            n = 1
+            for s in sp.shape:
+                n *= int(s)
+            total += n
+        return total
     total = 0
     for x in tree_leaves(unbox(state.params)):
         n = 1
