@@ -3,7 +3,7 @@
 // activation/dropout. All are sized to stream at HBM rate: 16-byte accesses, grid-stride loops
 // with a grid that is a multiple of the SM count.
 #include "../include/b200dist.h"
-#include "common.cuh"
+#include "comm.cuh"
 
 namespace b200 {
 
@@ -492,8 +492,13 @@ __global__ void rng_split_kernel(uint64_t* key, uint64_t* out_step, uint64_t sal
 // Start-of-step housekeeping in one launch: fp32 -> bf16 cast of the inputs and zeroing of up to two
 // small fp32 regions (step metrics, bias-gradient vectors).
 __global__ void cast_zero_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int64_t n,
-                                 float* __restrict__ z0, int64_t n0, float* __restrict__ z1, int64_t n1) {
+                                 float* __restrict__ z0, int64_t n0, float* __restrict__ z1, int64_t n1,
+                                 const uint32_t* __restrict__ sig, int rank, int world, uint64_t timeout_ns) {
   pdl_sync();
+  // First kernel of a step: the peers must have finished the previous step's update (they publish
+  // into our parameters and read our gradients) before anything here clears a gradient region or a
+  // later kernel reads a weight. See comm.cuh.
+  if (sig != nullptr) wait_published(sig, rank, world, timeout_ns);
   const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
   const int64_t tid = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   const int64_t n4 = n >> 2;
@@ -675,6 +680,12 @@ extern "C" int b200_rng_split_bump(uint64_t* key, uint64_t* out_step, uint64_t s
 
 extern "C" int b200_cast_zero(const float* src, void* dst, int64_t n, float* z0, int64_t n0, float* z1, int64_t n1,
                               void* stream) {
+  return b200_cast_zero_wait(src, dst, n, z0, n0, z1, n1, nullptr, 0, 1, stream);
+}
+
+extern "C" int b200_cast_zero_wait(const float* src, void* dst, int64_t n, float* z0, int64_t n0, float* z1, int64_t n1,
+                                   const void* signal_local, int rank, int world,
+                              void* stream) {
   B200_REQUIRE(n >= 0 && n0 >= 0 && n1 >= 0, "cast_zero: negative size");
   B200_REQUIRE(n == 0 || ((reinterpret_cast<uintptr_t>(src) & 15) == 0 && (reinterpret_cast<uintptr_t>(dst) & 7) == 0),
                "cast_zero: misaligned buffers");
@@ -682,7 +693,8 @@ extern "C" int b200_cast_zero(const float* src, void* dst, int64_t n, float* z0,
   if (n0 > work) work = n0;
   if (n1 > work) work = n1;
   B200_CUDA(launch_k(cast_zero_kernel, dim3(stream_grid(work, 256)), dim3(256), 0, static_cast<cudaStream_t>(stream), src,
-                     static_cast<__nv_bfloat16*>(dst), n, z0, n0, z1, n1));
+                     static_cast<__nv_bfloat16*>(dst), n, z0, n0, z1, n1,
+                     world > 1 ? static_cast<const uint32_t*>(signal_local) : nullptr, rank, world, comm_timeout_ns()));
   B200_CUDA(cudaGetLastError());
   return 0;
 }

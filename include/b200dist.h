@@ -16,7 +16,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 16
+#define B200_ABI_VERSION 17
 
 const char* b200_last_error(void);
 int b200_abi_version(void);
@@ -246,14 +246,18 @@ int b200_attention_bwd_noalloc(const void* qkv, const void* out, const void* dou
  * rank, every rank's copy mapped into every process; a multicast/NVLS address when the fabric
  * has one). One launch does, for a list of segments of the flat gradient buffer:
  *
- *   start barrier  (all ranks have finished writing their local gradients)
+ *   "gradients ready" exchange  every block stores its epoch into the signal buffer of every peer
+ *                  (one-way, st.relaxed.sys) and polls its own buffer for theirs (ld.acquire.sys)
  *   g  = sum over ranks of grad[seg]            multimem.ld_reduce (in-switch) or P2P loads
  *   g *= grad_scale                             (mean over devices and minibatches)
  *   AdamW on this rank's fp32 master / m / v for the segment
- *   publish: new fp32 + bf16 parameters         multimem.st / P2P stores to every rank  (DP)
- *            or bf16 shard written locally, to be pulled by the all-gather GEMM        (FSDP)
- *   metrics psum (optional, through the signal buffer)
- *   end barrier    (all ranks are done reading my gradients / writing my parameters)
+ *   publish: new bf16 (and, on request, fp32) parameters   multimem.st / P2P stores to every rank  (DP)
+ *            or bf16 shard written locally, to be pulled by the all-gather GEMM                    (FSDP)
+ *   metrics psum (optional, epoch-tagged 8-byte stores into the peers' signal buffers)
+ *   fence.sys + "published" counter increment in every peer's signal buffer. The kernel does NOT wait
+ *   for the peers' increments: that half of the end barrier belongs to whoever reads the published
+ *   parameters (or overwrites the gradients) next, i.e. the first kernel of the next step:
+ *   b200_cast_zero_wait or b200_comm_wait_published.
  *
  * Reference semantics: DP  = pmean(grads) then replicated apply_gradients
  *                            (data_paral.py:210-217);
@@ -266,7 +270,12 @@ typedef struct b200_seg {
   int64_t dst_off;   /* broadcast mode: element offset in every rank's param buffers         */
   int64_t loc_off;   /* element offset in this rank's local m / v (/ p_shard / bf16_shard)   */
   int32_t rows, row_len;
+  int32_t flags;     /* B200_SEG_*                                                           */
+  int32_t reserved;
 } b200_seg;
+/* The segment is reduced by several ranks redundantly (a replicated leaf of a sharded run): sum it
+ * with peer loads in rank order instead of the in-switch reduction, so all replicas get the same bits. */
+#define B200_SEG_ORDERED 1
 
 typedef struct b200_comm_ctx {
   int32_t rank, world;
@@ -306,6 +315,64 @@ int b200_fused_reduce_adamw_end(const b200_comm_ctx* ctx, const b200_seg* segs_d
                                 const b200_adamw_hparams* hp, int32_t* step_count, int bump_step,
                                 const float* step_metrics, float* metrics_acc, int nmetrics,
                                 int blocks, const b200_step_end* end, void* stream);
+/* The same launch described by one struct (what the engines call). publish_fp32 = 0 keeps the fp32
+ * master of a DP slice on its owner only (the bf16 working copy is still stored to every rank): one
+ * third of the publish traffic; readers of the full fp32 tree gather the owners' slices first. */
+typedef struct b200_fused_update_args {
+  const b200_comm_ctx* ctx;
+  const b200_seg* segs_dev;
+  int32_t nseg, broadcast, publish_fp32, nmetrics, blocks;
+  float* p_local;
+  void* bf16_local;
+  float* m;
+  float* v;
+  const b200_adamw_hparams* hp;
+  const int32_t* step_count;
+  const float* step_metrics;
+  float* metrics_acc;
+  const b200_step_end* end; /* or NULL */
+} b200_fused_update_args;
+int b200_fused_update(const b200_fused_update_args* args, void* stream);
+/* `nranks` ranks emulated on ONE GPU: a single cooperative launch whose blockIdx.y selects the rank,
+ * every rank's "peer" pointers being ordinary local buffers (no multicast). It runs the same device
+ * code as the real launch, flag protocol included, so the cross-rank logic is testable on a one-GPU
+ * box. scratch_dev: b200_fused_update_emulated_scratch_bytes() bytes of device memory. */
+int b200_fused_update_emulated(const b200_fused_update_args* ranks, int nranks, void* scratch_dev, void* stream);
+long long b200_fused_update_emulated_scratch_bytes(void);
+
+/* Second half of the split-phase end barrier as a kernel of its own (the engines fold it into
+ * b200_cast_zero_wait instead): returns when every publish this rank has issued so far has landed
+ * from every peer too. signal_local: this rank's own signal buffer. */
+int b200_comm_wait_published(const void* signal_local, int rank, int world, void* stream);
+/* b200_cast_zero preceded by that wait inside the same kernel. signal_local = NULL or world = 1: no wait. */
+int b200_cast_zero_wait(const float* src, void* dst, int64_t n, float* z0, int64_t n0, float* z1, int64_t n1,
+                        const void* signal_local, int rank, int world, void* stream);
+/* How long a rank polls for a peer before the kernel traps (default 30 s, or the environment's
+ * B200DIST_COMM_TIMEOUT_MS): a dead peer makes the survivors' launches fail instead of hang. */
+void b200_comm_set_timeout_ms(long long ms);
+/* Profiling aid: device buffer of uint64 [blocks][8]; thread 0 of every block of the fused update
+ * stores %globaltimer at kernel start, after the exchange, after the update loop, after the fence +
+ * publish, at the end. NULL switches it off. Read at launch (capture) time. */
+void b200_comm_set_stamps(void* dev_u64);
+
+/* Collectives without an optimizer on symmetric-memory buffers (comm/collectives.py backend "fused";
+ * reference: psum/pmean data_paral.py:212,223, psum_scatter param_sharding.py:136, all_gather :140).
+ *   mode 0  all-reduce in place:  buf[i] = scale * sum_p buf_p[i] on every rank       (fp32, n % (4*world) == 0)
+ *   mode 1  reduce-scatter:       out[i] = scale * sum_p buf_p[rank*n/world + i]      (fp32, out local, n/world elements)
+ *   mode 2  all-gather:           out[p*n + i] = buf_p[i] in 16-byte units            (n units per rank, out local)
+ * Complete when the kernel ends (flag exchanges on both sides). */
+typedef struct b200_collective_args {
+  int32_t rank, world, mode, blocks;
+  void* const* peer_buf;     /* host array[world] */
+  void* const* peer_signal;  /* host array[world] */
+  void* mc_buf;              /* multicast address of buf or NULL */
+  void* out;
+  int64_t n;
+  float scale;
+} b200_collective_args;
+int b200_fused_collective(const b200_collective_args* args, void* stream);
+int b200_fused_collective_emulated(const b200_collective_args* ranks, int nranks, void* scratch_dev, void* stream);
+
 /* All-gather through peer loads (no collective launch): for every segment and every rank p, `rows`
  * rows of `row_bytes` bytes are read from peer_base[p] + src_off (row pitch src_pitch) and written
  * to dst + dst_off + p*peer_stride (row pitch dst_pitch). Row shards: rows = 1 and peer_stride =
@@ -319,7 +386,7 @@ typedef struct b200_gather_seg {
 } b200_gather_seg;
 int b200_peer_gather(void* const* peer_base, int world, const b200_gather_seg* segs_dev, int nseg,
                      void* dst, int blocks, void* stream);
-/* Cross-GPU barrier on the signal buffers (every rank launches it). */
+/* Cross-GPU barrier on the signal buffers (every rank launches it): one flag exchange. */
 int b200_signal_barrier(const b200_comm_ctx* ctx, void* stream);
 
 #ifdef __cplusplus

@@ -191,7 +191,8 @@ class FusedEngine:
     def __init__(self, mesh: Mesh, *, mode: str = "dp", lr: float, b1: float = 0.9, b2: float = 0.999,
                  eps: float = 1e-8, weight_decay: float = 1e-4, num_minibatches: int = 4,
                  data_axis_name: str = "data", shard_axis: Optional[str] = None, min_weight_size: int = 2 ** 18,
-                 use_graph: bool = True, comm_blocks: int = 16, overlap: bool = True, fsdp_weights: str = "fused"):
+                 use_graph: bool = True, comm_blocks: int = 16, overlap: bool = True, fsdp_weights: str = "fused",
+                 publish_fp32: bool = False, stub_collectives: bool = False):
         if not torch.cuda.is_available():
             raise RuntimeError("the fused engine needs a CUDA device; use the generic tier on CPU")
         _lib.lib()  # fail loudly if the kernel library is missing
@@ -216,6 +217,15 @@ class FusedEngine:
         # prefetched on the side stream, and the GEMMs run on local (L2-cached) memory.
         assert fsdp_weights in ("fused", "gather"), "engines resolve 'auto' before calling the base class"
         self.fsdp_weights = fsdp_weights if (mode == "fsdp" and self.S > 1) else "fused"
+        # DP publishes the bf16 working copy to every rank; the fp32 master of a slice stays with its
+        # owner (like the Adam moments) unless publish_fp32 asks for the reference's fully replicated
+        # fp32 state (data_paral.py:214-217): one third of the publish traffic. Readers of the fp32
+        # tree (flat_params, checkpoints) gather the owners' slices first.
+        self.publish_fp32 = publish_fp32
+        self._master_stale = False
+        # Measurement aid (bench.py "exposed comm"): the same step with every cross-GPU access removed.
+        # Each rank updates its own part from its local gradients only; results are NOT a training run.
+        self.stub_collectives = stub_collectives and self.world > 1
         self.graph: Optional[torch.cuda.CUDAGraph] = None
         self._last_metrics = None
         self._counts = [0, 0]
@@ -254,6 +264,9 @@ class FusedEngine:
                 self._lru = 0
                 self._setup_bucket_gather()
         self.ctx = self._make_ctx(self.arena, "grad", "param" if self.mode == "dp" else None, "bf16", "signal")
+        if self.stub_collectives:
+            self.ctx_stub = self._make_ctx(self.arena, "grad", "param" if self.mode == "dp" else None, "bf16", "signal",
+                                           local_only=True)
         self._build_segments()
 
     def _plan_shards(self) -> None:
@@ -431,6 +444,8 @@ class FusedEngine:
         """path -> fp32 tensor. DP: views of the replicated master. FSDP: full arrays gathered over
         the shard axis (``gather=True``) or ``Partitioned`` boxes of the local slices."""
         out: Dict[str, object] = {}
+        if self.mode == "dp":
+            self._refresh_master()
         for path, sp in self.layout.leaves.items():
             if self.mode == "dp":
                 out[path] = self.layout.view(self.p32, path)
@@ -449,6 +464,20 @@ class FusedEngine:
                 names = tuple(self.shard_axis if i == dim else None for i in range(len(sp.shape)))
                 out[path] = Partitioned(loc, names)
         return out
+
+    def _refresh_master(self) -> None:
+        """DP without ``publish_fp32``: a rank's fp32 master is current only on the slices it owns.
+        All-gathers the owners' slices bucket by bucket so ``p32`` is the full replicated master again.
+        Collective (every rank calls ``flat_params`` / ``params_tree`` / checkpoint save together)."""
+        if self.mode != "dp" or self.world == 1 or self.publish_fp32 or not self._master_stale:
+            return
+        torch.cuda.synchronize()
+        W, r = self.world, self.rank
+        for (b0, b1) in self.layout.bucket_ranges:
+            sl = (b1 - b0) // W
+            dist.all_gather_into_tensor(self.p32[b0:b1], self.p32[b0 + r * sl: b0 + (r + 1) * sl].clone())
+        torch.cuda.synchronize()
+        self._master_stale = False
 
     # ---- optimizer state in the reference's (global, per-leaf) layout: checkpoints, inspection ----
     def _moment_flat(self, buf: torch.Tensor) -> Dict[str, torch.Tensor]:
@@ -539,12 +568,15 @@ class FusedEngine:
 
     # ---------------------------------------------------------------- collectives -------------
     def _make_ctx(self, arena: SymmetricArena, grad: str, param: Optional[str], bf16: Optional[str],
-                  signal: str) -> CommCtx:
+                  signal: str, local_only: bool = False) -> CommCtx:
         ctx = CommCtx()
-        ctx.rank, ctx.world = self.rank, self.world
+        ctx.rank, ctx.world = (0, 1) if local_only else (self.rank, self.world)
 
         def arr(name):
-            a = arena.peer_ptr_array(name)
+            if local_only:
+                a = (C.c_void_p * 1)(arena.peer_ptrs[self.rank] + arena.offsets[name])
+            else:
+                a = arena.peer_ptr_array(name)
             self._keep.append(a)
             return C.cast(a, C.POINTER(C.c_void_p))
 
@@ -557,7 +589,10 @@ class FusedEngine:
             if param:
                 ctx.mc_bf16 = arena.mc_ptr(bf16)
         ctx.peer_signal = arr(signal)
-        ctx.mc_grad = arena.mc_ptr(grad)
+        if local_only:
+            ctx.mc_param = ctx.mc_bf16 = None
+        else:
+            ctx.mc_grad = arena.mc_ptr(grad)
         return ctx
 
     def _segs_to_device(self, segs: List) -> torch.Tensor:
@@ -570,6 +605,7 @@ class FusedEngine:
         if self.mode == "dp":
             for (b0, b1) in self.layout.bucket_ranges:
                 sl = (b1 - b0) // W
+                assert sl // 4 < 2 ** 31, "bucket slice too large for one fused-update segment: use more buckets"
                 seg = Seg(src_off=b0 + r * sl, src_pitch=sl, dst_off=b0 + r * sl, loc_off=b0 // W, rows=1, row_len=sl)
                 self.bucket_segs.append((self._segs_to_device([seg]), 1))
             return
@@ -577,9 +613,9 @@ class FusedEngine:
         for path, sp in self.layout.leaves.items():
             dim = self.shard_dim[path]
             rws, c, ld = self._local_shape2d(path)
-            if dim is None:     # replicated leaf: every rank applies the same all-reduced update
+            if dim is None:     # replicated leaf: every rank applies the same all-reduced update (fixed summation order)
                 seg = Seg(src_off=sp.offset, src_pitch=sp.ld, dst_off=0, loc_off=self.loc_off[path],
-                          rows=sp.rows, row_len=sp.ld)
+                          rows=sp.rows, row_len=sp.ld, flags=_lib.SEG_ORDERED)
             elif c != sp.cols:  # sharded on the last dim: strided rows
                 assert ld == c, f"{path}: last-dim shards must be multiples of 8 wide"
                 seg = Seg(src_off=sp.offset + self.sidx * c, src_pitch=sp.ld, dst_off=0, loc_off=self.loc_off[path],
@@ -587,6 +623,9 @@ class FusedEngine:
             else:               # sharded on rows: contiguous
                 seg = Seg(src_off=sp.offset + self.sidx * rws * sp.ld, src_pitch=sp.ld, dst_off=0,
                           loc_off=self.loc_off[path], rows=rws, row_len=sp.ld)
+            # the kernel indexes a segment's 16-byte vectors and its rows / columns with 32 bits
+            assert seg.rows * seg.row_len // 4 < 2 ** 31 and seg.row_len < 2 ** 31 and seg.rows < 2 ** 31, \
+                f"{path}: segment of {seg.rows} x {seg.row_len} elements is too large for one fused-update segment"
             per_bucket.setdefault(sp.bucket, []).append(seg)
         order = sorted(per_bucket)
         assert order == list(range(len(order))), "bucket ids must be 0..n-1"
@@ -600,6 +639,16 @@ class FusedEngine:
             self._all_segs = (torch.frombuffer(bytearray(b"".join(raws)), dtype=torch.uint8).to(self.device),
                               sum(n for _, n in self.bucket_segs))
         self._sync_bucket(-1, last=True)
+
+    def _begin_step(self, src: Optional[torch.Tensor], dst: Optional[torch.Tensor]) -> None:
+        """First launch of a step: (optional) fp32 -> bf16 cast of the inputs, zeroing of the step
+        metrics and of the bias-gradient region, and - with more than one rank - the deferred half of
+        the previous update's end barrier: it returns once every peer has published its parameters
+        (and therefore has finished reading this rank's gradients), see csrc/comm.cuh."""
+        sig = None
+        if self.world > 1 and not self.stub_collectives:
+            sig = self.arena.peer_ptrs[self.rank] + self.arena.offsets["signal"]
+        K.cast_zero(src, dst, self.step_metrics, self._vec_grads, wait_signal=sig, rank=self.rank, world=self.world)
 
     def _end_step(self, next_rng) -> None:
         """state.rng <- rebase(next_rng) (the salt folds into the device-resident key in place) and
@@ -633,13 +682,23 @@ class FusedEngine:
         if last and self._end_salt is not None:
             end = _lib.StepEnd(self.rng_base.data_ptr(), self._end_salt, self.step_count.data_ptr(), self._done_word.data_ptr())
             self._end_folded = True
-        _lib.check(_lib.lib().b200_fused_reduce_adamw_end(
-            C.byref(self.ctx), segs.data_ptr(), nseg, int(dp),
-            None if dp else self.p_loc.data_ptr(), None if dp else self.pb.data_ptr(),
-            self.m.data_ptr(), self.v.data_ptr(), C.byref(hp), self.step_count.data_ptr(), 0,   # bumped by the end record / _end_step
-            self.step_metrics.data_ptr() if last else None, self.metrics_acc.data_ptr() if last else None,
-            nmet if last else 0, self.comm_blocks, C.byref(end) if end is not None else None,
-            torch.cuda.current_stream().cuda_stream))
+        u = _lib.FusedUpdateArgs()
+        u.ctx = C.pointer(self.ctx_stub if self.stub_collectives else self.ctx)
+        u.segs_dev, u.nseg, u.broadcast = segs.data_ptr(), nseg, int(dp)
+        u.publish_fp32 = int(self.publish_fp32)
+        u.nmetrics = nmet if last else 0
+        u.blocks = self.comm_blocks
+        u.p_local = None if dp else self.p_loc.data_ptr()
+        u.bf16_local = None if dp else self.pb.data_ptr()
+        u.m, u.v = self.m.data_ptr(), self.v.data_ptr()
+        u.hp = C.pointer(hp)
+        u.step_count = self.step_count.data_ptr()     # bumped by the end record / _end_step
+        u.step_metrics = self.step_metrics.data_ptr() if last else None
+        u.metrics_acc = self.metrics_acc.data_ptr() if last else None
+        u.end = C.pointer(end) if end is not None else None
+        _lib.check(_lib.lib().b200_fused_update(C.byref(u), torch.cuda.current_stream().cuda_stream))
+        if dp and not self.publish_fp32:
+            self._master_stale = True
 
     def _sync_bucket_async(self, b: int) -> None:
         """Launches bucket ``b``'s fused update on the side stream, after everything already

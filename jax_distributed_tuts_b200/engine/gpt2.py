@@ -150,7 +150,7 @@ class GPT2Engine(FusedEngine):
 
     def _step_body(self) -> None:
         nmb = self.num_minibatches
-        K.cast_zero(None, None, self.step_metrics, self._vec_grads)   # metrics + every bias / norm gradient, one launch
+        self._begin_step(None, None)   # metrics + every bias / norm gradient cleared, peers' last update awaited: one launch
         self._gather_small()
         next_rng = _rng.split(_rng.Key(self.rng_base, 0), 2)[0]
         for i in range(nmb):

@@ -113,9 +113,9 @@ class MLPEngine(FusedEngine):
         salts = [_rng.salt_word(_rng.fold_in(mb_keys[i], axis_idx)) for i in range(nmb)]
         xb = self.x_bf[:, : self.In]
         if self.x_bf.shape[1] == self.In:
-            K.cast_zero(self.x_in, self.x_bf, self.step_metrics, self._vec_grads)     # one launch
+            self._begin_step(self.x_in, self.x_bf)     # one launch
         else:
-            K.cast_zero(None, None, self.step_metrics, self._vec_grads)
+            self._begin_step(None, None)
             xb.copy_(self.x_in)
         self._gather_small()
         if self.fuse_minibatches:
@@ -158,8 +158,10 @@ class MLPEngine(FusedEngine):
                 K.gemm(self.h, dlogits, self.grad2d("output_dense/kernel"), a_mn=True, b_mn=True, accumulate=accumulate)
         else:
             K.gemm(self.h, dlogits, self.grad2d("output_dense/kernel"), a_mn=True, b_mn=True, accumulate=accumulate)
-        if last and self.overlap:
-            self._sync_bucket_async(0)   # output layer's matrix: reduce + update under the rest of the backward
         self.gemm_wT(dlogits, "output_dense/kernel", self.dpre, bwd=True, aux=self.pre, act="silu",
                      dbias=self.grad1d("input_dense/bias"), **drop)
+        if last and self.overlap:
+            # output layer's matrix: reduce + update under the rest of the backward. Queued only after
+            # the dgrad above, the last reader of W2 in this step: the update rewrites W2 on every rank.
+            self._sync_bucket_async(0)
         K.gemm(xs, self.dpre, self.grad2d("input_dense/kernel"), a_mn=True, b_mn=True, accumulate=accumulate)

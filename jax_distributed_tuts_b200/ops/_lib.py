@@ -12,7 +12,7 @@ from typing import Optional
 
 from . import _build
 
-ABI_VERSION = 16
+ABI_VERSION = 17
 
 _lib: Optional[C.CDLL] = None
 
@@ -84,7 +84,29 @@ class CommCtx(C.Structure):
 class Seg(C.Structure):
     _fields_ = [
         ("src_off", C.c_int64), ("src_pitch", C.c_int64), ("dst_off", C.c_int64), ("loc_off", C.c_int64),
-        ("rows", C.c_int32), ("row_len", C.c_int32),
+        ("rows", C.c_int32), ("row_len", C.c_int32), ("flags", C.c_int32), ("reserved", C.c_int32),
+    ]
+
+
+SEG_ORDERED = 1     # reduce with peer loads in rank order (segments that several ranks reduce redundantly)
+
+
+class FusedUpdateArgs(C.Structure):
+    _fields_ = [
+        ("ctx", C.POINTER(CommCtx)), ("segs_dev", C.c_void_p),
+        ("nseg", C.c_int32), ("broadcast", C.c_int32), ("publish_fp32", C.c_int32), ("nmetrics", C.c_int32),
+        ("blocks", C.c_int32),
+        ("p_local", C.c_void_p), ("bf16_local", C.c_void_p), ("m", C.c_void_p), ("v", C.c_void_p),
+        ("hp", C.POINTER(AdamWHParams)), ("step_count", C.c_void_p), ("step_metrics", C.c_void_p),
+        ("metrics_acc", C.c_void_p), ("end", C.POINTER(StepEnd)),
+    ]
+
+
+class CollectiveArgs(C.Structure):
+    _fields_ = [
+        ("rank", C.c_int32), ("world", C.c_int32), ("mode", C.c_int32), ("blocks", C.c_int32),
+        ("peer_buf", C.POINTER(C.c_void_p)), ("peer_signal", C.POINTER(C.c_void_p)),
+        ("mc_buf", C.c_void_p), ("out", C.c_void_p), ("n", C.c_int64), ("scale", C.c_float),
     ]
 
 
@@ -95,6 +117,8 @@ class GatherSeg(C.Structure):
 
 SIGNAL_WORDS = 8192
 COMM_MAX_BLOCKS = 128
+# word offsets inside a signal buffer (csrc/comm.cuh)
+SIG_READY, SIG_EPOCH, SIG_PUB = 0, 128 * 8, 128 * 8 + 128
 
 
 class B200Error(RuntimeError):
@@ -109,6 +133,12 @@ def _declare(lib: C.CDLL) -> None:
     lib.b200_reset_launch_count.restype = None
     lib.b200_set_pdl.restype = None
     lib.b200_set_pdl.argtypes = [C.c_int]
+    lib.b200_comm_set_timeout_ms.restype = None
+    lib.b200_comm_set_timeout_ms.argtypes = [C.c_longlong]
+    lib.b200_comm_set_stamps.restype = None
+    lib.b200_comm_set_stamps.argtypes = [C.c_void_p]
+    lib.b200_fused_update_emulated_scratch_bytes.restype = C.c_longlong
+    lib.b200_fused_update_emulated_scratch_bytes.argtypes = []
     if hasattr(lib, "b200_attention_bwd_scratch_bytes"):
         lib.b200_attention_bwd_scratch_bytes.restype = C.c_longlong
         lib.b200_attention_bwd_scratch_bytes.argtypes = [C.c_int, C.c_int, C.c_int]
@@ -126,6 +156,12 @@ def _declare(lib: C.CDLL) -> None:
         "b200_rng_split": [vp, vp, u64, u64, vp],
         "b200_rng_split_bump": [vp, vp, u64, u64, vp, vp],
         "b200_cast_zero": [vp, vp, i64, vp, i64, vp, i64, vp],
+        "b200_cast_zero_wait": [vp, vp, i64, vp, i64, vp, i64, vp, i32, i32, vp],
+        "b200_fused_update": [C.POINTER(FusedUpdateArgs), vp],
+        "b200_fused_update_emulated": [C.POINTER(FusedUpdateArgs), i32, vp, vp],
+        "b200_fused_collective": [C.POINTER(CollectiveArgs), vp],
+        "b200_fused_collective_emulated": [C.POINTER(CollectiveArgs), i32, vp, vp],
+        "b200_comm_wait_published": [vp, i32, i32, vp],
         "b200_act_dropout_fwd": [vp, vp, i64, i32, i32, i32, vp, u64, f32, vp],
         "b200_act_dropout_bwd": [vp, vp, vp, i64, i32, i32, i32, vp, u64, f32, vp],
         "b200_layernorm_fwd": [vp, vp, vp, vp, vp, vp, i32, i32, f32, vp],

@@ -14,6 +14,13 @@ def test_kernel_group(group):
     torch.cuda.synchronize()
 
 
+def test_cross_rank_protocol_emulated_on_one_gpu():
+    """Fused reduce+AdamW+publish and the optimizer-free collectives with 2/4/8 virtual ranks in one
+    cooperative launch: epoch flags, split-phase publish counters, metric mailboxes, dead-peer abort."""
+    from tools import gpu_check_comm
+    assert gpu_check_comm.group_comm_emulated()
+
+
 def test_library_is_the_native_one():
     from jax_distributed_tuts_b200.ops import _lib
     before = _lib.launch_count()
