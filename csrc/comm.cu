@@ -59,9 +59,11 @@ struct RankArgs {
   b200_step_end end;
   uint64_t timeout_ns;
   unsigned long long* stamps;   // optional [blocks][8] globaltimer stamps (profiling aid)
+  int defer_publish;
 };
 
 static uint64_t g_timeout_ns = 0;
+static int g_defer_publish = -1;
 static unsigned long long* g_stamps = nullptr;
 
 uint64_t comm_timeout_ns() {
@@ -72,6 +74,14 @@ uint64_t comm_timeout_ns() {
     g_timeout_ns = static_cast<uint64_t>(ms) * 1000000ull;
   }
   return g_timeout_ns;
+}
+
+bool comm_defer_publish() {
+  if (g_defer_publish < 0) {
+    const char* e = getenv("B200DIST_DEFER_PUBLISH");
+    g_defer_publish = (e && e[0] == '1') ? 1 : (e && e[0] == '2') ? 2 : 0;
+  }
+  return g_defer_publish == 1;
 }
 
 // One all-to-all flag exchange for this block index: returns the epoch it used. Doubles as the
@@ -101,8 +111,14 @@ __device__ __forceinline__ uint32_t exchange(const CommDev& c, int bid, uint64_t
 
 // Orders everything this block stored (locally, to peers, through the multicast address) before the
 // "published" increments that follow it.
-__device__ __forceinline__ void publish(const CommDev& c) {
-  __threadfence_system();
+__device__ __forceinline__ void publish(const CommDev& c, int one_thread_fence) {
+  if (one_thread_fence) {
+    // bar.sync orders the block's stores before thread 0's fence; the fence is cumulative
+    __syncthreads();
+    if (threadIdx.x == 0) __threadfence_system();
+  } else {
+    __threadfence_system();
+  }
   __syncthreads();
   if (c.world > 1 && static_cast<int>(threadIdx.x) < c.world)
     red_add_relaxed_sys_u32(c.signal[threadIdx.x] + SIG_PUB + c.rank, 1u);
@@ -165,7 +181,31 @@ __device__ __forceinline__ void fused_reduce_adamw_body(const RankArgs& a, const
   const bool fp32_everywhere = broadcast && c.world > 1 && a.publish_fp32;
   const bool bf16_everywhere = broadcast && c.world > 1;
 
-  for (int s = 0; s < a.nseg; ++s) {
+  // A short list of small segments (an MLP's leaves) is spread over disjoint block ranges so that all
+  // segments are in flight at once: one NVLink round trip for the launch instead of one per segment.
+  // Long or large lists keep the whole grid on one segment after the other.
+  int seg_lo = 0, seg_hi = a.nseg, vbid = bid, vnblocks = nblocks;
+  if (a.nseg > 1 && a.nseg <= 16) {
+    int first = 0, my_seg = -1, my_first = 0, my_need = 0;
+    bool fits = true;
+    for (int s = 0; s < a.nseg; ++s) {
+      const b200_seg sg = a.segs[s];
+      const bool vec = ((sg.row_len | sg.src_pitch | sg.src_off | sg.dst_off | sg.loc_off) & 3) == 0;
+      const int64_t items = static_cast<int64_t>(sg.rows) * sg.row_len;
+      const int64_t per_block = vec ? 256 * 4 * 4 : 256;        // elements one block covers in one pass
+      const int64_t need64 = (items + per_block - 1) / per_block;
+      if (need64 > nblocks) { fits = false; break; }
+      const int need = need64 < 1 ? 1 : static_cast<int>(need64);
+      if (bid >= first && bid < first + need) { my_seg = s; my_first = first; my_need = need; }
+      first += need;
+    }
+    if (fits && first <= nblocks) {
+      if (my_seg < 0) { seg_lo = seg_hi = 0; }
+      else { seg_lo = my_seg; seg_hi = my_seg + 1; vbid = bid - my_first; vnblocks = my_need; }
+    }
+  }
+
+  for (int s = seg_lo; s < seg_hi; ++s) {
     const b200_seg sg = a.segs[s];
     const bool vec = ((sg.row_len | sg.src_pitch | sg.src_off | sg.dst_off | sg.loc_off) & 3) == 0;
     // Segments that several ranks reduce redundantly (replicated leaves of an FSDP run) are summed
@@ -175,9 +215,9 @@ __device__ __forceinline__ void fused_reduce_adamw_body(const RankArgs& a, const
     if (vec) {
       const int rl4 = sg.row_len >> 2;
       const int64_t total4 = static_cast<int64_t>(sg.rows) * rl4;   // multi-row segments: < 2^31 (checked by the engine)
-      const int64_t nthreads = static_cast<int64_t>(nblocks) * blockDim.x;
+      const int64_t nthreads = static_cast<int64_t>(vnblocks) * blockDim.x;
       constexpr int U = 4;   // independent 16-byte vectors per thread per iteration (memory-level parallelism)
-      for (int64_t i0 = static_cast<int64_t>(bid) * blockDim.x + threadIdx.x; i0 < total4; i0 += nthreads * U) {
+      for (int64_t i0 = static_cast<int64_t>(vbid) * blockDim.x + threadIdx.x; i0 < total4; i0 += nthreads * U) {
         // per vector only (row, col) are kept (32-bit); the three 64-bit offsets are rebuilt where used
         uint32_t vrow[U], vcol[U];
         bool ok[U];
@@ -269,8 +309,8 @@ __device__ __forceinline__ void fused_reduce_adamw_body(const RankArgs& a, const
     } else {
       // scalar path for odd shapes (never hit by the padded layouts the engines build)
       const int64_t total = static_cast<int64_t>(sg.rows) * sg.row_len;
-      for (int64_t i = static_cast<int64_t>(bid) * blockDim.x + threadIdx.x; i < total;
-           i += static_cast<int64_t>(nblocks) * blockDim.x) {
+      for (int64_t i = static_cast<int64_t>(vbid) * blockDim.x + threadIdx.x; i < total;
+           i += static_cast<int64_t>(vnblocks) * blockDim.x) {
         const int64_t row = i / sg.row_len, col = i - row * sg.row_len;
         const int64_t src = sg.src_off + row * sg.src_pitch + col;
         const int64_t loc = sg.loc_off + i;
@@ -309,7 +349,7 @@ __device__ __forceinline__ void fused_reduce_adamw_body(const RankArgs& a, const
     }
     a.metrics_acc[threadIdx.x] += acc;
   }
-  publish(c);
+  if (a.defer_publish != 1) publish(c, a.defer_publish == 2);
   stamp(a, bid, 3);
   // End-of-step bookkeeping folded into the last update of the step: the block that finishes last
   // (self-resetting counter) advances the RNG key and the step counter. Every block read the step
@@ -569,6 +609,7 @@ static int fill_rank_args(RankArgs* ra, const b200_fused_update_args* u) {
   }
   ra->timeout_ns = comm_timeout_ns();
   ra->stamps = g_stamps;
+  ra->defer_publish = comm_defer_publish() ? 1 : (g_defer_publish == 2 ? 2 : 0);
   return 0;
 }
 
@@ -588,6 +629,9 @@ using namespace b200;
 extern "C" void b200_comm_set_timeout_ms(long long ms) {
   g_timeout_ns = ms > 0 ? static_cast<uint64_t>(ms) * 1000000ull : 0;
 }
+
+extern "C" void b200_comm_set_defer_publish(int on) { g_defer_publish = on < 0 ? -1 : (on > 2 ? 0 : on); }
+extern "C" int b200_comm_get_defer_publish(void) { return comm_defer_publish() ? 1 : 0; }
 
 extern "C" void b200_comm_set_stamps(void* dev_u64) { g_stamps = static_cast<unsigned long long*>(dev_u64); }
 

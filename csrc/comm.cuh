@@ -16,6 +16,10 @@
 //                        rank's own publishes, so "everything published so far has landed here" is
 //                        PUB[p] >= PUB[rank] for every p: the end barrier of the update kernel is
 //                        split-phase, its second half runs in the next step's first kernel.
+//   PUB2[peer]           deferred variant (b200_comm_set_defer_publish): the update kernel ends without a
+//                        fence; the next step's first kernel stores this rank's launch count into every
+//                        peer's PUB2 word (the update's stores are complete at its kernel boundary) and
+//                        waits for theirs.
 //   METRICS[peer][8]     (epoch tag, value) pairs: per-step metric partial sums, one 8-byte store
 //                        each, validated by the tag instead of by a fence.
 #pragma once
@@ -28,6 +32,7 @@ constexpr int MAX_WORLD = 8;
 constexpr int SIG_READY = 0;                                               // [MAX_BLOCKS][MAX_WORLD]
 constexpr int SIG_EPOCH = SIG_READY + B200_COMM_MAX_BLOCKS * MAX_WORLD;    // [MAX_BLOCKS]
 constexpr int SIG_PUB = SIG_EPOCH + B200_COMM_MAX_BLOCKS;                  // [MAX_WORLD]
+constexpr int SIG_PUB2 = SIG_PUB + MAX_WORLD;                              // [MAX_WORLD]
 constexpr int SIG_METRICS = SIG_PUB + 2 * MAX_WORLD;                       // [MAX_WORLD][8][2]
 constexpr int SIG_END = SIG_METRICS + MAX_WORLD * 8 * 2;
 static_assert(SIG_END <= B200_SIGNAL_WORDS, "signal buffer too small");
@@ -36,6 +41,8 @@ static_assert((SIG_METRICS & 1) == 0, "metric slots are 8-byte pairs");
 // Host-side settings (comm.cu): how long a rank waits for a peer before it gives up, and an
 // optional device buffer for per-phase globaltimer stamps.
 uint64_t comm_timeout_ns();
+bool comm_defer_publish();
+struct SignalPeers { uint32_t* p[MAX_WORLD]; };
 
 #ifdef __CUDACC__
 
@@ -89,6 +96,17 @@ __device__ __forceinline__ void wait_published(const uint32_t* sig, int rank, in
   if (world > 1 && static_cast<int>(threadIdx.x) < world) {
     const uint32_t want = ld_relaxed_sys_u32(sig + SIG_PUB + rank);
     spin_until_reached(sig + SIG_PUB + threadIdx.x, want, timeout_ns, rank, threadIdx.x, 1);
+  }
+  __syncthreads();
+}
+// Deferred variant: the publish itself happens here, one kernel boundary after the update's stores.
+// The count of fused launches so far (block 0's exchange counter) is the value every rank expects.
+__device__ __forceinline__ void publish_and_wait(const uint32_t* sig, const SignalPeers& peers, int rank, int world,
+                                                 uint64_t timeout_ns) {
+  if (world > 1 && static_cast<int>(threadIdx.x) < world) {
+    const uint32_t want = ld_relaxed_sys_u32(sig + SIG_EPOCH);
+    if (blockIdx.x == 0) st_relaxed_sys_u32(peers.p[threadIdx.x] + SIG_PUB2 + rank, want);
+    spin_until_reached(sig + SIG_PUB2 + threadIdx.x, want, timeout_ns, rank, threadIdx.x, 1);
   }
   __syncthreads();
 }

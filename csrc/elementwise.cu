@@ -493,12 +493,16 @@ __global__ void rng_split_kernel(uint64_t* key, uint64_t* out_step, uint64_t sal
 // small fp32 regions (step metrics, bias-gradient vectors).
 __global__ void cast_zero_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int64_t n,
                                  float* __restrict__ z0, int64_t n0, float* __restrict__ z1, int64_t n1,
-                                 const uint32_t* __restrict__ sig, int rank, int world, uint64_t timeout_ns) {
+                                 const uint32_t* __restrict__ sig, int rank, int world, uint64_t timeout_ns,
+                                 const SignalPeers peers, int deferred) {
   pdl_sync();
   // First kernel of a step: the peers must have finished the previous step's update (they publish
   // into our parameters and read our gradients) before anything here clears a gradient region or a
   // later kernel reads a weight. See comm.cuh.
-  if (sig != nullptr) wait_published(sig, rank, world, timeout_ns);
+  if (sig != nullptr) {
+    if (deferred) publish_and_wait(sig, peers, rank, world, timeout_ns);
+    else wait_published(sig, rank, world, timeout_ns);
+  }
   const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
   const int64_t tid = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   const int64_t n4 = n >> 2;
@@ -680,11 +684,11 @@ extern "C" int b200_rng_split_bump(uint64_t* key, uint64_t* out_step, uint64_t s
 
 extern "C" int b200_cast_zero(const float* src, void* dst, int64_t n, float* z0, int64_t n0, float* z1, int64_t n1,
                               void* stream) {
-  return b200_cast_zero_wait(src, dst, n, z0, n0, z1, n1, nullptr, 0, 1, stream);
+  return b200_cast_zero_wait(src, dst, n, z0, n0, z1, n1, nullptr, nullptr, 0, 1, stream);
 }
 
 extern "C" int b200_cast_zero_wait(const float* src, void* dst, int64_t n, float* z0, int64_t n0, float* z1, int64_t n1,
-                                   const void* signal_local, int rank, int world,
+                                   const void* signal_local, void* const* peer_signal, int rank, int world,
                               void* stream) {
   B200_REQUIRE(n >= 0 && n0 >= 0 && n1 >= 0, "cast_zero: negative size");
   B200_REQUIRE(n == 0 || ((reinterpret_cast<uintptr_t>(src) & 15) == 0 && (reinterpret_cast<uintptr_t>(dst) & 7) == 0),
@@ -692,9 +696,17 @@ extern "C" int b200_cast_zero_wait(const float* src, void* dst, int64_t n, float
   int64_t work = n / 4 + 1;
   if (n0 > work) work = n0;
   if (n1 > work) work = n1;
+  SignalPeers peers;
+  memset(&peers, 0, sizeof(peers));
+  const bool deferred = world > 1 && signal_local != nullptr && comm_defer_publish();
+  if (deferred) {
+    B200_REQUIRE(peer_signal != nullptr && world <= MAX_WORLD, "cast_zero_wait: deferred publish needs the peers' signal buffers");
+    for (int i = 0; i < world; ++i) peers.p[i] = static_cast<uint32_t*>(peer_signal[i]);
+  }
   B200_CUDA(launch_k(cast_zero_kernel, dim3(stream_grid(work, 256)), dim3(256), 0, static_cast<cudaStream_t>(stream), src,
                      static_cast<__nv_bfloat16*>(dst), n, z0, n0, z1, n1,
-                     world > 1 ? static_cast<const uint32_t*>(signal_local) : nullptr, rank, world, comm_timeout_ns()));
+                     world > 1 ? static_cast<const uint32_t*>(signal_local) : nullptr, rank, world, comm_timeout_ns(),
+                     peers, deferred ? 1 : 0));
   B200_CUDA(cudaGetLastError());
   return 0;
 }

@@ -344,9 +344,15 @@ long long b200_fused_update_emulated_scratch_bytes(void);
  * b200_cast_zero_wait instead): returns when every publish this rank has issued so far has landed
  * from every peer too. signal_local: this rank's own signal buffer. */
 int b200_comm_wait_published(const void* signal_local, int rank, int world, void* stream);
-/* b200_cast_zero preceded by that wait inside the same kernel. signal_local = NULL or world = 1: no wait. */
+/* b200_cast_zero preceded by that wait inside the same kernel. signal_local = NULL or world = 1: no wait.
+ * peer_signal (host array[world]) is needed only in the deferred-publish mode below. */
 int b200_cast_zero_wait(const float* src, void* dst, int64_t n, float* z0, int64_t n0, float* z1, int64_t n1,
-                        const void* signal_local, int rank, int world, void* stream);
+                        const void* signal_local, void* const* peer_signal, int rank, int world, void* stream);
+/* Deferred publish (default off, or B200DIST_DEFER_PUBLISH=1): the update kernel ends without the
+ * system fence + "published" increments; the next step's b200_cast_zero_wait sends the signal (the
+ * update's stores are complete at its kernel boundary) and then waits. 1 = on, 0 = off, -1 = environment. */
+void b200_comm_set_defer_publish(int on);
+int b200_comm_get_defer_publish(void);
 /* How long a rank polls for a peer before the kernel traps (default 30 s, or the environment's
  * B200DIST_COMM_TIMEOUT_MS): a dead peer makes the survivors' launches fail instead of hang. */
 void b200_comm_set_timeout_ms(long long ms);

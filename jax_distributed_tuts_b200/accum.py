@@ -7,10 +7,16 @@ util.py:77) and metrics *summed* (util.py:75).
 ``accum_grads_scan`` is the reference's ``lax.scan`` variant (one compiled body instead of n
 unrolled copies, util.py:81-137): zero-initialised carries with the shapes of one minibatch
 step (util.py:123-129) and the same body applied to ``narrow``-ed windows of the batch
-(the ``dynamic_slice_in_dim`` of util.py:97-105). There is no tracing compiler here, so in the
-generic tier the body simply runs n times; the compiled-once counterpart lives in the fused
-engines, whose whole step is one captured CUDA graph (and which can fold the minibatch loop
-into the GEMMs themselves, ``engine.MLPEngine(fuse_minibatches=True)``).
+(the ``dynamic_slice_in_dim`` of util.py:97-105). On CPU the body simply runs n times. On a GPU
+the body (forward + backward of one minibatch + accumulation into the carry) is captured ONCE as
+a CUDA graph over static buffers and replayed n times per step and on every later step
+(``ScanBody``): the "compile one body instead of n" of the reference without a tracing compiler.
+Because a replayed graph cannot take a different host-side RNG salt per minibatch, the captured
+body derives minibatch i's stream on the device (``rng.rebase(keys[i])`` written into a fixed
+key buffer): dropout masks are a different, equally valid per-minibatch stream than the loop's;
+with dropout off the two variants agree bit for bit. The fused engines go further: their whole
+step is one graph and the minibatch loop is folded into the GEMMs
+(``engine.MLPEngine(fuse_minibatches=True)``).
 """
 from __future__ import annotations
 
@@ -21,7 +27,7 @@ import torch
 from . import rng as _rng
 from .autodiff import value_and_grad
 from .state import Batch, Metrics, TrainState
-from .tree import Pytree, is_partitioned, tree_map
+from .tree import Pytree, is_partitioned, tree_leaves, tree_map
 
 
 def _add(a, b):
@@ -52,11 +58,93 @@ def accum_grads_loop(batch: Batch, state: TrainState, key: _rng.Key, n_minbatch:
     return grads, metrics
 
 
+class ScanBody:
+    """One minibatch step (``value_and_grad(loss_fn)`` + accumulation into the carry) captured as a
+    CUDA graph. Static buffers: a copy of the parameters, one minibatch of inputs / labels, the RNG
+    key state, the gradient and metric carries. ``run`` = zero the carries, then per minibatch copy
+    the window into the static batch, write its key, replay."""
+
+    def __init__(self, state: TrainState, example: Batch, loss_fn: Callable):
+        dev = example.inputs.device
+        clone = lambda p: p.replace(value=p.value.detach().clone()) if is_partitioned(p) else p.detach().clone()
+        self.params = tree_map(clone, state.params, is_leaf=is_partitioned)
+        self.inputs, self.labels = example.inputs.clone(), example.labels.clone()
+        self.key_buf = torch.zeros(1, dtype=torch.int64, device=dev)
+        self.apply_fn, self.loss_fn = state.apply_fn, loss_fn
+        self.grad_fn = value_and_grad(loss_fn, has_aux=True)
+        zeros = lambda x: (x.replace(value=torch.zeros_like(x.value)) if is_partitioned(x) else torch.zeros_like(x))
+        self.grads = tree_map(zeros, self.params, is_leaf=is_partitioned)
+        self.metric_tensors = None      # flat list of accumulated tensor-valued metric entries
+        self.metric_template = None
+        # warm-up on a side stream (lazy initialisation must not happen inside the capture), then capture
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            self._body(first=True)
+        torch.cuda.current_stream().wait_stream(s)
+        torch.cuda.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self._body(first=False)
+        self.replays = 0
+
+    def _body(self, first: bool) -> None:
+        key = _rng.Key(self.key_buf, 0)
+        (_, step_metric), step_grad = self.grad_fn(self.params, self.apply_fn, Batch(self.inputs, self.labels), key)
+        flat = []
+
+        def collect(x):
+            if isinstance(x, torch.Tensor):
+                flat.append(x)
+            return x
+        tree_map(collect, step_metric)
+        if first:
+            self.metric_template = step_metric
+            self.metric_tensors = [torch.zeros_like(t) for t in flat]
+            return
+        tree_map(lambda g, sg: (g.value if is_partitioned(g) else g).add_(sg.value if is_partitioned(sg) else sg),
+                 self.grads, step_grad, is_leaf=is_partitioned)
+        for acc, t in zip(self.metric_tensors, flat):
+            acc.add_(t)
+
+    def run(self, batch: Batch, state: TrainState, keys, n_minbatch: int) -> Tuple[Pytree, Metrics]:
+        mbs = self.inputs.shape[0]
+        tree_map(lambda dst, src: (dst.value if is_partitioned(dst) else dst).copy_(src.value if is_partitioned(src) else src),
+                 self.params, state.params, is_leaf=is_partitioned)
+        tree_map(lambda g: (g.value if is_partitioned(g) else g).zero_(), self.grads, is_leaf=is_partitioned)
+        for t in self.metric_tensors:
+            t.zero_()
+        for i in range(n_minbatch):
+            self.inputs.copy_(batch.inputs.narrow(0, i * mbs, mbs))
+            self.labels.copy_(batch.labels.narrow(0, i * mbs, mbs))
+            self.key_buf.copy_(_rng.rebase(keys[i]).base)
+            self.graph.replay()
+            self.replays += 1
+        grads = tree_map(lambda g: g.replace(value=g.value / n_minbatch) if is_partitioned(g) else g / n_minbatch,
+                         self.grads, is_leaf=is_partitioned)
+        it = iter(self.metric_tensors)
+        # tensor entries come from the accumulators, host numbers (row counts) are multiplied out
+        metrics = tree_map(lambda x: next(it).clone() if isinstance(x, torch.Tensor) else x * n_minbatch, self.metric_template)
+        return grads, metrics
+
+
+_SCAN_CACHE: dict = {}
+
+
 def accum_grads_scan(batch: Batch, state: TrainState, key: _rng.Key, n_minbatch: int,
                      loss_fn: Callable) -> Tuple[Pytree, Metrics]:
     bs = batch.inputs.shape[0]
     min_batch_size = bs // n_minbatch
     keys = _rng.split(key, n_minbatch)
+    if batch.inputs.is_cuda and key.base.is_cuda:
+        leaves = [p.value if is_partitioned(p) else p for p in tree_leaves(state.params, is_leaf=is_partitioned)]
+        sig = (id(loss_fn), id(state.apply_fn), min_batch_size, tuple(batch.inputs.shape[1:]), batch.inputs.dtype,
+               batch.labels.dtype, tuple((tuple(t.shape), t.dtype) for t in leaves), str(batch.inputs.device))
+        body = _SCAN_CACHE.get(sig)
+        if body is None:
+            body = ScanBody(state, batch.slice(0, min_batch_size), loss_fn)
+            _SCAN_CACHE[sig] = body
+        return body.run(batch, state, keys, n_minbatch)
     grad_fn = value_and_grad(loss_fn, has_aux=True)
 
     def minibatch_step(idx: int):

@@ -6,13 +6,23 @@
     psum_scatter(tiled)      param_sharding.py:136
     ppermute                 intended by pipeline_parallel.py (absent there)
 
-Transport is torch.distributed on the axis' communicator: NCCL over NVLink/NVSwitch on GPUs,
-gloo on CPU. These calls are the *baseline* transport and the fallback for odd shapes; the
-hot paths (gradient all-reduce + optimizer, reduce-scatter + optimizer, all-gather into the
-GEMM) are the fused kernels in ``comm/fused.py`` + ``csrc/comm.cu``.
+Three transports sit behind the same calls:
+
+    "fused"  one sm_100a kernel per collective over NVSwitch peer / multicast memory
+             (``comm/fused.py`` + ``csrc/comm.cu``: flag exchange, ``multimem.ld_reduce``,
+             ``multimem.st``), on a symmetric workspace owned by the mesh axis. GPUs only.
+    "nccl"   torch.distributed on the axis' NCCL communicator (the baseline transport).
+    "gloo"   torch.distributed on CPU processes (the fake-cluster mode, util.py:31-38).
+
+``set_backend("auto")`` (default) uses NCCL on GPUs and gloo on CPU; ``set_backend("fused")`` or
+``B200DIST_COLLECTIVES=fused`` switches psum / pmean / psum_scatter / all_gather on GPUs to the
+fused kernels (anything they do not handle, and ppermute / send_recv, stay on NCCL: pipeline
+traffic is point-to-point by design). The fused *optimizer* paths (gradient all-reduce + AdamW,
+reduce-scatter + sharded AdamW, all-gather inside the GEMM) are in ``engine/``.
 """
 from __future__ import annotations
 
+import os
 from typing import Optional, Sequence, Tuple
 
 import torch
@@ -20,6 +30,28 @@ import torch.distributed as dist
 
 from ..mesh import AxisNames, Mesh, current_mesh
 from ..tree import Pytree, tree_map
+
+
+_BACKEND = os.environ.get("B200DIST_COLLECTIVES", "auto")
+fused_calls = 0      # number of collectives served by the fused kernels (tests / diagnostics)
+
+
+def set_backend(name: str) -> None:
+    """"auto" | "fused" | "nccl" | "gloo" (the last two both mean: torch.distributed on the axis group)."""
+    global _BACKEND
+    assert name in ("auto", "fused", "nccl", "gloo"), name
+    _BACKEND = name
+
+
+def get_backend() -> str:
+    return _BACKEND
+
+
+def _use_fused(m: Mesh) -> bool:
+    if _BACKEND != "fused":
+        return False
+    from . import fused
+    return fused.available(m)
 
 
 def _mesh(mesh: Optional[Mesh]) -> Mesh:
@@ -45,6 +77,13 @@ def _psum_leaf(x, axis_name, mesh: Mesh, mean: bool):
     if n == 1:
         return x
     t, was_tensor = _as_tensor(x, mesh.device)
+    if _use_fused(mesh):
+        from . import fused
+        got = fused.psum(t, axis_name, mesh, mean)
+        if got is not None:
+            global fused_calls
+            fused_calls += 1
+            return got if was_tensor else got.item()
     out = t.clone() if was_tensor else t
     if out.dtype in (torch.bfloat16, torch.float16) and not out.is_cuda:
         tmp = out.float()
@@ -75,8 +114,16 @@ def all_gather(x: torch.Tensor, axis_name: AxisNames, *, axis: int = 0, tiled: b
     if n == 1:
         return x if tiled else x.unsqueeze(axis)
     xc = x.contiguous()
-    out = torch.empty((n,) + tuple(xc.shape), dtype=xc.dtype, device=xc.device)
-    dist.all_gather_into_tensor(out.view(-1), xc.view(-1), group=m.group(axis_name))
+    out = None
+    if _use_fused(m):
+        from . import fused
+        out = fused.all_gather(xc, axis_name, m)
+        if out is not None:
+            global fused_calls
+            fused_calls += 1
+    if out is None:
+        out = torch.empty((n,) + tuple(xc.shape), dtype=xc.dtype, device=xc.device)
+        dist.all_gather_into_tensor(out.view(-1), xc.view(-1), group=m.group(axis_name))
     if not tiled:
         return out.movedim(0, axis)
     # [n, ..., d_axis, ...] -> [..., n*d_axis, ...]
@@ -99,6 +146,13 @@ def psum_scatter(x: torch.Tensor, axis_name: AxisNames, *, scatter_dimension: in
     # bring the scattered dim to the front in n chunks
     chunks = x.movedim(d, 0).reshape((n, x.shape[d] // n) + tuple(s for i, s in enumerate(x.shape) if i != d))
     chunks = chunks.contiguous()
+    if _use_fused(m):
+        from . import fused
+        got = fused.psum_scatter(chunks, axis_name, m)
+        if got is not None:
+            global fused_calls
+            fused_calls += 1
+            return got.movedim(0, d)
     out = torch.empty_like(chunks[0])
     if chunks.is_cuda:
         dist.reduce_scatter_tensor(out.view(-1), chunks.view(-1), op=dist.ReduceOp.SUM, group=m.group(axis_name))

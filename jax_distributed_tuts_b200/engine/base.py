@@ -124,12 +124,23 @@ class FlatLayout:
 class SymmetricArena:
     """One symmetric-memory allocation carved into named sub-buffers.
 
-    With world > 1 the arena comes from ``torch.distributed._symmetric_memory`` (VMM allocation
-    mapped into every rank, NVLS multicast address when the fabric supports it); with world == 1
-    it is an ordinary device allocation. Sub-buffers are 1 KiB aligned."""
+    With more than one rank the arena comes from ``torch.distributed._symmetric_memory`` (VMM
+    allocation mapped into every rank of the group, NVLS multicast address when the fabric supports
+    it); with one rank it is an ordinary device allocation. Sub-buffers are 1 KiB aligned.
 
-    def __init__(self, sizes_bytes: Dict[str, int], mesh: Mesh, device: torch.device):
-        self.world, self.rank = mesh.size, mesh.rank
+    ``axes`` restricts the arena to the ranks of one mesh axis (or axis subset): the rendezvous runs
+    on that axis' communicator, ``rank`` / ``world`` are the coordinates within it and the multicast
+    address covers exactly those GPUs (a per-axis symmetric group for N-D meshes)."""
+
+    def __init__(self, sizes_bytes: Dict[str, int], mesh: Mesh, device: torch.device, axes=None):
+        if axes is None:
+            self.world, self.rank = mesh.size, mesh.rank
+            group = dist.group.WORLD if mesh.size > 1 else None
+        else:
+            self.world, self.rank = mesh.axis_size(axes), mesh.axis_index(axes)
+            group = mesh.group(axes)
+            ranks = mesh.group_ranks(axes)
+            assert self.world == 1 or ranks.index(mesh.rank) == self.rank, (ranks, mesh.rank, self.rank)
         self.offsets: Dict[str, int] = {}
         off = 0
         for name, nbytes in sizes_bytes.items():
@@ -140,7 +151,12 @@ class SymmetricArena:
         self.backend = "local"
         if self.world > 1:
             import torch.distributed._symmetric_memory as symm_mem
-            gname = dist.group.WORLD.group_name
+            gname = group.group_name
+            if hasattr(symm_mem, "enable_symm_mem_for_group"):
+                try:
+                    symm_mem.enable_symm_mem_for_group(gname)
+                except Exception:  # noqa: BLE001  (newer torch: every group is enabled)
+                    pass
             self.buf = symm_mem.empty(self.nbytes, dtype=torch.uint8, device=device)
             self.buf.zero_()
             hdl = symm_mem.rendezvous(self.buf, gname)
@@ -152,7 +168,7 @@ class SymmetricArena:
                 self.multicast_ptr = 0
             self.backend = "symm_mem+nvls" if self.multicast_ptr else "symm_mem+p2p"
             torch.cuda.synchronize()
-            dist.barrier()
+            dist.barrier(group=group)
         else:
             self.buf = torch.zeros(self.nbytes, dtype=torch.uint8, device=device)
             self.peer_ptrs = [self.buf.data_ptr()]
@@ -648,7 +664,8 @@ class FusedEngine:
         sig = None
         if self.world > 1 and not self.stub_collectives:
             sig = self.arena.peer_ptrs[self.rank] + self.arena.offsets["signal"]
-        K.cast_zero(src, dst, self.step_metrics, self._vec_grads, wait_signal=sig, rank=self.rank, world=self.world)
+        K.cast_zero(src, dst, self.step_metrics, self._vec_grads, wait_signal=sig, peer_signals=self.ctx.peer_signal,
+                    rank=self.rank, world=self.world)
 
     def _end_step(self, next_rng) -> None:
         """state.rng <- rebase(next_rng) (the salt folds into the device-resident key in place) and
@@ -783,10 +800,12 @@ class FusedEngine:
         captures it into a CUDA graph and replays it, later calls only replay. Every call performs
         exactly one real training step."""
         if not self.use_graph:
+            self._master_stale = True
             before = _lib.launch_count()
             self._launch_body()
             self.launches_per_step = _lib.launch_count() - before
             return
+        self._master_stale = True      # (replays do not pass through _sync_bucket)
         if self.graph is None:
             if not getattr(self, "_warmed", False):
                 s = torch.cuda.Stream()

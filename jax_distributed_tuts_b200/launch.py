@@ -46,6 +46,13 @@ def init_from_env(backend: Optional[str] = None) -> tuple[int, int, torch.device
         kw = {}
         if backend == "nccl":
             kw["device_id"] = device
+            # Failure detection: a collective whose peer died must abort the job, not hang.
+            # NCCL's watchdog tears the communicator down after the timeout; our own kernels that wait for
+            # a peer trap after B200DIST_COMM_TIMEOUT_MS (csrc/comm.cuh), which surfaces as a CUDA error.
+            os.environ.setdefault("TORCH_NCCL_ASYNC_ERROR_HANDLING", "1")
+            os.environ.setdefault("TORCH_NCCL_BLOCKING_WAIT", "0")
+            import datetime
+            kw["timeout"] = datetime.timedelta(seconds=int(os.environ.get("B200DIST_NCCL_TIMEOUT_S", "600")))
         dist.init_process_group(backend=backend, rank=rank, world_size=world, **kw)
     return rank, world, device
 

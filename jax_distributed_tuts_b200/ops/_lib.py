@@ -135,6 +135,10 @@ def _declare(lib: C.CDLL) -> None:
     lib.b200_set_pdl.argtypes = [C.c_int]
     lib.b200_comm_set_timeout_ms.restype = None
     lib.b200_comm_set_timeout_ms.argtypes = [C.c_longlong]
+    lib.b200_comm_set_defer_publish.restype = None
+    lib.b200_comm_set_defer_publish.argtypes = [C.c_int]
+    lib.b200_comm_get_defer_publish.restype = C.c_int
+    lib.b200_comm_get_defer_publish.argtypes = []
     lib.b200_comm_set_stamps.restype = None
     lib.b200_comm_set_stamps.argtypes = [C.c_void_p]
     lib.b200_fused_update_emulated_scratch_bytes.restype = C.c_longlong
@@ -156,7 +160,7 @@ def _declare(lib: C.CDLL) -> None:
         "b200_rng_split": [vp, vp, u64, u64, vp],
         "b200_rng_split_bump": [vp, vp, u64, u64, vp, vp],
         "b200_cast_zero": [vp, vp, i64, vp, i64, vp, i64, vp],
-        "b200_cast_zero_wait": [vp, vp, i64, vp, i64, vp, i64, vp, i32, i32, vp],
+        "b200_cast_zero_wait": [vp, vp, i64, vp, i64, vp, i64, vp, C.POINTER(C.c_void_p), i32, i32, vp],
         "b200_fused_update": [C.POINTER(FusedUpdateArgs), vp],
         "b200_fused_update_emulated": [C.POINTER(FusedUpdateArgs), i32, vp, vp],
         "b200_fused_collective": [C.POINTER(CollectiveArgs), vp],

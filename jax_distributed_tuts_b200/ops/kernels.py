@@ -211,15 +211,15 @@ def rng_split_bump_(key: torch.Tensor, salt_next: int, step_count: torch.Tensor)
 
 
 def cast_zero(src: Optional[torch.Tensor], dst: Optional[torch.Tensor], z0: Optional[torch.Tensor] = None,
-              z1: Optional[torch.Tensor] = None, *, wait_signal: Optional[int] = None, rank: int = 0,
-              world: int = 1) -> None:
+              z1: Optional[torch.Tensor] = None, *, wait_signal: Optional[int] = None, peer_signals=None,
+              rank: int = 0, world: int = 1) -> None:
     """bf16 cast of ``src`` into ``dst`` plus zeroing of up to two fp32 regions, one launch.
     ``wait_signal`` (address of this rank's signal buffer) makes the kernel first wait until every
     peer has published its part of the previous fused update (csrc/comm.cuh)."""
     _lib.check(_lib.lib().b200_cast_zero_wait(_ptr(src), _ptr(dst), src.numel() if src is not None else 0,
                                                _ptr(z0), z0.numel() if z0 is not None else 0,
                                                _ptr(z1), z1.numel() if z1 is not None else 0,
-                                               wait_signal if world > 1 else None, rank, world, _stream()))
+                                               wait_signal if world > 1 else None, peer_signals, rank, world, _stream()))
 
 
 def act_dropout_fwd(x: torch.Tensor, y: torch.Tensor, act, drop_key, drop_salt: int, drop_rate: float):

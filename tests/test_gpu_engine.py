@@ -266,3 +266,63 @@ def test_engine_head_variants_match_each_other(num_classes, fuse_xent):
             assert _mean_close(p_eng[k][kk], s_gen.params[k][kk], lr, steps), (k, kk)
     assert abs(float(m_gen["loss"][0]) / m_gen["loss"][1] - float(m_eng["loss"][0]) / m_eng["loss"][1]) < 2e-2
     assert float(m_gen["accuracy"][0]) == pytest.approx(float(m_eng["accuracy"][0]), abs=3)
+
+
+def test_accum_scan_is_a_captured_graph_and_equals_the_loop():
+    """accum_grads(use_scan=True) on a GPU replays ONE captured minibatch body (util.py:81-137 compiles one
+    body instead of n): same gradients as the loop with dropout off, and no per-minibatch kernel launches
+    from the host besides the key write."""
+    from jax_distributed_tuts_b200.accum import accum_grads, _SCAN_CACHE
+    from jax_distributed_tuts_b200.ops import _lib
+    cfg, _, model, state, batch = _setup("cpu", batch=64, dropout=0.0)
+    mesh_g = Mesh((1,), ("data",), device=torch.device("cuda"))
+    st, bg = _to(state, "cuda"), batch.to("cuda")
+    key = rng.PRNGKey(3, device="cuda")
+    with mesh_g:
+        g_loop, m_loop = accum_grads(st, bg, key, 4, dp.loss_fn, use_scan=False)
+        _SCAN_CACHE.clear()
+        g_scan, m_scan = accum_grads(st, bg, key, 4, dp.loss_fn, use_scan=True)      # captures
+        torch.cuda.synchronize()
+        before = _lib.launch_count()
+        g_scan2, m_scan2 = accum_grads(st, bg, key, 4, dp.loss_fn, use_scan=True)    # replays only
+        torch.cuda.synchronize()
+        launches = _lib.launch_count() - before
+    assert len(_SCAN_CACHE) == 1 and next(iter(_SCAN_CACHE.values())).replays == 8
+    assert launches <= 4, f"{launches} library launches for 4 replayed minibatches (only the key writes are expected)"
+    for a, b, c in zip(tree_leaves(g_loop), tree_leaves(g_scan), tree_leaves(g_scan2)):
+        assert torch.equal(a, b) and torch.equal(b, c)
+    assert torch.equal(m_loop["loss"][0], m_scan["loss"][0]) and m_loop["loss"][1] == m_scan["loss"][1] == 64
+    assert torch.equal(m_loop["accuracy"][0], m_scan2["accuracy"][0])
+
+
+def test_engine_gradients_match_fp32_pytorch():
+    """One fused MLP step with dropout off: the flat fp32 gradient buffer against autograd of the same model in
+    plain fp32 PyTorch on the bf16-rounded operands, element-wise (atol + rtol * |ref|), before any optimizer
+    arithmetic can blur a wrong sign or a missing term."""
+    from jax_distributed_tuts_b200.engine import MLPEngine
+    cfg, _, model, state, batch = _setup("cpu", batch=64, dropout=0.0)
+    mesh_g = Mesh((1,), ("data",), device=torch.device("cuda"))
+    with mesh_g:
+        eng = MLPEngine(cfg.model, mesh_g, mode="dp", batch_per_rank=64, lr=1e-3, num_minibatches=4,
+                        init_params=state.params, use_graph=False)
+        s_eng = eng.make_state(model, state.rng)
+        eng.train_step(s_eng, None, Batch(batch.inputs.pin_memory(), batch.labels.pin_memory()))
+        torch.cuda.synchronize()
+    bf = lambda t: t.to(torch.bfloat16).float()
+    P = {k: {kk: bf(v).clone().requires_grad_(True) for kk, v in sub.items()} for k, sub in state.params.items()}
+    x = bf(batch.inputs)
+    total = 0.0
+    for i in range(4):      # mean over minibatches of the minibatch-mean loss (util.py:58-77)
+        xs, ys = x[i * 16:(i + 1) * 16], batch.labels[i * 16:(i + 1) * 16]
+        pre = bf(xs @ P["input_dense"]["kernel"] + P["input_dense"]["bias"])
+        h = bf(torch.nn.functional.silu(pre))
+        logits = h @ P["output_dense"]["kernel"] + P["output_dense"]["bias"]
+        total = total + torch.nn.functional.cross_entropy(logits, ys) / 4
+    total.backward()
+    for k in ("input_dense", "output_dense"):
+        for kk in ("kernel", "bias"):
+            got = eng.layout.view(eng.g32, f"{k}/{kk}").float().cpu() / 4      # the buffer holds the sum over minibatches
+            ref = P[k][kk].grad
+            err = (got - ref).abs()
+            tol = 2e-4 + 3e-2 * ref.abs()
+            assert bool((err <= tol).all()), f"{k}/{kk}: {int((err > tol).sum())} of {err.numel()} elements off, max {err.max():.3e}"

@@ -35,7 +35,7 @@ def _adamw_ref(p, m, v, g, t, lr, b1, b2, eps, wd):
 class _Ranks:
     """W virtual ranks' buffers for the fused update, DP (broadcast) or FSDP-like (local shards)."""
 
-    def __init__(self, W: int, n: int, broadcast: bool, publish_fp32: bool, blocks: int):
+    def __init__(self, W: int, n: int, broadcast: bool, publish_fp32: bool, blocks: int, pieces: int = 1):
         import torch
         from jax_distributed_tuts_b200.ops import _lib
         self.W, self.n, self.broadcast, self.blocks = W, n, broadcast, blocks
@@ -62,9 +62,17 @@ class _Ranks:
         self.scratch = torch.zeros(int(_lib.lib().b200_fused_update_emulated_scratch_bytes()), dtype=torch.uint8, device=d)
         segs = []
         for r in range(W):
-            sg = _lib.Seg(src_off=r * self.sl, src_pitch=self.sl, dst_off=r * self.sl if broadcast else 0, loc_off=0,
-                          rows=1, row_len=self.sl, flags=0)
-            segs.append(torch.frombuffer(bytearray(bytes(sg)), dtype=torch.uint8).to(d))
+            # the rank's slice as `pieces` segments (multiples of 64 elements); the last one takes the
+            # ordered peer-load path like a replicated leaf would
+            cuts = [0] + [min(self.sl, (self.sl // pieces // 64 + 1) * 64 * (i + 1)) for i in range(pieces - 1)] + [self.sl]
+            raw = b""
+            for i in range(pieces):
+                lo, hi = cuts[i], cuts[i + 1]
+                sg = _lib.Seg(src_off=r * self.sl + lo, src_pitch=hi - lo, dst_off=(r * self.sl + lo) if broadcast else 0,
+                              loc_off=lo, rows=1, row_len=hi - lo,
+                              flags=_lib.SEG_ORDERED if (pieces > 1 and i == pieces - 1) else 0)
+                raw += bytes(sg)
+            segs.append(torch.frombuffer(bytearray(raw), dtype=torch.uint8).to(d))
         self.segs = segs
         for r in range(W):
             ctx = _lib.CommCtx()
@@ -79,7 +87,7 @@ class _Ranks:
             self.keep.append(end)
             u = self.args[r]
             u.ctx = C.pointer(ctx)
-            u.segs_dev, u.nseg, u.broadcast = segs[r].data_ptr(), 1, int(broadcast)
+            u.segs_dev, u.nseg, u.broadcast = segs[r].data_ptr(), pieces, int(broadcast)
             u.publish_fp32, u.nmetrics, u.blocks = int(publish_fp32), 2, blocks
             u.p_local = None if broadcast else self.p_loc[r].data_ptr()
             u.bf16_local = None if broadcast else self.b_loc[r].data_ptr()
@@ -106,10 +114,11 @@ class _Ranks:
                                                             torch.cuda.current_stream().cuda_stream))
 
 
-def check_fused_update(W: int, n: int, broadcast: bool, publish_fp32: bool, blocks: int, steps: int = 4) -> bool:
+def check_fused_update(W: int, n: int, broadcast: bool, publish_fp32: bool, blocks: int, steps: int = 4,
+                       pieces: int = 1) -> bool:
     import torch
     from jax_distributed_tuts_b200.ops import _lib
-    R = _Ranks(W, n, broadcast, publish_fp32, blocks)
+    R = _Ranks(W, n, broadcast, publish_fp32, blocks, pieces)
     gen = torch.Generator().manual_seed(11)
     for t in range(1, steps + 1):
         gs = [torch.randn(n, generator=gen) for _ in range(W)]
@@ -149,7 +158,7 @@ def check_fused_update(W: int, n: int, broadcast: bool, publish_fp32: bool, bloc
     pub = [int(R.signal[r][_lib.SIG_PUB + p].item()) for r in range(W) for p in range(W)]     # SIG_PUB block
     ok &= len(set(pub)) == 1 and pub[0] > 0
     print(f"  [{'ok' if ok else 'FAIL'}] fused update emulated: W={W} n={n} {'dp' if broadcast else 'fsdp'} "
-          f"publish_fp32={int(publish_fp32)} blocks={blocks} steps={steps} publishes/peer={pub[0]}", flush=True)
+          f"publish_fp32={int(publish_fp32)} blocks={blocks} segments={pieces} steps={steps} publishes/peer={pub[0]}", flush=True)
     return bool(ok)
 
 
@@ -221,7 +230,7 @@ def _dead_peer_child() -> None:
     print("SURVIVED")
 
 
-def group_comm_emulated() -> bool:
+def group_comm_emulated(dead_peer: bool = True) -> bool:
     from jax_distributed_tuts_b200.ops import _lib
     _lib.lib().b200_comm_set_timeout_ms(5000)
     ok = True
@@ -230,11 +239,15 @@ def group_comm_emulated() -> bool:
                                         (8, 8 * 64 * 5, True, False, 32), (8, 8 * 64 * 1000, True, False, 32),
                                         (4, 4 * 4096, False, False, 16), (8, 8 * 64 * 33, False, False, 8)]:
             ok &= check_fused_update(W, n, bc, p32, blocks)
+        # several segments per rank: spread over block ranges (small) or one after the other (large)
+        ok &= check_fused_update(4, 4 * 4096, False, False, 16, pieces=3)
+        ok &= check_fused_update(8, 8 * 64 * 1000, True, False, 8, pieces=4)
         ok &= check_collectives(4, 4 * 4 * 1000, 8)
         ok &= check_collectives(8, 8 * 4 * 64, 32)
     finally:
         _lib.lib().b200_comm_set_timeout_ms(0)
-    ok &= check_dead_peer()
+    if dead_peer:
+        ok &= check_dead_peer()
     return bool(ok)
 
 
@@ -242,6 +255,6 @@ if __name__ == "__main__":
     if "--dead-peer" in sys.argv:
         _dead_peer_child()
         sys.exit(0)
-    good = group_comm_emulated()
+    good = group_comm_emulated(dead_peer="--no-dead-peer" not in sys.argv)
     print("COMM EMULATED CHECK", "PASS" if good else "FAIL")
     sys.exit(0 if good else 1)
