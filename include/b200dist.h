@@ -348,9 +348,14 @@ int b200_comm_wait_published(const void* signal_local, int rank, int world, void
  * peer_signal (host array[world]) is needed only in the deferred-publish mode below. */
 int b200_cast_zero_wait(const float* src, void* dst, int64_t n, float* z0, int64_t n0, float* z1, int64_t n1,
                         const void* signal_local, void* const* peer_signal, int rank, int world, void* stream);
-/* Deferred publish (default off, or B200DIST_DEFER_PUBLISH=1): the update kernel ends without the
- * system fence + "published" increments; the next step's b200_cast_zero_wait sends the signal (the
- * update's stores are complete at its kernel boundary) and then waits. 1 = on, 0 = off, -1 = environment. */
+/* How the update kernel orders its parameter stores before the "published" increments
+ * (B200DIST_DEFER_PUBLISH in the environment, or this call; -1 = back to the environment):
+ *   2 (default)  one thread per block executes fence.sys behind a block barrier (the fence is cumulative);
+ *   0            every thread executes fence.sys (measured ~5 us slower on a 70 us step);
+ *   1            deferred: the update kernel ends without fence or increments; the next step's
+ *                b200_cast_zero_wait sends the signal (the update's stores are complete at its kernel
+ *                boundary) and then waits. Relies on full kernel-boundary ordering between the two
+ *                kernels (CUDA graph replays, plain stream order), not on programmatic dependent launch. */
 void b200_comm_set_defer_publish(int on);
 int b200_comm_get_defer_publish(void);
 /* How long a rank polls for a peer before the kernel traps (default 30 s, or the environment's

@@ -208,7 +208,7 @@ class FusedEngine:
                  eps: float = 1e-8, weight_decay: float = 1e-4, num_minibatches: int = 4,
                  data_axis_name: str = "data", shard_axis: Optional[str] = None, min_weight_size: int = 2 ** 18,
                  use_graph: bool = True, comm_blocks: int = 16, overlap: bool = True, fsdp_weights: str = "fused",
-                 publish_fp32: bool = False, stub_collectives: bool = False):
+                 publish_fp32: bool = False, stub_collectives: bool = False, deterministic: bool = False):
         if not torch.cuda.is_available():
             raise RuntimeError("the fused engine needs a CUDA device; use the generic tier on CPU")
         _lib.lib()  # fail loudly if the kernel library is missing
@@ -239,6 +239,13 @@ class FusedEngine:
         # tree (flat_params, checkpoints) gather the owners' slices first.
         self.publish_fp32 = publish_fp32
         self._master_stale = False
+        # Run-to-run bit reproducibility. The default schedules sum some things in arrival order:
+        # split-K partial tiles (red.global.add in the wgrad GEMMs), bias-gradient column sums added
+        # atomically from GEMM / cross-entropy / LayerNorm epilogues, the embedding gradient scatter,
+        # attention's dQ tile reduce-adds, and the loss / accuracy metric sums. With deterministic=True an
+        # engine that supports it switches every gradient-carrying one of those to a fixed order (metric
+        # sums stay atomics: they do not feed the parameters).
+        self.deterministic = deterministic
         # Measurement aid (bench.py "exposed comm"): the same step with every cross-GPU access removed.
         # Each rank updates its own part from its local gradients only; results are NOT a training run.
         self.stub_collectives = stub_collectives and self.world > 1

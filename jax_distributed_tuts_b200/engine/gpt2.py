@@ -49,6 +49,12 @@ class GPT2Engine(FusedEngine):
             kw["fsdp_weights"] = "gather" if tokens > 1024 else "fused"
         super().__init__(mesh, mode=mode, lr=lr, num_minibatches=num_minibatches,
                          data_axis_name=config.get("data_axis_name", "data"), **kw)
+        if self.deterministic:
+            raise NotImplementedError(
+                "GPT2Engine has no deterministic schedule: embedding_bwd scatters with atomics, attention backward "
+                "reduce-adds dQ tiles in arrival order, LayerNorm backward and the GELU' dgrad add their column sums "
+                "atomically, and the weight-gradient GEMMs use split-K; results are reproducible to fp32 rounding, "
+                "not bit for bit")
         self.cfg = config
         self.pdl = tokens < 4096       # long persistent kernels: dependent launch only ties up SMs (see FusedEngine.pdl)
         self.L, self.Hh, self.C = config.n_layer, config.n_head, config.d_model

@@ -138,30 +138,36 @@ class MLPEngine(FusedEngine):
         """Forward + backward of one row block (a minibatch, or all minibatches at once)."""
         logits = self.logits[:, : self.Cn]
         dlogits = self.dlogits[:, : self.Cn]
+        det = self.deterministic
+        sk = dict(split_k=1) if det else {}     # deterministic: no arrival-order sums (split-K, atomic column sums)
+        db2 = None if det else self.grad1d("output_dense/bias")
+        db1 = None if det else self.grad1d("input_dense/bias")
         drop = dict(drop_key=self.rng_base, drop_rate=self.rate, drop_salts=salts, drop_rows_per_salt=rows_per_salt)
         self.gemm_w(xs, "input_dense/kernel", self.h, bias=self.vec("input_dense/bias"), act="silu", pre=self.pre, **drop)
         w2_shard = self._weight("output_dense/kernel")[2]
         if self.fuse_xent and self.Cn <= 32 and not (w2_shard is not None and w2_shard[0]):     # not for a class-sharded head
             # head + softmax cross-entropy + its bias gradient in one launch: the logits stay in TMEM
             self.gemm_w(self.h, "output_dense/kernel", dlogits, bias=self.vec("output_dense/bias"), xent_labels=lab,
-                        xent_metrics=self.step_metrics, xent_scale=1.0 / self.mb, dbias=self.grad1d("output_dense/bias"))
+                        xent_metrics=self.step_metrics, xent_scale=1.0 / self.mb, dbias=db2)
         else:
             self.gemm_w(self.h, "output_dense/kernel", logits, bias=self.vec("output_dense/bias"))
-            K.softmax_xent(logits, lab, grad_scale=1.0 / self.mb, dlogits=dlogits, metrics=self.step_metrics,
-                           dbias=self.grad1d("output_dense/bias"))
+            K.softmax_xent(logits, lab, grad_scale=1.0 / self.mb, dlogits=dlogits, metrics=self.step_metrics, dbias=db2)
+        if det:
+            self.grad1d("output_dense/bias").add_(dlogits.float().sum(0))
         if self.fork_wgrad:
             # dW2 only depends on h and dlogits: in a latency-bound step it runs as a parallel branch of
             # the graph next to the dgrad -> dW1 chain instead of in front of it
             main = torch.cuda.current_stream()
             self.side_stream.wait_stream(main)
             with torch.cuda.stream(self.side_stream):
-                K.gemm(self.h, dlogits, self.grad2d("output_dense/kernel"), a_mn=True, b_mn=True, accumulate=accumulate)
+                K.gemm(self.h, dlogits, self.grad2d("output_dense/kernel"), a_mn=True, b_mn=True, accumulate=accumulate, **sk)
         else:
-            K.gemm(self.h, dlogits, self.grad2d("output_dense/kernel"), a_mn=True, b_mn=True, accumulate=accumulate)
-        self.gemm_wT(dlogits, "output_dense/kernel", self.dpre, bwd=True, aux=self.pre, act="silu",
-                     dbias=self.grad1d("input_dense/bias"), **drop)
+            K.gemm(self.h, dlogits, self.grad2d("output_dense/kernel"), a_mn=True, b_mn=True, accumulate=accumulate, **sk)
+        self.gemm_wT(dlogits, "output_dense/kernel", self.dpre, bwd=True, aux=self.pre, act="silu", dbias=db1, **drop)
+        if det:
+            self.grad1d("input_dense/bias").add_(self.dpre.float().sum(0))
         if last and self.overlap:
             # output layer's matrix: reduce + update under the rest of the backward. Queued only after
             # the dgrad above, the last reader of W2 in this step: the update rewrites W2 on every rank.
             self._sync_bucket_async(0)
-        K.gemm(xs, self.dpre, self.grad2d("input_dense/kernel"), a_mn=True, b_mn=True, accumulate=accumulate)
+        K.gemm(xs, self.dpre, self.grad2d("input_dense/kernel"), a_mn=True, b_mn=True, accumulate=accumulate, **sk)

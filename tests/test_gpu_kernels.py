@@ -30,3 +30,15 @@ def test_library_is_the_native_one():
     K.scale_(x, 2.0)
     torch.cuda.synchronize()
     assert _lib.launch_count() == before + 1 and x[0].item() == 2.0
+
+
+def test_no_kernel_writes_outside_its_outputs():
+    """Every kernel family on odd shapes with 4 KiB guard bands around every tensor (the stand-in for a memory
+    checker on this pool, see tools/smoke_all_kernels.py)."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "tools", "smoke_all_kernels.py"), "--guard"],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "0 overrun(s)" in r.stdout, (r.stdout + r.stderr)[-2000:]

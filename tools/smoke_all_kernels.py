@@ -10,6 +10,43 @@ from jax_distributed_tuts_b200.ops import kernels as K
 torch.manual_seed(0)
 bf = torch.bfloat16
 dev = "cuda"
+
+# Guard bands: with --guard every tensor this script creates sits in the middle of a larger allocation
+# whose 4 KiB on either side hold a byte pattern; after all kernels have run, every band must still hold
+# it. A kernel that stores outside the tensor it was given (partial tiles, odd pitches, tails) is caught
+# without a memory checker (compute-sanitizer is closed on this GPU pool).
+GUARD = "--guard" in sys.argv
+_BANDS = []
+_PAD = 4096
+
+
+def _guarded(t: torch.Tensor) -> torch.Tensor:
+    if not GUARD or not t.is_cuda:
+        return t
+    nbytes = t.numel() * t.element_size()
+    nb16 = (nbytes + 15) // 16 * 16
+    raw = torch.full((_PAD + nb16 + _PAD,), 0xA5, dtype=torch.uint8, device=t.device)
+    mid = raw[_PAD:_PAD + nbytes].view(t.dtype).view(t.shape)
+    mid.copy_(t)
+    _BANDS.append((raw, nbytes))
+    return mid
+
+
+for _name in ("randn", "empty", "zeros", "ones", "randint", "randn_like", "empty_like", "zeros_like"):
+    def _wrap(fn):
+        def inner(*a, **k):
+            return _guarded(fn(*a, **k))
+        return inner
+    setattr(torch, _name, _wrap(getattr(torch, _name)))
+
+
+def check_guards() -> int:
+    bad = 0
+    for raw, nbytes in _BANDS:
+        lo, hi = raw[:_PAD], raw[_PAD + nbytes:]
+        if not bool((lo == 0xA5).all()) or not bool((hi == 0xA5).all()):
+            bad += 1
+    return bad
 # GEMMs: plain, bias+gelu+pre, bwd gelu' with dbias, wgrad fp32 (split-K), fused cross-entropy head
 m, n, k = 256, 384, 320
 x = torch.randn(m, k, device=dev, dtype=bf); w = torch.randn(k, n, device=dev, dtype=bf) * 0.05
@@ -46,3 +83,7 @@ K.attention_fwd(qkv, o, lse, B, T, H)
 K.attention_bwd(qkv, o, torch.randn_like(o), lse, torch.empty_like(qkv), torch.empty(K.attention_bwd_scratch_numel(B, T, H), device=dev), B, T, H)
 torch.cuda.synchronize()
 print("all kernels launched and finished")
+if GUARD:
+    bad = check_guards()
+    print(f"guard bands: {len(_BANDS)} tensors, {bad} overrun(s)")
+    sys.exit(1 if bad else 0)
