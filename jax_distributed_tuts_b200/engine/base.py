@@ -225,7 +225,7 @@ class FusedEngine:
         self.shard_peer_ranks = list(mesh.group_ranks(self.shard_axis)) if (mode == "fsdp" and self.S > 1) else [self.rank]
         self.min_weight_size = min_weight_size
         self.use_graph = use_graph
-        self.comm_blocks = comm_blocks
+        self.comm_blocks = int(os.environ.get("B200DIST_COMM_BLOCKS", comm_blocks))     # (environment: tuning sweeps)
         self.overlap = overlap and self.world > 1
         # FSDP weight access: "fused" = the GEMM's TMA producer reads the peer shards in place (best
         # when the GEMM has few row tiles: every tile of the weight crosses NVLink once per row tile);
