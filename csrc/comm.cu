@@ -155,12 +155,181 @@ __device__ __forceinline__ void stamp(const RankArgs& a, int bid, int k) {
   if (a.stamps != nullptr && threadIdx.x == 0) a.stamps[bid * 8 + k] = globaltimer_ns();
 }
 
-__device__ __forceinline__ void fused_reduce_adamw_body(const RankArgs& a, const int bid, const int nblocks) {
+// Reduce + AdamW + publish of one segment by the blocks [0, vnblocks) of a (sub-)grid.
+__device__ __noinline__ void update_segment(const RankArgs& a, const b200_seg& sg, const int vbid, const int vnblocks,
+                                               const float c1, const float c2) {
   const CommDev& c = a.c;
   const b200_adamw_hparams& hp = a.hp;
   const int broadcast = a.broadcast;
   float* const m = a.m;
   float* const v = a.v;
+  const float* my_grad = c.grad[c.rank];
+  // DP: the fp32 master leaves the owner only when asked to (publish_fp32); the bf16 working copy
+  // always goes to every rank.
+  const bool fp32_everywhere = broadcast && c.world > 1 && a.publish_fp32;
+  const bool bf16_everywhere = broadcast && c.world > 1;
+    const bool vec = ((sg.row_len | sg.src_pitch | sg.src_off | sg.dst_off | sg.loc_off) & 3) == 0;
+  // Segments that several ranks reduce redundantly (replicated leaves of an FSDP run) are summed
+  // with peer loads in a fixed rank order, so that every replica computes bit-identical values;
+  // the in-switch reduction is not documented to return the same sum to different requesters.
+  const bool use_mc = c.mc_grad != nullptr && !(sg.flags & B200_SEG_ORDERED);
+  if (vec) {
+    const int rl4 = sg.row_len >> 2;
+    const int64_t total4 = static_cast<int64_t>(sg.rows) * rl4;   // multi-row segments: < 2^31 (checked by the engine)
+    const int64_t nthreads = static_cast<int64_t>(vnblocks) * blockDim.x;
+    constexpr int U = 4;   // independent 16-byte vectors per thread per iteration (memory-level parallelism)
+    for (int64_t i0 = static_cast<int64_t>(vbid) * blockDim.x + threadIdx.x; i0 < total4; i0 += nthreads * U) {
+      // per vector only (row, col) are kept (32-bit); the three 64-bit offsets are rebuilt where used
+      uint32_t vrow[U], vcol[U];
+      bool ok[U];
+      float4 g[U], pp[U], mm[U], vv[U];
+      float* p_base = broadcast ? c.param[c.rank] : a.p_local;
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int64_t i = i0 + u * nthreads;
+        ok[u] = i < total4;
+        const uint32_t ii = ok[u] ? static_cast<uint32_t>(i) : 0u;
+        // rows == 1 (every DP segment, contiguous FSDP shards) needs no division; otherwise the
+        // segment is far below 2^31 vectors and a 32-bit division is enough
+        vrow[u] = sg.rows == 1 ? 0u : ii / static_cast<uint32_t>(rl4);
+        vcol[u] = (ii - vrow[u] * static_cast<uint32_t>(rl4)) << 2;
+      }
+      auto src_of = [&](int u) { return sg.src_off + static_cast<int64_t>(vrow[u]) * sg.src_pitch + vcol[u]; };
+      auto loc_of = [&](int u) { return sg.loc_off + static_cast<int64_t>(vrow[u]) * sg.row_len + vcol[u]; };
+      auto dst_of = [&](int u) {
+        return (broadcast ? sg.dst_off : sg.loc_off) + static_cast<int64_t>(vrow[u]) * sg.row_len + vcol[u];
+      };
+      // ---- loads (all issued before any use; the peer-load path fetches m / v / p after its sums to
+      //      keep the registers for the peers' vectors) ----
+      const bool p2p = c.world > 1 && !use_mc;
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        if (!ok[u]) continue;
+        if (c.world == 1) g[u] = *reinterpret_cast<const float4*>(my_grad + src_of(u));
+        else if (use_mc) g[u] = mc_ld_reduce_f32x4(c.mc_grad + src_of(u));
+        else g[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (!p2p) {
+          mm[u] = *reinterpret_cast<float4*>(m + loc_of(u));
+          vv[u] = *reinterpret_cast<float4*>(v + loc_of(u));
+          pp[u] = *reinterpret_cast<float4*>(p_base + dst_of(u));
+        }
+      }
+      if (p2p) {
+        // Peer loads, PF peers in flight at a time (each load is an NVLink round trip), summed in a
+        // fixed order. DP slices are disjoint per rank: start at myself to spread the traffic.
+        // Segments reduced by every rank use the same order everywhere (see above).
+#pragma unroll 1
+        constexpr int PF = 2;
+        for (int k0 = 0; k0 < c.world; k0 += PF) {
+          float4 t4[PF][U];
+#pragma unroll
+          for (int kk = 0; kk < PF; ++kk) {
+            if (k0 + kk >= c.world) continue;
+            int peer = broadcast ? c.rank + k0 + kk : k0 + kk;
+            if (peer >= c.world) peer -= c.world;
+#pragma unroll
+            for (int u = 0; u < U; ++u)
+              if (ok[u]) t4[kk][u] = ld_sys_f32x4(c.grad[peer] + src_of(u));
+          }
+#pragma unroll
+          for (int kk = 0; kk < PF; ++kk) {
+            if (k0 + kk >= c.world) continue;
+#pragma unroll
+            for (int u = 0; u < U; ++u)
+              if (ok[u]) { g[u].x += t4[kk][u].x; g[u].y += t4[kk][u].y; g[u].z += t4[kk][u].z; g[u].w += t4[kk][u].w; }
+          }
+        }
+      }
+      if (p2p) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          if (!ok[u]) continue;
+          mm[u] = *reinterpret_cast<float4*>(m + loc_of(u));
+          vv[u] = *reinterpret_cast<float4*>(v + loc_of(u));
+          pp[u] = *reinterpret_cast<float4*>(p_base + dst_of(u));
+        }
+      }
+      // ---- AdamW + publish ----
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        if (!ok[u]) continue;
+        adamw1(pp[u].x, mm[u].x, vv[u].x, g[u].x * hp.grad_scale, hp, c1, c2);
+        adamw1(pp[u].y, mm[u].y, vv[u].y, g[u].y * hp.grad_scale, hp, c1, c2);
+        adamw1(pp[u].z, mm[u].z, vv[u].z, g[u].z * hp.grad_scale, hp, c1, c2);
+        adamw1(pp[u].w, mm[u].w, vv[u].w, g[u].w * hp.grad_scale, hp, c1, c2);
+        *reinterpret_cast<float4*>(m + loc_of(u)) = mm[u];
+        *reinterpret_cast<float4*>(v + loc_of(u)) = vv[u];
+        __nv_bfloat162 lo = __floats2bfloat162_rn(pp[u].x, pp[u].y), hi = __floats2bfloat162_rn(pp[u].z, pp[u].w);
+        const uint32_t w0 = *reinterpret_cast<uint32_t*>(&lo), w1 = *reinterpret_cast<uint32_t*>(&hi);
+        // fp32 master
+        if (!fp32_everywhere) {
+          *reinterpret_cast<float4*>(p_base + dst_of(u)) = pp[u];
+        } else if (c.mc_param != nullptr) {
+          mc_st_f32x4(c.mc_param + dst_of(u), pp[u]);
+        } else {
+#pragma unroll 1
+          for (int k = 0; k < c.world; ++k) {
+            int peer = c.rank + k;
+            if (peer >= c.world) peer -= c.world;
+            *reinterpret_cast<float4*>(c.param[peer] + dst_of(u)) = pp[u];
+          }
+        }
+        // bf16 working copy
+        if (!bf16_everywhere) {
+          __nv_bfloat16* b = broadcast ? c.bf16[c.rank] : a.bf16_local;
+          if (b != nullptr) *reinterpret_cast<uint2*>(b + dst_of(u)) = make_uint2(w0, w1);
+        } else if (c.mc_bf16 != nullptr) {
+          mc_st_b32x2(c.mc_bf16 + dst_of(u), w0, w1);
+        } else {
+#pragma unroll 1
+          for (int k = 0; k < c.world; ++k) {
+            int peer = c.rank + k;
+            if (peer >= c.world) peer -= c.world;
+            if (c.bf16[peer] != nullptr) *reinterpret_cast<uint2*>(c.bf16[peer] + dst_of(u)) = make_uint2(w0, w1);
+          }
+        }
+      }
+    }
+  } else {
+    // scalar path for odd shapes (never hit by the padded layouts the engines build)
+    const int64_t total = static_cast<int64_t>(sg.rows) * sg.row_len;
+    for (int64_t i = static_cast<int64_t>(vbid) * blockDim.x + threadIdx.x; i < total;
+         i += static_cast<int64_t>(vnblocks) * blockDim.x) {
+      const int64_t row = i / sg.row_len, col = i - row * sg.row_len;
+      const int64_t src = sg.src_off + row * sg.src_pitch + col;
+      const int64_t loc = sg.loc_off + i;
+      float g = 0.f;
+      for (int k = 0; k < c.world; ++k) g += *reinterpret_cast<const volatile float*>(c.grad[k] + src);
+      const int64_t dst = broadcast ? sg.dst_off + i : loc;
+      float* p_base = broadcast ? c.param[c.rank] : a.p_local;
+      float pp = p_base[dst], mm = m[loc], vv = v[loc];
+      adamw1(pp, mm, vv, g * hp.grad_scale, hp, c1, c2);
+      m[loc] = mm; v[loc] = vv;
+      if (broadcast) {
+        for (int k = 0; k < c.world; ++k) {
+          if (k == c.rank || a.publish_fp32) c.param[k][dst] = pp;
+          if (c.bf16[k] != nullptr) c.bf16[k][dst] = __float2bfloat16_rn(pp);
+        }
+      } else {
+        p_base[dst] = pp;
+        if (a.bf16_local != nullptr) a.bf16_local[dst] = __float2bfloat16_rn(pp);
+      }
+    }
+  }
+}
+
+// Blocks one pass over a segment needs (every thread: 4 vectors of 4 floats, or one scalar).
+__device__ __forceinline__ int segment_blocks(const b200_seg& sg) {
+  const bool vec = ((sg.row_len | sg.src_pitch | sg.src_off | sg.dst_off | sg.loc_off) & 3) == 0;
+  const int64_t items = static_cast<int64_t>(sg.rows) * sg.row_len;
+  const int64_t per_block = vec ? 256 * 4 * 4 : 256;
+  const int64_t need = (items + per_block - 1) / per_block;
+  return need < 1 ? 1 : need > (1 << 20) ? (1 << 20) : static_cast<int>(need);
+}
+
+__device__ __forceinline__ void fused_reduce_adamw_body(const RankArgs& a, const int bid, const int nblocks) {
+  const CommDev& c = a.c;
+  const b200_adamw_hparams& hp = a.hp;
   stamp(a, bid, 0);
   const uint32_t epoch = exchange(c, bid, a.timeout_ns);
   stamp(a, bid, 1);
@@ -177,163 +346,30 @@ __device__ __forceinline__ void fused_reduce_adamw_body(const RankArgs& a, const
   const float t = static_cast<float>(*a.step_count + 1);
   const float c1 = 1.0f / (1.0f - __powf(hp.beta1, t));
   const float c2 = 1.0f / (1.0f - __powf(hp.beta2, t));
-  const float* my_grad = c.grad[c.rank];
-  // DP: the fp32 master leaves the owner only when asked to (publish_fp32); the bf16 working copy
-  // always goes to every rank.
-  const bool fp32_everywhere = broadcast && c.world > 1 && a.publish_fp32;
-  const bool bf16_everywhere = broadcast && c.world > 1;
 
-  // A short list of small segments (an MLP's leaves) is spread over disjoint block ranges so that all
-  // segments are in flight at once: one NVLink round trip for the launch instead of one per segment.
-  // Long or large lists keep the whole grid on one segment after the other.
-  int seg_lo = 0, seg_hi = a.nseg, vbid = bid, vnblocks = nblocks;
-  if (a.nseg > 1 && a.nseg <= 16) {
-    int first = 0, my_seg = -1, my_first = 0, my_need = 0;
-    bool fits = true;
-    for (int s = 0; s < a.nseg; ++s) {
-      const b200_seg sg = a.segs[s];
-      const bool vec = ((sg.row_len | sg.src_pitch | sg.src_off | sg.dst_off | sg.loc_off) & 3) == 0;
-      const int64_t items = static_cast<int64_t>(sg.rows) * sg.row_len;
-      const int64_t per_block = vec ? 256 * 4 * 4 : 256;        // elements one block covers in one pass
-      const int64_t need64 = (items + per_block - 1) / per_block;
-      if (need64 > nblocks) { fits = false; break; }
-      const int need = need64 < 1 ? 1 : static_cast<int>(need64);
-      if (bid >= first && bid < first + need) { my_seg = s; my_first = first; my_need = need; }
-      first += need;
-    }
-    if (fits && first <= nblocks) {
-      if (my_seg < 0) { seg_lo = seg_hi = 0; }
-      else { seg_lo = my_seg; seg_hi = my_seg + 1; vbid = bid - my_first; vnblocks = my_need; }
-    }
-  }
-
-  for (int s = seg_lo; s < seg_hi; ++s) {
+  // Segments larger than a quarter of the grid take the whole grid, one after the other. Runs of
+  // smaller segments (an MLP's leaves, the bias / norm vectors of a transformer) are spread over
+  // disjoint block ranges so that a whole run is in flight at once: one NVLink round trip per run
+  // instead of one per segment.
+  const int small_limit = nblocks / 4 > 0 ? nblocks / 4 : 1;
+  for (int s = 0; s < a.nseg;) {
     const b200_seg sg = a.segs[s];
-    const bool vec = ((sg.row_len | sg.src_pitch | sg.src_off | sg.dst_off | sg.loc_off) & 3) == 0;
-    // Segments that several ranks reduce redundantly (replicated leaves of an FSDP run) are summed
-    // with peer loads in a fixed rank order, so that every replica computes bit-identical values;
-    // the in-switch reduction is not documented to return the same sum to different requesters.
-    const bool use_mc = c.mc_grad != nullptr && !(sg.flags & B200_SEG_ORDERED);
-    if (vec) {
-      const int rl4 = sg.row_len >> 2;
-      const int64_t total4 = static_cast<int64_t>(sg.rows) * rl4;   // multi-row segments: < 2^31 (checked by the engine)
-      const int64_t nthreads = static_cast<int64_t>(vnblocks) * blockDim.x;
-      constexpr int U = 4;   // independent 16-byte vectors per thread per iteration (memory-level parallelism)
-      for (int64_t i0 = static_cast<int64_t>(vbid) * blockDim.x + threadIdx.x; i0 < total4; i0 += nthreads * U) {
-        // per vector only (row, col) are kept (32-bit); the three 64-bit offsets are rebuilt where used
-        uint32_t vrow[U], vcol[U];
-        bool ok[U];
-        float4 g[U], pp[U], mm[U], vv[U];
-        float* p_base = broadcast ? c.param[c.rank] : a.p_local;
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-          const int64_t i = i0 + u * nthreads;
-          ok[u] = i < total4;
-          const uint32_t ii = ok[u] ? static_cast<uint32_t>(i) : 0u;
-          // rows == 1 (every DP segment, contiguous FSDP shards) needs no division; otherwise the
-          // segment is far below 2^31 vectors and a 32-bit division is enough
-          vrow[u] = sg.rows == 1 ? 0u : ii / static_cast<uint32_t>(rl4);
-          vcol[u] = (ii - vrow[u] * static_cast<uint32_t>(rl4)) << 2;
-        }
-        auto src_of = [&](int u) { return sg.src_off + static_cast<int64_t>(vrow[u]) * sg.src_pitch + vcol[u]; };
-        auto loc_of = [&](int u) { return sg.loc_off + static_cast<int64_t>(vrow[u]) * sg.row_len + vcol[u]; };
-        auto dst_of = [&](int u) {
-          return (broadcast ? sg.dst_off : sg.loc_off) + static_cast<int64_t>(vrow[u]) * sg.row_len + vcol[u];
-        };
-        // ---- loads (all issued before any use) ----
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-          if (!ok[u]) continue;
-          if (c.world == 1) g[u] = *reinterpret_cast<const float4*>(my_grad + src_of(u));
-          else if (use_mc) g[u] = mc_ld_reduce_f32x4(c.mc_grad + src_of(u));
-          else g[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-          mm[u] = *reinterpret_cast<float4*>(m + loc_of(u));
-          vv[u] = *reinterpret_cast<float4*>(v + loc_of(u));
-          pp[u] = *reinterpret_cast<float4*>(p_base + dst_of(u));
-        }
-        if (c.world > 1 && !use_mc) {
-#pragma unroll 1
-          for (int k = 0; k < c.world; ++k) {
-            // DP slices are disjoint per rank: start at myself to spread the traffic. Segments reduced
-            // by every rank use the same order everywhere (see above).
-            int peer = broadcast ? c.rank + k : k;
-            if (peer >= c.world) peer -= c.world;
-            float4 t4[U];
-#pragma unroll
-            for (int u = 0; u < U; ++u)
-              if (ok[u]) t4[u] = ld_sys_f32x4(c.grad[peer] + src_of(u));
-#pragma unroll
-            for (int u = 0; u < U; ++u)
-              if (ok[u]) { g[u].x += t4[u].x; g[u].y += t4[u].y; g[u].z += t4[u].z; g[u].w += t4[u].w; }
-          }
-        }
-        // ---- AdamW + publish ----
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-          if (!ok[u]) continue;
-          adamw1(pp[u].x, mm[u].x, vv[u].x, g[u].x * hp.grad_scale, hp, c1, c2);
-          adamw1(pp[u].y, mm[u].y, vv[u].y, g[u].y * hp.grad_scale, hp, c1, c2);
-          adamw1(pp[u].z, mm[u].z, vv[u].z, g[u].z * hp.grad_scale, hp, c1, c2);
-          adamw1(pp[u].w, mm[u].w, vv[u].w, g[u].w * hp.grad_scale, hp, c1, c2);
-          *reinterpret_cast<float4*>(m + loc_of(u)) = mm[u];
-          *reinterpret_cast<float4*>(v + loc_of(u)) = vv[u];
-          __nv_bfloat162 lo = __floats2bfloat162_rn(pp[u].x, pp[u].y), hi = __floats2bfloat162_rn(pp[u].z, pp[u].w);
-          const uint32_t w0 = *reinterpret_cast<uint32_t*>(&lo), w1 = *reinterpret_cast<uint32_t*>(&hi);
-          // fp32 master
-          if (!fp32_everywhere) {
-            *reinterpret_cast<float4*>(p_base + dst_of(u)) = pp[u];
-          } else if (c.mc_param != nullptr) {
-            mc_st_f32x4(c.mc_param + dst_of(u), pp[u]);
-          } else {
-#pragma unroll 1
-            for (int k = 0; k < c.world; ++k) {
-              int peer = c.rank + k;
-              if (peer >= c.world) peer -= c.world;
-              *reinterpret_cast<float4*>(c.param[peer] + dst_of(u)) = pp[u];
-            }
-          }
-          // bf16 working copy
-          if (!bf16_everywhere) {
-            __nv_bfloat16* b = broadcast ? c.bf16[c.rank] : a.bf16_local;
-            if (b != nullptr) *reinterpret_cast<uint2*>(b + dst_of(u)) = make_uint2(w0, w1);
-          } else if (c.mc_bf16 != nullptr) {
-            mc_st_b32x2(c.mc_bf16 + dst_of(u), w0, w1);
-          } else {
-#pragma unroll 1
-            for (int k = 0; k < c.world; ++k) {
-              int peer = c.rank + k;
-              if (peer >= c.world) peer -= c.world;
-              if (c.bf16[peer] != nullptr) *reinterpret_cast<uint2*>(c.bf16[peer] + dst_of(u)) = make_uint2(w0, w1);
-            }
-          }
-        }
-      }
-    } else {
-      // scalar path for odd shapes (never hit by the padded layouts the engines build)
-      const int64_t total = static_cast<int64_t>(sg.rows) * sg.row_len;
-      for (int64_t i = static_cast<int64_t>(vbid) * blockDim.x + threadIdx.x; i < total;
-           i += static_cast<int64_t>(vnblocks) * blockDim.x) {
-        const int64_t row = i / sg.row_len, col = i - row * sg.row_len;
-        const int64_t src = sg.src_off + row * sg.src_pitch + col;
-        const int64_t loc = sg.loc_off + i;
-        float g = 0.f;
-        for (int k = 0; k < c.world; ++k) g += *reinterpret_cast<const volatile float*>(c.grad[k] + src);
-        const int64_t dst = broadcast ? sg.dst_off + i : loc;
-        float* p_base = broadcast ? c.param[c.rank] : a.p_local;
-        float pp = p_base[dst], mm = m[loc], vv = v[loc];
-        adamw1(pp, mm, vv, g * hp.grad_scale, hp, c1, c2);
-        m[loc] = mm; v[loc] = vv;
-        if (broadcast) {
-          for (int k = 0; k < c.world; ++k) {
-            if (k == c.rank || a.publish_fp32) c.param[k][dst] = pp;
-            if (c.bf16[k] != nullptr) c.bf16[k][dst] = __float2bfloat16_rn(pp);
-          }
-        } else {
-          p_base[dst] = pp;
-          if (a.bf16_local != nullptr) a.bf16_local[dst] = __float2bfloat16_rn(pp);
-        }
-      }
+    const int need = segment_blocks(sg);
+    if (need > small_limit || s + 1 == a.nseg) {
+      update_segment(a, sg, bid, nblocks, c1, c2);
+      ++s;
+      continue;
     }
+    int first = need, e = s + 1, my_seg = bid < need ? s : -1, my_first = 0, my_need = need;
+    while (e < a.nseg) {
+      const int n2 = segment_blocks(a.segs[e]);
+      if (n2 > small_limit || first + n2 > nblocks) break;
+      if (bid >= first && bid < first + n2) { my_seg = e; my_first = first; my_need = n2; }
+      first += n2;
+      ++e;
+    }
+    if (my_seg >= 0) update_segment(a, a.segs[my_seg], bid - my_first, my_need, c1, c2);
+    s = e;
   }
   stamp(a, bid, 2);
 
