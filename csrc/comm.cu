@@ -156,7 +156,7 @@ __device__ __forceinline__ void stamp(const RankArgs& a, int bid, int k) {
 }
 
 // Reduce + AdamW + publish of one segment by the blocks [0, vnblocks) of a (sub-)grid.
-__device__ __noinline__ void update_segment(const RankArgs& a, const b200_seg& sg, const int vbid, const int vnblocks,
+__device__ __forceinline__ void update_segment(const RankArgs& a, const b200_seg& sg, const int vbid, const int vnblocks,
                                                const float c1, const float c2) {
   const CommDev& c = a.c;
   const b200_adamw_hparams& hp = a.hp;
@@ -353,22 +353,26 @@ __device__ __forceinline__ void fused_reduce_adamw_body(const RankArgs& a, const
   // instead of one per segment.
   const int small_limit = nblocks / 4 > 0 ? nblocks / 4 : 1;
   for (int s = 0; s < a.nseg;) {
-    const b200_seg sg = a.segs[s];
-    const int need = segment_blocks(sg);
-    if (need > small_limit || s + 1 == a.nseg) {
-      update_segment(a, sg, bid, nblocks, c1, c2);
-      ++s;
-      continue;
+    // one pass: either segment s alone on the whole grid, or the run [s, e) of small segments side by side
+    int my_seg = s, my_first = 0, my_need = nblocks, e = s + 1;
+    const int need = segment_blocks(a.segs[s]);
+    if (need <= small_limit && s + 1 < a.nseg) {
+      int first = need;
+      my_seg = bid < need ? s : -1;
+      my_need = need;
+      while (e < a.nseg) {
+        const int n2 = segment_blocks(a.segs[e]);
+        if (n2 > small_limit || first + n2 > nblocks) break;
+        if (bid >= first && bid < first + n2) { my_seg = e; my_first = first; my_need = n2; }
+        first += n2;
+        ++e;
+      }
+      if (e == s + 1) { my_seg = s; my_first = 0; my_need = nblocks; }   // a run of one: give it the whole grid
     }
-    int first = need, e = s + 1, my_seg = bid < need ? s : -1, my_first = 0, my_need = need;
-    while (e < a.nseg) {
-      const int n2 = segment_blocks(a.segs[e]);
-      if (n2 > small_limit || first + n2 > nblocks) break;
-      if (bid >= first && bid < first + n2) { my_seg = e; my_first = first; my_need = n2; }
-      first += n2;
-      ++e;
+    if (my_seg >= 0) {
+      const b200_seg sg = a.segs[my_seg];
+      update_segment(a, sg, bid - my_first, my_need, c1, c2);
     }
-    if (my_seg >= 0) update_segment(a, a.segs[my_seg], bid - my_first, my_need, c1, c2);
     s = e;
   }
   stamp(a, bid, 2);
