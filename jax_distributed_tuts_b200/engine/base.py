@@ -208,14 +208,24 @@ class FusedEngine:
                  eps: float = 1e-8, weight_decay: float = 1e-4, num_minibatches: int = 4,
                  data_axis_name: str = "data", shard_axis: Optional[str] = None, min_weight_size: int = 2 ** 18,
                  use_graph: bool = True, comm_blocks: int = 16, overlap: bool = True, fsdp_weights: str = "fused",
-                 publish_fp32: bool = False, stub_collectives: bool = False, deterministic: bool = False):
+                 publish_fp32: bool = False, stub_collectives: bool = False, deterministic: bool = False,
+                 comm_axes=None):
         if not torch.cuda.is_available():
             raise RuntimeError("the fused engine needs a CUDA device; use the generic tier on CPU")
         _lib.lib()  # fail loudly if the kernel library is missing
         assert mode in ("dp", "fsdp")
         self.mesh, self.mode = mesh, mode
         self.device = torch.device("cuda", torch.cuda.current_device())
-        self.world, self.rank = mesh.size, mesh.rank
+        # comm_axes: the mesh axes the engine's gradients are reduced over (default: the whole mesh). A
+        # pipeline stage passes ("data",): its replicas along the data axis form the symmetric group,
+        # the pipe axis is somebody else's business.
+        self.comm_axes = comm_axes
+        if comm_axes is None:
+            self.world, self.rank = mesh.size, mesh.rank
+            self.group = dist.group.WORLD if mesh.size > 1 else None
+        else:
+            self.world, self.rank = mesh.axis_size(comm_axes), mesh.axis_index(comm_axes)
+            self.group = mesh.group(comm_axes) if self.world > 1 else None
         self.hp = dict(lr=lr, beta1=b1, beta2=b2, eps=eps, weight_decay=weight_decay)
         self.num_minibatches = num_minibatches
         self.data_axis_name = data_axis_name
@@ -269,7 +279,7 @@ class FusedEngine:
         else:
             self._plan_shards()
             sizes.update({"bf16": self.local_total * 2})   # every rank's bf16 slices at the same local offsets
-        self.arena = SymmetricArena(sizes, self.mesh, d)
+        self.arena = SymmetricArena(sizes, self.mesh, d, axes=self.comm_axes)
         self.g32 = self.arena.tensor("grad", torch.float32, n)
         if self.mode == "dp":
             self.p32 = self.arena.tensor("param", torch.float32, n)
@@ -353,6 +363,7 @@ class FusedEngine:
             for i, r in enumerate(self.shard_peer_ranks):
                 arr[i] = self.arena.peer_ptrs[r] + self.arena.offsets["bf16"]
             self._bias_peers = arr
+            self._bias_peers_stub = (C.c_void_p * self.S)(*[self.arena.peer_ptrs[self.rank] + self.arena.offsets["bf16"]] * self.S)
             self.bias_full = {k: self._bias_buf[o: o + n_] for k, (o, n_) in spans.items()}
 
     def _setup_bucket_gather(self) -> None:
@@ -385,6 +396,7 @@ class FusedEngine:
         for i, r_ in enumerate(self.shard_peer_ranks):
             arr[i] = self.arena.peer_ptrs[r_] + self.arena.offsets["bf16"]
         self._gather_peers = arr
+        self._gather_peers_stub = (C.c_void_p * self.S)(*[self.arena.peer_ptrs[self.rank] + self.arena.offsets["bf16"]] * self.S)
 
     def prefetch_bucket(self, b: int, keep: Optional[int] = None) -> None:
         """Starts assembling bucket ``b``'s weights on the gather stream (no-op unless in gather
@@ -400,7 +412,8 @@ class FusedEngine:
         self.gather_stream.wait_stream(main)      # every reader of the recycled buffer is already queued on main
         segs, nseg = self._gbuf_segs[b]
         with torch.cuda.stream(self.gather_stream):
-            _lib.check(_lib.lib().b200_peer_gather(C.cast(self._gather_peers, C.POINTER(C.c_void_p)), self.S,
+            _lib.check(_lib.lib().b200_peer_gather(C.cast(self._gather_peers_stub if self.stub_collectives else self._gather_peers,
+                                                           C.POINTER(C.c_void_p)), self.S,
                                                     segs.data_ptr(), nseg, self._gbufs[slot].data_ptr(), 32,
                                                     self.gather_stream.cuda_stream))
             ev = torch.cuda.Event()
@@ -433,7 +446,8 @@ class FusedEngine:
     def _gather_small(self) -> None:
         if self.mode != "fsdp" or not self._bias_nseg:
             return
-        _lib.check(_lib.lib().b200_peer_gather(C.cast(self._bias_peers, C.POINTER(C.c_void_p)), self.S,
+        _lib.check(_lib.lib().b200_peer_gather(C.cast(self._bias_peers_stub if self.stub_collectives else self._bias_peers,
+                                                       C.POINTER(C.c_void_p)), self.S,
                                                 self._bias_segs.data_ptr(), self._bias_nseg,
                                                 self._bias_buf.data_ptr(), 2,
                                                 torch.cuda.current_stream().cuda_stream))
@@ -461,7 +475,7 @@ class FusedEngine:
             K.cast_f32_bf16(self.p_loc, self.pb)
         torch.cuda.synchronize()
         if self.world > 1:
-            dist.barrier()
+            dist.barrier(group=self.group)
 
     def flat_params(self, gather: bool = True) -> Dict[str, object]:
         """path -> fp32 tensor. DP: views of the replicated master. FSDP: full arrays gathered over
@@ -498,7 +512,7 @@ class FusedEngine:
         W, r = self.world, self.rank
         for (b0, b1) in self.layout.bucket_ranges:
             sl = (b1 - b0) // W
-            dist.all_gather_into_tensor(self.p32[b0:b1], self.p32[b0 + r * sl: b0 + (r + 1) * sl].clone())
+            dist.all_gather_into_tensor(self.p32[b0:b1], self.p32[b0 + r * sl: b0 + (r + 1) * sl].clone(), group=self.group)
         torch.cuda.synchronize()
         self._master_stale = False
 
@@ -515,7 +529,7 @@ class FusedEngine:
                 full = buf
             else:
                 g = torch.empty(W, buf.numel(), dtype=buf.dtype, device=buf.device)
-                dist.all_gather_into_tensor(g.view(-1), buf.contiguous().view(-1))
+                dist.all_gather_into_tensor(g.view(-1), buf.contiguous().view(-1), group=self.group)
                 full = self.layout.owner_slices_to_flat(g)
             for path, sp in self.layout.leaves.items():
                 out[path] = self.layout.view(full, path).clone().reshape(sp.shape)
@@ -569,7 +583,7 @@ class FusedEngine:
         self.step_count.fill_(int(count))
         torch.cuda.synchronize()
         if self.world > 1:
-            dist.barrier()
+            dist.barrier(group=self.group)
 
     @staticmethod
     def _nest(flat: Dict[str, object], order: Optional[Sequence[str]] = None) -> Dict:
@@ -625,12 +639,14 @@ class FusedEngine:
     def _build_segments(self) -> None:
         W, r = self.world, self.rank
         self.bucket_segs: List[Tuple[torch.Tensor, int]] = []
+        self._host_segs: List[Seg] = []
         if self.mode == "dp":
             for (b0, b1) in self.layout.bucket_ranges:
                 sl = (b1 - b0) // W
                 assert sl // 4 < 2 ** 31, "bucket slice too large for one fused-update segment: use more buckets"
                 seg = Seg(src_off=b0 + r * sl, src_pitch=sl, dst_off=b0 + r * sl, loc_off=b0 // W, rows=1, row_len=sl)
                 self.bucket_segs.append((self._segs_to_device([seg]), 1))
+                self._host_segs.append(seg)
             return
         per_bucket: Dict[int, List[Seg]] = {}
         for path, sp in self.layout.leaves.items():
@@ -654,6 +670,7 @@ class FusedEngine:
         assert order == list(range(len(order))), "bucket ids must be 0..n-1"
         for b in order:
             self.bucket_segs.append((self._segs_to_device(per_bucket[b]), len(per_bucket[b])))
+            self._host_segs.extend(per_bucket[b])
 
     def _sync_all_buckets(self) -> None:
         """All buckets in one launch (used when there is nothing to overlap with: one rank, or overlap off)."""
@@ -733,6 +750,76 @@ class FusedEngine:
         with torch.cuda.stream(self.side_stream):
             self._sync_bucket(b, last=False)
 
+    # ---------------------------------------------------------------- self-check / measurement aids
+    def set_stub_collectives(self, on: bool) -> None:
+        """Switches the "collectives stubbed" variant of the step on or off (bench.py's exposed-comm
+        measurement): every cross-GPU access is replaced by the same access to local memory and the
+        flag exchanges are skipped, so the kernels do the same arithmetic and local traffic without
+        NVLink and without waiting for peers. The parameters it produces are NOT a training result.
+        The step graph is re-captured on the next call."""
+        on = bool(on) and self.world > 1
+        if on == self.stub_collectives:
+            return
+        self.stub_collectives = on
+        if on and not hasattr(self, "ctx_stub"):
+            self.ctx_stub = self._make_ctx(self.arena, "grad", "param" if self.mode == "dp" else None, "bf16", "signal",
+                                           local_only=True)
+        self.graph = None
+        self._warmed = False
+        self.release_gathered()
+        torch.cuda.synchronize()
+        if self.world > 1:
+            dist.barrier(group=self.group)
+
+    def _peer_base(self, g: int) -> int:
+        """Base address of rank ``g``'s arena as this rank sees it (its own when collectives are stubbed)."""
+        return self.arena.peer_ptrs[self.rank if self.stub_collectives else g]
+
+    def selfcheck(self, run_one_step) -> Dict[str, object]:
+        """One real step of the fused update checked against an independent path: the gradients the
+        step left in ``g32`` are all-reduced with NCCL, a plain fp32 PyTorch AdamW is applied to a
+        snapshot of this rank's master parameters / moments taken before the step, and the result is
+        compared with what the fused kernel wrote; the bf16 working copies (DP) must be bit-identical
+        on every rank. ``run_one_step`` is a callable that performs exactly one training step.
+        Collective: every rank calls it. Returns {"ok", "max_abs_err", "replicas_identical"}."""
+        dp = self.mode == "dp"
+        torch.cuda.synchronize()
+        p_buf = self.p32 if dp else self.p_loc
+        p0, m0, v0 = p_buf.clone(), self.m.clone(), self.v.clone()
+        t = int(self.step_count.item()) + 1
+        run_one_step()
+        torch.cuda.synchronize()
+        g = self.g32.clone()
+        if self.world > 1:
+            dist.all_reduce(g, group=self.group)
+        g.mul_(1.0 / (self.num_minibatches * self.world))
+        hp = self.hp
+        worst = 0.0
+        for sg in self._host_segs:
+            rows, rl = int(sg.rows), int(sg.row_len)
+            src = torch.as_strided(g, (rows, rl), (int(sg.src_pitch), 1), int(sg.src_off)).reshape(-1)
+            loc = slice(int(sg.loc_off), int(sg.loc_off) + rows * rl)
+            pos = slice(int(sg.dst_off), int(sg.dst_off) + rows * rl) if dp else loc
+            m = hp["beta1"] * m0[loc] + (1 - hp["beta1"]) * src
+            v = hp["beta2"] * v0[loc] + (1 - hp["beta2"]) * src * src
+            mhat, vhat = m / (1 - hp["beta1"] ** t), v / (1 - hp["beta2"] ** t)
+            ref = p0[pos] - hp["lr"] * (mhat / (vhat.sqrt() + hp["eps"]) + hp["weight_decay"] * p0[pos])
+            worst = max(worst, (p_buf[pos] - ref).abs().max().item(), (self.m[loc] - m).abs().max().item())
+        same = True
+        if dp and self.world > 1:
+            ref_b = self.pb.clone()
+            src0 = dist.get_global_rank(self.group, 0) if self.group is not dist.group.WORLD else 0
+            dist.broadcast(ref_b, src0, group=self.group)
+            flag = torch.tensor([int(torch.equal(ref_b, self.pb))], device=self.device)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.group)
+            same = bool(flag.item())
+        w = torch.tensor([worst], device=self.device, dtype=torch.float64)
+        if self.world > 1:
+            dist.all_reduce(w, op=dist.ReduceOp.MAX, group=self.group)
+        worst = float(w.item())
+        return {"ok": bool(worst < 1e-5 and same), "max_abs_err": worst, "replicas_identical": same,
+                "against": "NCCL all_reduce of the step's gradients + fp32 PyTorch AdamW"}
+
     # ---------------------------------------------------------------- weights for GEMMs -------
     def grad2d(self, path: str) -> torch.Tensor:
         return self.layout.view2d(self.g32, path)
@@ -757,7 +844,7 @@ class FusedEngine:
         if self.fsdp_weights == "gather":
             return self._gathered(path), {}, None
         r, c, ld = self._local_shape2d(path)
-        srcs = [self.arena.peer_ptrs[g] + self.arena.offsets["bf16"] + self.loc_off[path] * 2
+        srcs = [self._peer_base(g) + self.arena.offsets["bf16"] + self.loc_off[path] * 2
                 for g in self.shard_peer_ranks]
         last_dim = c != sp.cols
         return srcs, dict(b_shape=(sp.rows, sp.cols), ldb=ld), (last_dim, c if last_dim else r)
@@ -826,7 +913,7 @@ class FusedEngine:
                 return
             torch.cuda.synchronize()
             if self.world > 1:
-                dist.barrier()
+                dist.barrier(group=self.group)
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g, stream=torch.cuda.Stream()):
                 self._launch_body()

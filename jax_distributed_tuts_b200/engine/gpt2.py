@@ -151,7 +151,7 @@ class GPT2Engine(FusedEngine):
         r, c, ld = self._local_shape2d(path)
         if self.shard_dim[path] is None:
             return [self._local_view(self.pb, path).data_ptr()], 1 << 30
-        return ([self.arena.peer_ptrs[g] + self.arena.offsets["bf16"] + self.loc_off[path] * 2
+        return ([self._peer_base(g) + self.arena.offsets["bf16"] + self.loc_off[path] * 2
                  for g in self.shard_peer_ranks], r)
 
     def _step_body(self) -> None:
