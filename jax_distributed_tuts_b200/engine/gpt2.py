@@ -16,7 +16,7 @@ FSDP: reduce-scatter + sharded update, param_sharding.py:134-138,353).
 """
 from __future__ import annotations
 
-from typing import Dict, List, Optional
+from typing import Dict, List, Optional, Sequence
 
 import torch
 
@@ -42,7 +42,14 @@ def _layer_leaves(i: int, c: int, bucket: int):
 
 class GPT2Engine(FusedEngine):
     def __init__(self, config, mesh: Mesh, *, mode: str = "dp", batch_per_rank: int, seq_len: Optional[int] = None,
-                 lr: float = 3e-4, num_minibatches: int = 1, init_params: Optional[Dict] = None, **kw):
+                 lr: float = 3e-4, num_minibatches: int = 1, init_params: Optional[Dict] = None,
+                 layer_ids: Optional[Sequence[int]] = None, has_embed: bool = True, has_head: bool = True,
+                 slots: int = 1, **kw):
+        """``layer_ids`` / ``has_embed`` / ``has_head`` / ``slots`` make the engine one *pipeline stage*
+        (``engine.pp.PipelineEngine``): it owns only those transformer blocks (plus the embeddings on the
+        first stage, the final norm and a tied copy of ``wte`` on the last), keeps ``slots`` sets of
+        activations (one per microbatch in flight) and its forward / backward take and return the
+        activations at the stage boundary instead of tokens and logits."""
         kw.setdefault("comm_blocks", 128)   # hundreds of MB per bucket: keep many bytes in flight
         tokens = (batch_per_rank // num_minibatches) * (seq_len or config.n_ctx)
         if kw.get("fsdp_weights", "auto") == "auto":   # many row tiles per GEMM: gather once per layer
@@ -57,7 +64,10 @@ class GPT2Engine(FusedEngine):
                 "not bit for bit")
         self.cfg = config
         self.pdl = tokens < 4096       # long persistent kernels: dependent launch only ties up SMs (see FusedEngine.pdl)
-        self.L, self.Hh, self.C = config.n_layer, config.n_head, config.d_model
+        self.layer_ids = list(range(config.n_layer)) if layer_ids is None else list(layer_ids)
+        self.has_embed, self.has_head, self.slots = has_embed, has_head, slots
+        self.is_stage = not (has_embed and has_head and len(self.layer_ids) == config.n_layer)
+        self.L, self.Hh, self.C = len(self.layer_ids), config.n_head, config.d_model
         self.T = seq_len or config.n_ctx
         assert self.T % 128 == 0 and self.T <= config.n_ctx
         self.V = config.vocab_size
@@ -73,32 +83,45 @@ class GPT2Engine(FusedEngine):
         # launch per step and filled by atomics from the kernels that already hold the data (dgrad
         # epilogues, LayerNorm backward) instead of separate column-sum passes.
         mats, vecs = [], []
-        for j, i in enumerate(range(L - 1, -1, -1)):
+        for j, i in enumerate(reversed(self.layer_ids)):
             for path, shape, _ in _layer_leaves(i, c, j):
                 (mats if len(shape) == 2 else vecs).append((path, shape, j if len(shape) == 2 else L))
-        leaves = mats + [("wte", (self.Vp, c), L), ("wpe", (config.n_ctx, c), L)] + vecs + \
-            [("ln_f/scale", (c,), L), ("ln_f/bias", (c,), L)]
+        tables = ([("wte", (self.Vp, c), L)] if (has_embed or has_head) else []) + \
+            ([("wpe", (config.n_ctx, c), L)] if has_embed else [])
+        if has_head:
+            vecs = vecs + [("ln_f/scale", (c,), L), ("ln_f/bias", (c,), L)]
+        leaves = mats + tables + vecs
         self._setup_buffers(FlatLayout(leaves, self.world))
-        first_vec, last_vec = self.layout.leaves[vecs[0][0]], self.layout.leaves["ln_f/bias"]
-        self._vec_grads = self.g32[first_vec.offset: last_vec.offset + last_vec.ld]
+        if vecs:
+            first_vec, last_vec = self.layout.leaves[vecs[0][0]], self.layout.leaves[vecs[-1][0]]
+            self._vec_grads = self.g32[first_vec.offset: last_vec.offset + last_vec.ld]
+        else:
+            self._vec_grads = None
         d, M = self.device, self.M
         bf, f32 = torch.bfloat16, torch.float32
         self.tokens = torch.zeros(self.B, self.T, dtype=torch.int64, device=d)
         self.targets = torch.zeros(self.B, self.T, dtype=torch.int64, device=d)
         z = lambda *s, dt=bf: torch.zeros(*s, dtype=dt, device=d)
-        self.x0 = z(M, c)
-        self.acts: List[Dict[str, torch.Tensor]] = []
-        for _ in range(L):
-            self.acts.append(dict(a=z(M, c), qkv=z(M, 3 * c), att=z(M, c), x1=z(M, c), m2=z(M, c), hpre=z(M, 4 * c),
-                                  hact=z(M, 4 * c), x2=z(M, c), mean1=z(M, dt=f32), rstd1=z(M, dt=f32),
-                                  mean2=z(M, dt=f32), rstd2=z(M, dt=f32), lse=z(self.mbB * self.Hh * self.T, dt=f32)))
-        self.xf, self.meanf, self.rstdf = z(M, c), z(M, dt=f32), z(M, dt=f32)
-        self.logits = z(M, self.Vp)
+        def new_acts():
+            return [dict(a=z(M, c), qkv=z(M, 3 * c), att=z(M, c), x1=z(M, c), m2=z(M, c), hpre=z(M, 4 * c),
+                         hact=z(M, 4 * c), x2=z(M, c), mean1=z(M, dt=f32), rstd1=z(M, dt=f32),
+                         mean2=z(M, dt=f32), rstd2=z(M, dt=f32), lse=z(self.mbB * self.Hh * self.T, dt=f32))
+                    for _ in range(L)]
+        self.slot_acts: List[List[Dict[str, torch.Tensor]]] = [new_acts() for _ in range(slots)]
+        self.slot_x0 = [z(M, c) for _ in range(slots)]        # stage input: embeddings, or the activations received
+        self.acts, self.x0 = self.slot_acts[0], self.slot_x0[0]
+        if has_head:
+            self.xf, self.meanf, self.rstdf = z(M, c), z(M, dt=f32), z(M, dt=f32)
+            self.logits = z(M, self.Vp)
+        if self.is_stage:
+            self.slot_dx_top = [z(M, c) for _ in range(slots)]   # gradient entering the stage from above
+            self.slot_dx_out = [z(M, c) for _ in range(slots)]   # gradient leaving the stage downwards
         # backward temporaries
+        self.slot_dx_top0 = self.slot_dx_top[0] if self.is_stage else z(M, c)
         self.dxa, self.dxb = z(M, c), z(M, c)
         self.dh, self.dm = z(M, 4 * c), z(M, c)
         self.dqkv = z(M, 3 * c)
-        self.att_scratch = z(K.attention_bwd_scratch_numel(self.mbB, self.T, self.Hh), dt=f32)
+        self.att_scratch = z(K.attention_bwd_scratch_numel(self.mbB, self.T, self.Hh), dt=f32) if L else None
         self.rng_base = None
         if init_params is not None:
             self.load_params(init_params)
@@ -127,8 +150,8 @@ class GPT2Engine(FusedEngine):
 
     def params_tree(self, gather: bool = True) -> Dict:
         flat = self.flat_params(gather=gather)
-        order = ["wte", "wpe"] + [p for i in range(self.L) for p, _, _ in _layer_leaves(i, self.C, 0)] + ["ln_f/scale", "ln_f/bias"]
-        return self._nest(flat, order)
+        order = ["wte", "wpe"] + [p for i in self.layer_ids for p, _, _ in _layer_leaves(i, self.C, 0)] + ["ln_f/scale", "ln_f/bias"]
+        return self._nest(flat, [p for p in order if p in flat])
 
     # ------------------------------------------------------------------ step ------------------
     def _load_batch(self, batch: Batch) -> None:
@@ -138,11 +161,12 @@ class GPT2Engine(FusedEngine):
     def _rows_per_step(self) -> int:
         return self.B * self.T * self.world
 
-    def _embed(self, tok: torch.Tensor) -> None:
+    def _embed(self, tok: torch.Tensor, out: Optional[torch.Tensor] = None) -> None:
+        out = self.x0 if out is None else out
         if self.mode == "fsdp" and self.S > 1 and (self.shard_dim["wte"] is not None or self.shard_dim["wpe"] is not None):
-            K.embedding_fwd_sharded(tok, self._table_peers("wte"), self._table_peers("wpe"), self.x0, self.C)
+            K.embedding_fwd_sharded(tok, self._table_peers("wte"), self._table_peers("wpe"), out, self.C)
         else:
-            K.embedding_fwd(tok, self._table("wte"), self._table("wpe"), self.x0)
+            K.embedding_fwd(tok, self._table("wte"), self._table("wpe"), out)
 
     def _table(self, path: str) -> torch.Tensor:
         return self.layout.view2d(self.pb, path) if self.mode == "dp" else self._local_view(self.pb, path)
@@ -171,15 +195,21 @@ class GPT2Engine(FusedEngine):
             self._sync_all_buckets()
         self._end_step(next_rng)
 
-    def _forward(self, tok: torch.Tensor) -> None:
-        c = self.C
-        self._embed(tok)
-        x = self.x0
-        bucket_of = lambda layer: self.L - 1 - layer
-        self.prefetch_bucket(bucket_of(0))
-        for i in range(self.L):
-            p, A = f"h_{i}/", self.acts[i]
-            self.prefetch_bucket(bucket_of(i + 1) if i + 1 < self.L else self.L, keep=bucket_of(i))   # next layer / the tied head
+    def _forward(self, tok: Optional[torch.Tensor], slot: int = 0) -> torch.Tensor:
+        """Forward of one microbatch through this engine's blocks. The input is ``tok`` (engines that own
+        the embeddings) or whatever the caller put into ``slot_x0[slot]`` (a pipeline stage's received
+        activations). Returns the output activations (the logits stay in ``self.logits`` when the
+        engine owns the head)."""
+        acts, x = self.slot_acts[slot], self.slot_x0[slot]
+        if self.has_embed:
+            self._embed(tok, x)
+        L = self.L
+        bucket_of = lambda li: L - 1 - li
+        if L:
+            self.prefetch_bucket(bucket_of(0))
+        for li, i in enumerate(self.layer_ids):
+            p, A = f"h_{i}/", acts[li]
+            self.prefetch_bucket(bucket_of(li + 1) if li + 1 < L else L, keep=bucket_of(li))   # next layer / the tied head
             K.layernorm_fwd(x, self.vec(p + "ln_1/scale"), self.vec(p + "ln_1/bias"), A["a"], A["mean1"], A["rstd1"])
             self.gemm_w(A["a"], p + "attn/c_attn/kernel", A["qkv"], bias=self.vec(p + "attn/c_attn/bias"))
             K.attention_fwd(A["qkv"], A["att"], A["lse"], self.mbB, self.T, self.Hh)
@@ -190,28 +220,40 @@ class GPT2Engine(FusedEngine):
             self.gemm_w(A["hact"], p + "mlp/c_proj/kernel", A["x2"], bias=self.vec(p + "mlp/c_proj/bias"), resid=A["x1"])
             A["x_in"] = x
             x = A["x2"]
-        K.layernorm_fwd(x, self.vec("ln_f/scale"), self.vec("ln_f/bias"), self.xf, self.meanf, self.rstdf)
-        self.gemm_wT(self.xf, "wte", self.logits)          # tied head: logits = xf @ wte^T
+        if self.has_head:
+            K.layernorm_fwd(x, self.vec("ln_f/scale"), self.vec("ln_f/bias"), self.xf, self.meanf, self.rstdf)
+            self.gemm_wT(self.xf, "wte", self.logits)          # tied head: logits = xf @ wte^T
         self._x_last = x
+        return x
 
-    def _backward(self, tok: torch.Tensor, tgt: torch.Tensor, *, accumulate: bool, last: bool) -> None:
-        c, M = self.C, self.M
+    def _head_backward(self, tgt: torch.Tensor, dx_out: torch.Tensor, *, accumulate: bool) -> None:
+        """Loss + backward of the final norm and the tied head for the microbatch whose logits are in
+        ``self.logits``: writes the gradient of the residual stream into ``dx_out``."""
         g2, g1 = self.grad2d, self.grad1d
-        acc = accumulate
         logits = self.logits[:, : self.V]
-        K.softmax_xent_bf16_(logits, tgt.reshape(-1), grad_scale=1.0 / M, metrics=self.step_metrics)
+        K.softmax_xent_bf16_(logits, tgt.reshape(-1), grad_scale=1.0 / self.M, metrics=self.step_metrics)
         dlog = self.logits                                   # now the gradient (pad columns stay zero)
-        self.prefetch_bucket(0, keep=self.L)                 # top layer's weights while the head runs
-        K.gemm(dlog, self.xf, g2("wte"), a_mn=True, b_mn=True, accumulate=acc)      # dwte = dlogits^T xf
-        self.gemm_w(dlog, "wte", self.dm)                                            # dxf = dlogits wte
-        dx, spare = self.dxa, self.dxb
-        top = f"h_{self.L - 1}/"
+        if self.L:
+            self.prefetch_bucket(0, keep=self.L)             # top layer's weights while the head runs
+        K.gemm(dlog, self.xf, g2("wte"), a_mn=True, b_mn=True, accumulate=accumulate)      # dwte = dlogits^T xf
+        self.gemm_w(dlog, "wte", self.dm)                                                   # dxf = dlogits wte
         # d(residual stream) out of the final norm; its column sums are the top layer's mlp/c_proj bias gradient
-        K.layernorm_bwd(self.dm, self._x_last, self.vec("ln_f/scale"), self.meanf, self.rstdf, dx, g1("ln_f/scale"),
-                        g1("ln_f/bias"), dxsum=g1(top + "mlp/c_proj/bias"))
-        for j, i in enumerate(range(self.L - 1, -1, -1)):
-            p, A = f"h_{i}/", self.acts[i]
-            if i > 0:
+        top_bias = g1(f"h_{self.layer_ids[-1]}/mlp/c_proj/bias") if self.L else None
+        K.layernorm_bwd(self.dm, self._x_last, self.vec("ln_f/scale"), self.meanf, self.rstdf, dx_out, g1("ln_f/scale"),
+                        g1("ln_f/bias"), dxsum=top_bias)
+
+    def _layers_backward(self, dx: torch.Tensor, *, accumulate: bool, last: bool, slot: int = 0,
+                         final_out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """Backward through this engine's blocks, top to bottom, for the microbatch saved in ``slot``.
+        ``dx`` is the gradient of the output activations (read only). Returns the gradient of the input
+        activations (in ``final_out`` if given)."""
+        g2, g1 = self.grad2d, self.grad1d
+        acc, L = accumulate, self.L
+        acts = self.slot_acts[slot]
+        for j, li in enumerate(range(L - 1, -1, -1)):
+            i = self.layer_ids[li]
+            p, A = f"h_{i}/", acts[li]
+            if li > 0:
                 self.prefetch_bucket(j + 1, keep=j)          # the layer below, needed next
             # x2 = x1 + gelu(m2 Wfc + bfc) Wproj + bproj          (bias gradient of Wproj: already summed from dx)
             K.gemm(A["hact"], dx, g2(p + "mlp/c_proj/kernel"), a_mn=True, b_mn=True, accumulate=acc)
@@ -219,9 +261,9 @@ class GPT2Engine(FusedEngine):
                          dbias=g1(p + "mlp/c_fc/bias"))      # dh = d(pre-GELU); its column sums = c_fc bias gradient
             K.gemm(A["m2"], self.dh, g2(p + "mlp/c_fc/kernel"), a_mn=True, b_mn=True, accumulate=acc)
             self.gemm_wT(self.dh, p + "mlp/c_fc/kernel", self.dm)
-            K.layernorm_bwd(self.dm, A["x1"], self.vec(p + "ln_2/scale"), A["mean2"], A["rstd2"], spare,
+            K.layernorm_bwd(self.dm, A["x1"], self.vec(p + "ln_2/scale"), A["mean2"], A["rstd2"], self.dxa,
                             g1(p + "ln_2/scale"), g1(p + "ln_2/bias"), dresid=dx, dxsum=g1(p + "attn/c_proj/bias"))
-            dx, spare = spare, dx                           # dx = d(x1)
+            dx = self.dxa                                    # dx = d(x1)
             # x1 = x + att Wo + bo
             K.gemm(A["att"], dx, g2(p + "attn/c_proj/kernel"), a_mn=True, b_mn=True, accumulate=acc)
             self.gemm_wT(dx, p + "attn/c_proj/kernel", self.dm)                      # d(att)
@@ -229,15 +271,26 @@ class GPT2Engine(FusedEngine):
             K.gemm(A["a"], self.dqkv, g2(p + "attn/c_attn/kernel"), a_mn=True, b_mn=True, accumulate=acc)
             K.colsum(self.dqkv, g1(p + "attn/c_attn/bias"), accumulate=True)
             self.gemm_wT(self.dqkv, p + "attn/c_attn/kernel", self.dm)               # d(a)
-            below = g1(f"h_{i - 1}/mlp/c_proj/bias") if i > 0 else None
-            K.layernorm_bwd(self.dm, A["x_in"], self.vec(p + "ln_1/scale"), A["mean1"], A["rstd1"], spare,
+            below = g1(f"h_{self.layer_ids[li - 1]}/mlp/c_proj/bias") if li > 0 else None
+            out = final_out if (li == 0 and final_out is not None) else self.dxb
+            K.layernorm_bwd(self.dm, A["x_in"], self.vec(p + "ln_1/scale"), A["mean1"], A["rstd1"], out,
                             g1(p + "ln_1/scale"), g1(p + "ln_1/bias"), dresid=dx, dxsum=below)
-            dx, spare = spare, dx                           # dx = d(x_in)
+            dx = out                                         # dx = d(x_in)
             if last and self.overlap:
                 self._sync_bucket_async(j)                   # this layer's matrices: reduce + update under the rest
-        if not acc:
+        return dx
+
+    def _embed_backward(self, tok: torch.Tensor, dx: torch.Tensor, *, accumulate: bool, zero_wte: bool = False) -> None:
+        if not accumulate:
             K.scale_(self.grad2d_full("wpe"), 0.0)
+            if zero_wte:          # a first pipeline stage: no head GEMM has written the table's gradient
+                K.scale_(self.grad2d_full("wte"), 0.0)
         K.embedding_bwd(tok, dx, self.grad2d_full("wte"), self.grad2d_full("wpe"))
+
+    def _backward(self, tok: torch.Tensor, tgt: torch.Tensor, *, accumulate: bool, last: bool) -> None:
+        self._head_backward(tgt, self.slot_dx_top0, accumulate=accumulate)
+        dx = self._layers_backward(self.slot_dx_top0, accumulate=accumulate, last=last)
+        self._embed_backward(tok, dx, accumulate=accumulate)
 
     def grad2d_full(self, path: str) -> torch.Tensor:
         """Contiguous [rows, ld] gradient region of a 2-D leaf whose last dim needs no padding."""
