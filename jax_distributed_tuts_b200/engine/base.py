@@ -138,9 +138,10 @@ class SymmetricArena:
             group = dist.group.WORLD if mesh.size > 1 else None
         else:
             self.world, self.rank = mesh.axis_size(axes), mesh.axis_index(axes)
-            group = mesh.group(axes)
-            ranks = mesh.group_ranks(axes)
-            assert self.world == 1 or ranks.index(mesh.rank) == self.rank, (ranks, mesh.rank, self.rank)
+            group = mesh.group(axes) if self.world > 1 else None
+            if self.world > 1:
+                ranks = mesh.group_ranks(axes)
+                assert ranks.index(mesh.rank) == self.rank, (ranks, mesh.rank, self.rank)
         self.offsets: Dict[str, int] = {}
         off = 0
         for name, nbytes in sizes_bytes.items():
