@@ -78,7 +78,7 @@ class PipelineEngine:
     def __init__(self, config, mesh: Mesh, *, batch_per_replica: int, seq_len: Optional[int] = None,
                  num_microbatches: int = 4, lr: float = 3e-4, init_params: Optional[Dict] = None,
                  pipe_axis: str = "pipe", data_axis: Optional[str] = "data", use_graph: bool = True,
-                 layer_split: Optional[Sequence[range]] = None):
+                 layer_split: Optional[Sequence[range]] = None, schedule: str = "1f1b"):
         assert torch.cuda.is_available(), "the pipeline engine needs CUDA devices; use parallel/pp.py on CPU"
         self.mesh, self.cfg = mesh, config
         self.pipe_axis = pipe_axis
@@ -91,6 +91,12 @@ class PipelineEngine:
         assert self.B % self.Mb == 0
         self.mbB = self.B // self.Mb
         self.use_graph = use_graph
+        # "gpipe": all forwards, then all backwards in reverse order. "1f1b": the same microbatches and the
+        # same gradients, but a stage starts the backward of microbatch k as soon as its gradient arrives
+        # (one forward, one backward in turn after a warm-up of S-1-s forwards): the stages below the head
+        # work on backwards while the head stage is still busy with later microbatches.
+        assert schedule in ("gpipe", "1f1b")
+        self.schedule = schedule
         head_cost = padded_vocab(config.vocab_size) / (12.0 * config.d_model)
         self.split = list(layer_split) if layer_split is not None else balanced_split(config.n_layer, self.S, head_cost)
         assert len(self.split) == self.S
@@ -105,6 +111,8 @@ class PipelineEngine:
         self.compute = torch.cuda.current_stream()
         self.comm_stream = torch.cuda.Stream()
         self._setup_groups()
+        self._bwd_order = list(range(self.Mb - 1, -1, -1)) if schedule == "gpipe" else list(range(self.Mb))
+        self._first_bwd = self._bwd_order[0]
         self.graphs: Dict[Tuple[str, int], torch.cuda.CUDAGraph] = {}
         self._calls = 0
         self._send_works: List = []
@@ -124,7 +132,7 @@ class PipelineEngine:
         ai_p = m.axis_names.index(self.pipe_axis)
         others = [i for i in range(len(m.axis_names)) if i != ai_p]
         self.prev_rank = self.next_rank = None
-        self.pair_prev = self.pair_next = self.pair_ends = None
+        self.up_prev = self.up_next = self.down_prev = self.down_next = self.pair_ends = None
         self.ends_peer = None
         import itertools
         for fixed in itertools.product(*(range(m.shape[i]) for i in others)):
@@ -137,11 +145,14 @@ class PipelineEngine:
             mine = all(m.coords[i] == v for i, v in zip(others, fixed))
             for st in range(self.S - 1):
                 a, b = rank_of(st), rank_of(st + 1)
-                g = dist.new_group([a, b]) if m.size > 1 else None
+                # one communicator per direction: activations go up on one, gradients come down on the
+                # other, so neither ever queues behind the other
+                up = dist.new_group([a, b]) if m.size > 1 else None
+                down = dist.new_group([a, b]) if m.size > 1 else None
                 if mine and st == self.s:
-                    self.pair_next, self.next_rank = g, b
+                    self.up_next, self.down_next, self.next_rank = up, down, b
                 if mine and st + 1 == self.s:
-                    self.pair_prev, self.prev_rank = g, a
+                    self.up_prev, self.down_prev, self.prev_rank = up, down, a
             if self.S > 2:
                 a, b = rank_of(0), rank_of(self.S - 1)
                 g = dist.new_group([a, b])
@@ -149,9 +160,11 @@ class PipelineEngine:
                     self.pair_ends, self.ends_peer = g, b
                 if mine and self.last:
                     self.pair_ends, self.ends_peer = g, a
-            elif self.S == 2 and mine:
-                self.pair_ends = self.pair_next if self.first else self.pair_prev
-                self.ends_peer = self.next_rank if self.first else self.prev_rank
+            elif self.S == 2:
+                a, b = rank_of(0), rank_of(1)
+                g = dist.new_group([a, b])
+                if mine:
+                    self.pair_ends, self.ends_peer = g, (b if self.first else a)
         self.all_group = dist.group.WORLD if m.size > 1 else None
 
     # ------------------------------------------------------------------ per-microbatch bodies -----
@@ -170,7 +183,7 @@ class PipelineEngine:
 
     def _bwd_body(self, k: int) -> None:
         st = self.stage
-        acc = k != self.Mb - 1                     # the backward phase starts with the last microbatch
+        acc = k != self._first_bwd                 # the first backward of the step overwrites, the others accumulate
         dx_in = st.slot_dx_top[k]                  # from the head (last stage) or received from the stage above
         if not self.last and st.L:
             # the column sums of the incoming gradient are the bias gradient of this stage's top projection
@@ -253,25 +266,42 @@ class PipelineEngine:
         self._fwd_out: Dict[int, torch.Tensor] = getattr(self, "_fwd_out", {})
         self._bwd_out: Dict[int, torch.Tensor] = getattr(self, "_bwd_out", {})
         self._run("begin", 0, lambda: st._begin_step(None, None))
-        # ---- forward phase: microbatches 0 .. M-1 ----
-        recvs = None if self.first else self._post_recvs([st.slot_x0[k] for k in range(Mb)], self.prev_rank, self.pair_prev)
-        for k in range(Mb):
-            if recvs is not None:
-                recvs[k].wait()                           # the compute stream waits; the host does not
-            self._run("fwd", k, lambda k=k: self._fwd_body(k))
+        has_bwd = bool(st.L or self.first)
+        # receives of the whole step, posted up front in the order the neighbours send
+        act_recv = None if self.first else self._post_recvs([st.slot_x0[k] for k in range(Mb)], self.prev_rank, self.up_prev)
+        border = self._bwd_order
+        grad_recv = None if self.last else dict(zip(border, self._post_recvs([st.slot_dx_top[k] for k in border],
+                                                                             self.next_rank, self.down_next)))
+
+        def fwd(k):
+            if act_recv is not None:
+                act_recv[k].wait()                        # the compute stream waits; the host does not
+            self._run("fwd", k, lambda: self._fwd_body(k))
             if not self.last:
-                self._isend(self._fwd_out[k], self.next_rank, self.pair_next)
-        # ---- backward phase: microbatches M-1 .. 0 ----
-        order = list(range(Mb - 1, -1, -1))
-        recvs = None if self.last else dict(zip(order, self._post_recvs([st.slot_dx_top[k] for k in order], self.next_rank,
-                                                                        self.pair_next)))
-        for k in order:
-            if recvs is not None:
-                recvs[k].wait()
-            if st.L or self.first:
-                self._run("bwd", k, lambda k=k: self._bwd_body(k))
+                self._isend(self._fwd_out[k], self.next_rank, self.up_next)
+
+        def bwd(k):
+            if grad_recv is not None:
+                grad_recv[k].wait()
+            if has_bwd:
+                self._run("bwd", k, lambda: self._bwd_body(k))
             if not self.first:
-                self._isend(self._bwd_out.get(k, st.slot_dx_top[k]), self.prev_rank, self.pair_prev)
+                self._isend(self._bwd_out.get(k, st.slot_dx_top[k]), self.prev_rank, self.down_prev)
+
+        if self.schedule == "gpipe":
+            for k in range(Mb):
+                fwd(k)
+            for k in border:
+                bwd(k)
+        else:
+            warm = min(self.S - 1 - self.s, Mb)
+            for k in range(warm):
+                fwd(k)
+            for i in range(Mb - warm):
+                fwd(warm + i)
+                bwd(i)
+            for k in range(Mb - warm, Mb):
+                bwd(k)
         # ---- tied embedding: first and last stage exchange their wte gradients and both keep the sum ----
         if self.S > 1 and (self.first or self.last):
             self.comm_stream.wait_stream(self.compute)
@@ -323,7 +353,7 @@ class PipelineEngine:
         if self.mesh.size > 1:
             dist.all_reduce(hi, op=dist.ReduceOp.MAX, group=self.all_group)
             dist.all_reduce(lo, op=dist.ReduceOp.MIN, group=self.all_group)
-        return {"stages": self.S, "microbatches": self.Mb, "layers_per_stage": [len(r) for r in self.split],
+        return {"stages": self.S, "microbatches": self.Mb, "schedule": self.schedule, "layers_per_stage": [len(r) for r in self.split],
                 "ideal_bubble_frac": (self.S - 1) / (self.Mb + self.S - 1),
                 "stage_busy_ms_max": float(hi.item()), "stage_busy_ms_min": float(lo.item()),
                 "note": "busy = this stage's graphs replayed without communication (the measurement perturbs the training "

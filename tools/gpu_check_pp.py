@@ -31,7 +31,7 @@ def log(*a):
         print(*a, flush=True)
 
 
-def run_case(rank, world, device, S, use_graph) -> bool:
+def run_case(rank, world, device, S, use_graph, schedule="1f1b") -> bool:
     D = world // S
     cfg = gpt2_config("tiny", n_layer=4, d_model=256, n_head=4, vocab_size=1024, n_ctx=256)
     model = GPT2(cfg)
@@ -58,7 +58,7 @@ def run_case(rank, world, device, S, use_graph) -> bool:
     lb = Batch(tok[d * B:(d + 1) * B, :T].contiguous().pin_memory(), tok[d * B:(d + 1) * B, 1:].contiguous().pin_memory())
     with mesh:
         eng = PipelineEngine(cfg, mesh, batch_per_replica=B, seq_len=T, num_microbatches=Mb, lr=lr, init_params=params,
-                             use_graph=use_graph)
+                             use_graph=use_graph, schedule=schedule)
         losses = []
         for _ in range(steps):
             ls, n = eng.train_step(lb)
@@ -77,7 +77,7 @@ def run_case(rank, world, device, S, use_graph) -> bool:
             ok = False
     t = torch.tensor([int(ok)], device=device)
     dist.all_reduce(t, op=dist.ReduceOp.MIN)
-    log(f"[{'ok' if t.item() else 'FAIL'}] pipeline S={S} D={D} graphs={use_graph}: losses {[f'{x:.4f}' for x in losses]} "
+    log(f"[{'ok' if t.item() else 'FAIL'}] pipeline S={S} D={D} graphs={use_graph} {schedule}: losses {[f'{x:.4f}' for x in losses]} "
         f"(single GPU {[f'{x:.4f}' for x in ref_losses]}) split {[len(r) for r in eng.split]} "
         f"worst leaf on stage 0: {worst[0]} mean|d|={worst[1]:.2e}")
     del eng
@@ -91,10 +91,12 @@ def main():
     a = ap.parse_args()
     rank, world, device = init_from_env()
     ok = True
-    cases = [(a.stages, True)] if a.stages else [(world, False), (world, True)] + ([(world // 2, True)] if world >= 4 else [])
-    for S, graph in cases:
+    cases = [(a.stages, True, "1f1b")] if a.stages else \
+        [(world, False, "gpipe"), (world, True, "gpipe"), (world, False, "1f1b"), (world, True, "1f1b")] + \
+        ([(world // 2, True, "1f1b")] if world >= 4 else [])
+    for S, graph, sched in cases:
         try:
-            ok &= run_case(rank, world, device, S, graph)
+            ok &= run_case(rank, world, device, S, graph, sched)
         except Exception as e:  # noqa: BLE001
             traceback.print_exc()
             log(f"[FAIL] pipeline S={S}: {type(e).__name__}: {e}")
