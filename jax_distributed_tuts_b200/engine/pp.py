@@ -134,6 +134,7 @@ class PipelineEngine:
         self.prev_rank = self.next_rank = None
         self.up_prev = self.up_next = self.down_prev = self.down_next = self.pair_ends = None
         self.ends_peer = None
+        self._conn_plan = []          # (group, sender, receiver) in creation order, identical on every rank
         import itertools
         for fixed in itertools.product(*(range(m.shape[i]) for i in others)):
             def rank_of(stage):
@@ -149,6 +150,8 @@ class PipelineEngine:
                 # other, so neither ever queues behind the other
                 up = dist.new_group([a, b]) if m.size > 1 else None
                 down = dist.new_group([a, b]) if m.size > 1 else None
+                if m.size > 1:
+                    self._conn_plan += [(up, a, b), (down, b, a)]
                 if mine and st == self.s:
                     self.up_next, self.down_next, self.next_rank = up, down, b
                 if mine and st + 1 == self.s:
@@ -156,6 +159,7 @@ class PipelineEngine:
             if self.S > 2:
                 a, b = rank_of(0), rank_of(self.S - 1)
                 g = dist.new_group([a, b])
+                self._conn_plan += [(g, a, b), (g, b, a)]
                 if mine and self.first:
                     self.pair_ends, self.ends_peer = g, b
                 if mine and self.last:
@@ -163,9 +167,28 @@ class PipelineEngine:
             elif self.S == 2:
                 a, b = rank_of(0), rank_of(1)
                 g = dist.new_group([a, b])
+                self._conn_plan += [(g, a, b), (g, b, a)]
                 if mine:
                     self.pair_ends, self.ends_peer = g, (b if self.first else a)
         self.all_group = dist.group.WORLD if m.size > 1 else None
+        self._warm_connections()
+
+    def _warm_connections(self) -> None:
+        """NCCL sets up the connection of a (communicator, peer) pair inside the first send / receive on it, and
+        that handshake blocks the host until the peer issues its matching call. The step posts receives long
+        before the matching sends, on several communicators at once, which would turn those first handshakes
+        into a cycle. So every connection is opened here, one communicator after the other in the same order
+        on every rank (a total order: no cycle), with a one-element message in the direction it will carry."""
+        if self.mesh.size == 1:
+            return
+        tiny = torch.zeros(1, device=self.stage.device)
+        me = self.mesh.rank
+        for (g, src, dst) in self._conn_plan:
+            if me == src:
+                dist.send(tiny, dst, group=g)
+            elif me == dst:
+                dist.recv(tiny, src, group=g)
+        torch.cuda.synchronize()
 
     # ------------------------------------------------------------------ per-microbatch bodies -----
     def _tok(self, k: int) -> torch.Tensor:
