@@ -31,6 +31,8 @@ from __future__ import annotations
 
 from typing import Dict, List, Optional, Sequence, Tuple
 
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -96,7 +98,9 @@ class PipelineEngine:
         # (one forward, one backward in turn after a warm-up of S-1-s forwards): the stages below the head
         # work on backwards while the head stage is still busy with later microbatches.
         assert schedule in ("gpipe", "1f1b")
-        self.schedule = schedule
+        self.schedule = os.environ.get("B200DIST_PP_SCHEDULE", schedule)
+        assert self.schedule in ("gpipe", "1f1b")
+        schedule = self.schedule
         head_cost = padded_vocab(config.vocab_size) / (12.0 * config.d_model)
         self.split = list(layer_split) if layer_split is not None else balanced_split(config.n_layer, self.S, head_cost)
         assert len(self.split) == self.S
@@ -109,7 +113,8 @@ class PipelineEngine:
         self.stage.rng_base = _rng.rebase(_rng.fold_in(_rng.PRNGKey(0), self.s)).base.to(self.stage.device)
         self.device = self.stage.device
         self.compute = torch.cuda.current_stream()
-        self.comm_stream = torch.cuda.Stream()
+        self.comm_stream = torch.cuda.Stream()       # sends are issued here, behind the compute that produced their data
+        self.recv_stream = torch.cuda.Stream()       # receives are issued here, behind nothing but the previous step
         self._setup_groups()
         self._bwd_order = list(range(self.Mb - 1, -1, -1)) if schedule == "gpipe" else list(range(self.Mb))
         self._first_bwd = self._bwd_order[0]
@@ -276,55 +281,61 @@ class PipelineEngine:
         with torch.cuda.stream(self.comm_stream):
             self._send_works.append(dist.isend(t, dst, group=group))
 
-    def _post_recvs(self, bufs: List[torch.Tensor], src: int, group) -> List:
-        """Posts the receives of a whole phase, in the order the peer will send."""
-        self.comm_stream.wait_stream(self.compute)       # the buffers' previous readers are queued on the compute stream
-        with torch.cuda.stream(self.comm_stream):
-            return [dist.irecv(b, src, group=group) for b in bufs]
+    def _irecv(self, buf: torch.Tensor, src: int, group):
+        with torch.cuda.stream(self.recv_stream):
+            return dist.irecv(buf, src, group=group)
+
+    def _sequence(self) -> List[Tuple[str, int]]:
+        """This stage's order of forwards and backwards."""
+        Mb = self.Mb
+        if self.schedule == "gpipe":
+            return [("F", k) for k in range(Mb)] + [("B", k) for k in self._bwd_order]
+        warm = min(self.S - 1 - self.s, Mb)
+        seq = [("F", k) for k in range(warm)]
+        for i in range(Mb - warm):
+            seq += [("F", warm + i), ("B", i)]
+        return seq + [("B", k) for k in range(Mb - warm, Mb)]
 
     def run_step(self) -> None:
-        st, Mb = self.stage, self.Mb
+        st = self.stage
         if self.use_graph and self._calls == 1 and not self.graphs:
             self._capture_all()
         self._fwd_out: Dict[int, torch.Tensor] = getattr(self, "_fwd_out", {})
         self._bwd_out: Dict[int, torch.Tensor] = getattr(self, "_bwd_out", {})
+        # receive buffers were last read by the previous step's kernels, all queued on the compute stream by now
+        self.recv_stream.wait_stream(self.compute)
         self._run("begin", 0, lambda: st._begin_step(None, None))
         has_bwd = bool(st.L or self.first)
-        # receives of the whole step, posted up front in the order the neighbours send
-        act_recv = None if self.first else self._post_recvs([st.slot_x0[k] for k in range(Mb)], self.prev_rank, self.up_prev)
-        border = self._bwd_order
-        grad_recv = None if self.last else dict(zip(border, self._post_recvs([st.slot_dx_top[k] for k in border],
-                                                                             self.next_rank, self.down_next)))
+        posted: Dict[Tuple[str, int], object] = {}
 
-        def fwd(k):
-            if act_recv is not None:
-                act_recv[k].wait()                        # the compute stream waits; the host does not
-            self._run("fwd", k, lambda: self._fwd_body(k))
-            if not self.last:
-                self._isend(self._fwd_out[k], self.next_rank, self.up_next)
+        def post(op):
+            """The receive that feeds ``op``. A receive is posted only once everything this rank contributes
+            to the message's production has been queued (the operation before ``op`` and its send): a
+            waiting receive can then never sit in front of work it depends on, however the streams are
+            mapped onto hardware queues."""
+            kind, k = op
+            if kind == "F" and not self.first:
+                posted[op] = self._irecv(st.slot_x0[k], self.prev_rank, self.up_prev)
+            elif kind == "B" and not self.last:
+                posted[op] = self._irecv(st.slot_dx_top[k], self.next_rank, self.down_next)
 
-        def bwd(k):
-            if grad_recv is not None:
-                grad_recv[k].wait()
-            if has_bwd:
-                self._run("bwd", k, lambda: self._bwd_body(k))
-            if not self.first:
-                self._isend(self._bwd_out.get(k, st.slot_dx_top[k]), self.prev_rank, self.down_prev)
-
-        if self.schedule == "gpipe":
-            for k in range(Mb):
-                fwd(k)
-            for k in border:
-                bwd(k)
-        else:
-            warm = min(self.S - 1 - self.s, Mb)
-            for k in range(warm):
-                fwd(k)
-            for i in range(Mb - warm):
-                fwd(warm + i)
-                bwd(i)
-            for k in range(Mb - warm, Mb):
-                bwd(k)
+        seq = self._sequence()
+        post(seq[0])
+        for n, op in enumerate(seq):
+            kind, k = op
+            if op in posted:
+                posted[op].wait()                         # the compute stream waits; the host does not
+            if kind == "F":
+                self._run("fwd", k, lambda: self._fwd_body(k))
+                if not self.last:
+                    self._isend(self._fwd_out[k], self.next_rank, self.up_next)
+            else:
+                if has_bwd:
+                    self._run("bwd", k, lambda: self._bwd_body(k))
+                if not self.first:
+                    self._isend(self._bwd_out.get(k, st.slot_dx_top[k]), self.prev_rank, self.down_prev)
+            if n + 1 < len(seq):
+                post(seq[n + 1])                          # host runs ahead of the GPU: this is long before op n finishes
         # ---- tied embedding: first and last stage exchange their wte gradients and both keep the sum ----
         if self.S > 1 and (self.first or self.last):
             self.comm_stream.wait_stream(self.compute)

@@ -33,6 +33,10 @@ def init_from_env(backend: Optional[str] = None) -> tuple[int, int, torch.device
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", str(rank)))
+    # More hardware launch queues than the default 8 (read when the CUDA context is created): a step uses a
+    # compute stream, side streams and one NCCL stream per communicator, and two streams that share a queue
+    # pick up each other's waits.
+    os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
     use_cuda = torch.cuda.is_available() and os.environ.get("B200DIST_FORCE_CPU", "0") != "1"
     if use_cuda:
         torch.cuda.set_device(local % torch.cuda.device_count())
