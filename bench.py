@@ -489,6 +489,22 @@ def main() -> None:
     if args.config == "mlp_dp" and args.impl == "ours" and not args.no_extra:
         names = ["gpt2s_dp", "gpt2s_fsdp", "mlp_fsdp", "gpt2m_2d"] + (["gpt2s_pp4"] if world % 4 == 0 else [])
         extra = {}
+        # The headline above is measured; an extra that hangs (a lost peer, a wedged collective) must not
+        # take it along. Past the deadline every rank's watchdog ends its process, rank 0 after printing
+        # the line with what it has.
+        import threading
+        deadline = t_start + args.extra_budget_s + 150.0
+        finished = threading.Event()
+
+        def watchdog():
+            while not finished.wait(1.0):
+                if time.perf_counter() > deadline:
+                    if rank == 0:
+                        out["extra"] = dict(extra, watchdog="an extra configuration did not finish in time; the process was ended")
+                        print(json.dumps(out), flush=True)
+                    os._exit(0)
+
+        threading.Thread(target=watchdog, daemon=True).start()
         R.clear()
         del R
         for nm in names:
@@ -511,6 +527,7 @@ def main() -> None:
                 del Rx
             except Exception as e:  # noqa: BLE001  (never lose the headline line because of an extra)
                 extra[nm] = {"error": f"{type(e).__name__}: {e}"[:300]}
+        finished.set()
         out["extra"] = extra
     if rank == 0:
         print(json.dumps(out), flush=True)

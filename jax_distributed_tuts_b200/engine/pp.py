@@ -108,7 +108,9 @@ class PipelineEngine:
                                 num_minibatches=self.Mb, init_params=init_params, layer_ids=self.split[self.s],
                                 has_embed=self.first, has_head=self.last, slots=self.Mb, use_graph=False, overlap=False,
                                 comm_axes=(self.data_axis,) if self.data_axis else ())
-        self.stage.pdl = False
+        # programmatic dependent launch inside each microbatch graph: a stage's kernels at microbatch size are
+        # short (tens of microseconds), the same regime as the MLP step (FusedEngine.pdl)
+        self.pdl = os.environ.get("B200DIST_PP_PDL", "1") == "1"
         # per-stage RNG stream (the fold_rng_over_axis the reference's stub imports, pipeline_parallel.py:37)
         self.stage.rng_base = _rng.rebase(_rng.fold_in(_rng.PRNGKey(0), self.s)).base.to(self.stage.device)
         self.device = self.stage.device
@@ -238,7 +240,7 @@ class PipelineEngine:
             g.replay()
             return
         before = _lib.launch_count()
-        _lib.set_pdl(0)
+        _lib.set_pdl(1 if self.pdl else 0)
         try:
             body()
         finally:
@@ -259,7 +261,7 @@ class PipelineEngine:
         bodies += [("end", 0, self._end_body)]
         for name, k, body in bodies:
             g = torch.cuda.CUDAGraph()
-            _lib.set_pdl(0)
+            _lib.set_pdl(1 if self.pdl else 0)
             try:
                 with torch.cuda.graph(g, stream=cap, capture_error_mode="thread_local"):
                     body()
