@@ -810,10 +810,9 @@ extern "C" int b200_attention_fwd(const void* qkv, void* out, float* lse, int ba
   CUtensorMap tm;
   rc = make_tmap_2d(&tm, qkv, 2, (uint64_t)3 * C, (uint64_t)batch * seq, (uint64_t)3 * C * 2, 64, 128, 128);
   if (rc) return rc;
-  static bool attr = false;
-  if (!attr) {
+  static unsigned long long attr = 0;
+  if (first_use_on_this_device(attr)) {
     B200_CUDA(cudaFuncSetAttribute(attention_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AttnFwdSmem::BYTES));
-    attr = true;
   }
   const float scale_log2 = 1.4426950408889634f / 8.0f;   // log2(e) / sqrt(64)
   CUtensorMap tm_out;
@@ -850,10 +849,9 @@ extern "C" int b200_attention_bwd(const void* qkv, const void* out, const void* 
   CUtensorMap tm_dqkv;
   rc = make_tmap_2d(&tm_dqkv, dqkv, 2, (uint64_t)3 * C, (uint64_t)batch * seq, (uint64_t)3 * C * 2, 64, 128, 128);
   if (rc) return rc;
-  static bool attr = false;
-  if (!attr) {
+  static unsigned long long attr = 0;
+  if (first_use_on_this_device(attr)) {
     B200_CUDA(cudaFuncSetAttribute(attention_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AttnBwdSmem::BYTES));
-    attr = true;
   }
   int pblocks = (int)((rows * 8 + 255) / 256);
   if (pblocks > num_sms() * 8) pblocks = num_sms() * 8;

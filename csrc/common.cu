@@ -112,3 +112,8 @@ void b200_reset_launch_count(void) { b200::g_launches.store(0); }
 int b200_abi_version(void) { return B200_ABI_VERSION; }
 void b200_set_pdl(int mode) { b200::g_pdl_override.store(mode < 0 ? -1 : (mode ? 1 : 0)); }
 }
+
+#ifndef B200_SOURCE_HASH
+#define B200_SOURCE_HASH "unstamped"
+#endif
+extern "C" const char* b200_source_hash(void) { return B200_SOURCE_HASH; }

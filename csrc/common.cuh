@@ -49,6 +49,17 @@ int make_tmap_2d(CUtensorMap* out, const void* base, int elem_bytes, uint64_t in
                  uint64_t outer_stride_bytes, uint32_t box_inner, uint32_t box_outer,
                  int swizzle_bytes /*0,32,64,128*/);
 int num_sms();
+// One-time set-up per device and call site: function attributes (dynamic shared memory limits) belong
+// to a device, so a process that drives several GPUs must set them on each. `mask` is the call
+// site's static word, one bit per device ordinal. (Two threads racing here set the attribute twice.)
+inline bool first_use_on_this_device(unsigned long long& mask) {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return true;
+  const unsigned long long bit = 1ull << (dev & 63);
+  if (mask & bit) return false;
+  mask |= bit;
+  return true;
+}
 
 // ---------------------------------------------------------------------------------------
 // Device helpers

@@ -969,11 +969,10 @@ static int launch_gemm(const b200_gemm_args& a, const GemmDev& dev, cudaStream_t
     if (rc) return rc;
   }
   auto kern = gemm_tcgen05_kernel<BN, A_MN, B_MN>;
-  static bool attr_done = false;
-  if (!attr_done) {
+  static unsigned long long attr_done = 0;
+  if (first_use_on_this_device(attr_done)) {
     B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    Cfg::SMEM_BYTES));
-    attr_done = true;
   }
   int m_tiles = (a.m + BM - 1) / BM;
   int n_tiles = (a.b_shard_mode == 2) ? ((a.b_shard_len + BN - 1) / BN) * dev.nsrc
@@ -1008,10 +1007,9 @@ static int launch_gemm_pair(const b200_gemm_args& a, const GemmDev& dev, cudaStr
     if (rc) return rc;
   }
   auto kern = gemm_tcgen05_pair_kernel<BN, A_MN, B_MN>;
-  static bool attr_done = false;
-  if (!attr_done) {
+  static unsigned long long attr_done = 0;
+  if (first_use_on_this_device(attr_done)) {
     B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
-    attr_done = true;
   }
   int m_tiles = (a.m + 2 * BM - 1) / (2 * BM);
   int n_tiles = (a.b_shard_mode == 2) ? ((a.b_shard_len + BN - 1) / BN) * dev.nsrc : (a.n + BN - 1) / BN;

@@ -20,6 +20,9 @@ extern "C" {
 
 const char* b200_last_error(void);
 int b200_abi_version(void);
+/* Digest of the sources this library was built from (csrc/, include/), or "unstamped". The Python
+ * loader compares it with the tree it runs from and rebuilds a library that does not match. */
+const char* b200_source_hash(void);
 /* Number of kernels launched by this library since the last reset (host-side counter). */
 long long b200_launch_count(void);
 void b200_reset_launch_count(void);

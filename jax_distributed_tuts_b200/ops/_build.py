@@ -46,12 +46,25 @@ def _deps_mtime() -> float:
     return max((h.stat().st_mtime for h in hdrs), default=0.0)
 
 
+def source_hash() -> str:
+    """Digest of everything the library is built from (csrc/*.cu, csrc/*.cuh, include/*.h). It is compiled
+    into the library (``b200_source_hash()``) and kept beside it, so a library built from other sources -
+    an older checkout, a header edited after the build - is rebuilt instead of loaded."""
+    import hashlib
+    h = hashlib.sha256()
+    for f in sorted(list(CSRC.glob("*.cu")) + list(CSRC.glob("*.cuh")) + list(INCLUDE.glob("*.h"))):
+        h.update(f.name.encode())
+        h.update(f.read_bytes())
+    return h.hexdigest()[:16]
+
+
+HASH_PATH = LIB_DIR / "libb200dist.so.hash"
+
+
 def needs_build() -> bool:
-    if not LIB_PATH.exists():
+    if not LIB_PATH.exists() or not HASH_PATH.exists():
         return True
-    lib_m = LIB_PATH.stat().st_mtime
-    newest = max([s.stat().st_mtime for s in _sources()] + [_deps_mtime()])
-    return newest > lib_m
+    return HASH_PATH.read_text().strip() != source_hash()
 
 
 def build(force: bool = False, verbose: bool = False) -> Path:
@@ -62,12 +75,16 @@ def build(force: bool = False, verbose: bool = False) -> Path:
     OBJ_DIR.mkdir(parents=True, exist_ok=True)
     LIB_DIR.mkdir(parents=True, exist_ok=True)
     hdr_m = _deps_mtime()
+    digest = source_hash()
 
     def compile_one(src: Path) -> Path:
         obj = OBJ_DIR / (src.stem + ".o")
-        if not force and obj.exists() and obj.stat().st_mtime > max(src.stat().st_mtime, hdr_m):
+        stamped = src.name == "common.cu"          # carries the source digest: always recompiled (a second)
+        if not force and not stamped and obj.exists() and obj.stat().st_mtime > max(src.stat().st_mtime, hdr_m):
             return obj
         cmd = [nvcc, *NVCC_FLAGS, "-c", str(src), "-o", str(obj)]
+        if stamped:
+            cmd.insert(1, f'-DB200_SOURCE_HASH="{digest}"')
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
         r = subprocess.run(cmd, capture_output=True, text=True)
@@ -87,6 +104,7 @@ def build(force: bool = False, verbose: bool = False) -> Path:
     if r.returncode != 0:
         raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
     os.replace(tmp, LIB_PATH)
+    HASH_PATH.write_text(digest + "\n")
     return LIB_PATH
 
 

@@ -128,6 +128,8 @@ class B200Error(RuntimeError):
 def _declare(lib: C.CDLL) -> None:
     vp, i32, i64, f32, u64 = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_uint64
     lib.b200_last_error.restype = C.c_char_p
+    lib.b200_source_hash.restype = C.c_char_p
+    lib.b200_source_hash.argtypes = []
     lib.b200_abi_version.restype = C.c_int
     lib.b200_launch_count.restype = C.c_longlong
     lib.b200_reset_launch_count.restype = None
@@ -198,6 +200,13 @@ def lib() -> C.CDLL:
     if _lib is not None:
         return _lib
     path = Path(os.environ["B200DIST_LIB"]) if os.environ.get("B200DIST_LIB") else _build.LIB_PATH   # override: A/B builds
+    if path == _build.LIB_PATH and _build.needs_build():
+        # missing, or built from other sources than this tree's (another checkout, a header edited since):
+        # rebuild where a compiler exists, otherwise fall through to the checks below
+        try:
+            _build.build()
+        except Exception:  # noqa: BLE001
+            pass
     if not path.exists():
         raise B200Error(
             f"{path} is missing: build the CUDA library first "
@@ -208,6 +217,12 @@ def lib() -> C.CDLL:
     got = handle.b200_abi_version()
     if got != ABI_VERSION:
         raise B200Error(f"{path} has ABI version {got}, expected {ABI_VERSION}: rebuild it")
+    if path == _build.LIB_PATH and hasattr(handle, "b200_source_hash"):
+        handle.b200_source_hash.restype = C.c_char_p
+        built_from = handle.b200_source_hash().decode()
+        if built_from != _build.source_hash():
+            raise B200Error(f"{path} was built from other sources (digest {built_from}, this tree {_build.source_hash()}): "
+                            "rebuild it (python -c 'import __graft_entry__ as g; g.build()')")
     _lib = handle
     return handle
 

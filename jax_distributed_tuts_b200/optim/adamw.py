@@ -10,7 +10,7 @@ every leaf (no mask). ``opt_state`` has Optax's shape
 sharded optimizer state (param_sharding.py:232-239).
 
 This module is the generic pytree implementation (any device, any leaf). The fused path is
-``b200_adamw`` / ``b200_allreduce_adamw`` / ``b200_reducescatter_adamw`` over flat buffers.
+``b200_adamw`` (stand-alone) and ``b200_fused_update`` (gradient all-reduce or reduce-scatter + AdamW + publish in one launch) over flat buffers.
 """
 from __future__ import annotations
 

@@ -5,7 +5,7 @@ This file is the generic tier: it works on any mesh/backend (gloo on CPU, NCCL o
 with any ``loss_fn``. ``make_train_step_dp`` is the analogue of
 ``jax.jit(shard_map(train_step_dp, ...), donate_argnames=("state", "metrics"))``
 (data_paral.py:241-251); when the state was created by the fused engine
-(``engine.DPEngine``) the returned callable runs the CUDA-graph-captured, fused-collective
+(``engine.MLPEngine`` / ``engine.GPT2Engine`` with ``mode="dp"``) the returned callable runs the CUDA-graph-captured, fused-collective
 step instead.
 """
 from __future__ import annotations

@@ -6,7 +6,7 @@ reduce-scatters the gradient and divides by the axis size (``gather_arr_mean_gra
 gradients and AdamW state stay sharded.
 
 Generic tier: the gather is a collective call followed by the consuming op. The fused tier
-(``engine.FSDPEngine``) never materialises the gathered weight: the consuming tcgen05 GEMM's
+(``engine.MLPEngine`` / ``engine.GPT2Engine`` with ``mode="fsdp"``) never materialises the gathered weight: the consuming tcgen05 GEMM's
 TMA producer reads the peer shards in place, and the reduce-scatter is fused with the sharded
 AdamW step.
 """

@@ -152,7 +152,8 @@ def main():
                                  use_graph=True, fsdp_weights=fw)
                 s3 = eng.make_state(smodel, rng.PRNGKey(2))
                 for _ in range(4):
-                    s3, m3 = eng.train_step(s3, None, sb)
+                    s3, m3 = eng.train_step(s3, None, sb)      # metrics=None: m3 holds this step only
+                last_loss = float(m3["loss"][0]) / m3["loss"][1]
                 torch.cuda.synchronize()
                 evs = []
                 for _ in range(10):
@@ -165,7 +166,7 @@ def main():
                 t = torch.tensor([ms], device=device)
                 dist.all_reduce(t, op=dist.ReduceOp.MAX)
                 log(f"gpt2-small {name} x{world}: {t.item():.2f} ms/step, {8 * world / t.item() * 1e3:.0f} samples/s, "
-                    f"loss {float(m3['loss'][0]) / m3['loss'][1]:.3f}, launches/step {eng.launches_per_step}")
+                    f"loss of the last warm-up step {last_loss:.3f}, launches/step {eng.launches_per_step}")
                 del eng
                 torch.cuda.empty_cache()
             except Exception as e:  # noqa: BLE001
