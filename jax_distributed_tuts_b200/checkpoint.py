@@ -6,7 +6,9 @@ from ``flax.serialization``: ``{"step", "params", "opt_state": {"0": {"count", "
 {...}}`` in fp32, (in, out) kernels (data_paral.py:86-98,137-143). Checkpoints here always hold the
 *global, unsharded* arrays — the same tensors for DP, FSDP, 2-D mesh and pipeline runs — so a file
 written by one strategy loads into any other; sharded runs gather on save and slice on load with
-the same shard rule as ``shard_params`` (param_sharding.py:89-113).
+the same shard rule as ``shard_params`` (param_sharding.py:89-113); pipeline runs merge the stages'
+trees over the ``pipe`` axis on save (``pipe_axis=``; the tied ``wte`` is stored once) and each stage
+picks its own blocks on load (``restore_params`` with the stage's tree as template).
 
 Two containers:
   * ``.msgpack``     Flax's wire format: msgpack map with ndarrays as ExtType 1 holding
@@ -67,9 +69,45 @@ def partition_names(params: Pytree) -> Dict[str, Tuple[Optional[str], ...]]:
     return {p: tuple(v.names) for p, v in tree_leaves_with_path(params, is_leaf=is_partitioned) if is_partitioned(v)}
 
 
-def state_dict(state, *, mesh: Optional[Mesh] = None) -> Dict[str, Any]:
+def _merge_trees(trees) -> Dict[str, Any]:
+    """Union of nested dicts by key; where several stages hold the same leaf (the tied ``wte`` lives
+    on the first and on the last pipeline stage) the first one is kept."""
+    out: Dict[str, Any] = {}
+    for t in trees:
+        for k, v in t.items():
+            if isinstance(v, dict):
+                out[k] = _merge_trees([out.get(k, {}), v]) if isinstance(out.get(k), dict) else _merge_trees([v])
+            else:
+                out.setdefault(k, v)
+    return out
+
+
+def merge_over_pipe(sd: Dict[str, Any], mesh: Mesh, pipe_axis: str) -> Dict[str, Any]:
+    """A pipeline stage's state dict holds only the blocks that stage owns. Gathers the stages' dicts over
+    the ``pipe`` axis (every rank of the axis calls this) and returns the union: the whole model's
+    parameters and Adam moments, as a single-device run would have saved them."""
+    import torch.distributed as dist
+    n = mesh.axis_size(pipe_axis)
+    if n == 1:
+        return sd
+    parts = [None] * n
+    dist.all_gather_object(parts, {"params": sd["params"], "opt": sd["opt_state"]["0"]}, group=mesh.group(pipe_axis))
+    out = dict(sd)
+    out["params"] = _merge_trees([p["params"] for p in parts])
+    adam = dict(sd["opt_state"]["0"])
+    adam["mu"] = _merge_trees([p["opt"]["mu"] for p in parts])
+    adam["nu"] = _merge_trees([p["opt"]["nu"] for p in parts])
+    out["opt_state"] = dict(sd["opt_state"], **{"0": adam})
+    return out
+
+
+def state_dict(state, *, mesh: Optional[Mesh] = None, pipe_axis: Optional[str] = None) -> Dict[str, Any]:
     """Global (unsharded) state dict of a TrainState. Sharded leaves are gathered over their named
-    axes; states owned by a fused engine read the engine's buffers."""
+    axes; states owned by a fused engine read the engine's buffers; a pipeline stage's state
+    (``pipe_axis`` names the mesh axis the stages sit on) is merged with the other stages' into the
+    whole model."""
+    if pipe_axis is not None and mesh is not None and pipe_axis in mesh.axis_names:
+        return merge_over_pipe(state_dict(state, mesh=mesh), mesh, pipe_axis)
     from .parallel.fsdp import unshard_params
     eng = getattr(state, "engine", None)
     if eng is not None:
@@ -148,10 +186,17 @@ def _unflatten(flat: Dict[str, Any]) -> Dict[str, Any]:
     return out
 
 
-def save_checkpoint(path: str, state, *, mesh: Optional[Mesh] = None, rank: Optional[int] = None) -> Optional[str]:
-    """Writes the global state. Every rank must call it (sharded leaves are gathered collectively);
-    only rank 0 touches the file system. The container follows the file extension."""
-    sd = state_dict(state, mesh=mesh)
+def save_checkpoint(path: str, state, *, mesh: Optional[Mesh] = None, rank: Optional[int] = None,
+                    pipe_axis: Optional[str] = None) -> Optional[str]:
+    """Writes the global state. Every rank must call it (sharded leaves are gathered collectively, pipeline
+    stages are merged over ``pipe_axis``); only rank 0 touches the file system. The container follows the
+    file extension. A state that holds only part of the model (a pipeline stage) is refused unless
+    ``pipe_axis`` says how to complete it: a file with one stage's blocks would restore into nothing."""
+    if pipe_axis is None and mesh is not None and "pipe" in mesh.axis_names and mesh.axis_size("pipe") > 1 \
+            and getattr(state, "engine", None) is None:
+        raise ValueError("this mesh has a 'pipe' axis: pass pipe_axis='pipe' so the stages' parameters are merged "
+                         "into one global checkpoint (each stage's TrainState holds only its own blocks)")
+    sd = state_dict(state, mesh=mesh, pipe_axis=pipe_axis)
     if rank is None:
         import torch.distributed as dist
         rank = dist.get_rank() if dist.is_available() and dist.is_initialized() else 0

@@ -371,6 +371,28 @@ class PipelineEngine:
         """This stage's parameters (global layout of its leaves)."""
         return self.stage.params_tree()
 
+    def state_dict(self) -> Dict[str, object]:
+        """The whole model's state in the checkpoint layout (``checkpoint.py``): every stage contributes its
+        blocks, the dicts are merged over the pipe axis (tied ``wte`` once), Adam moments in the global
+        per-leaf layout. Collective over the mesh; every rank gets the same dict."""
+        from .. import checkpoint as ckpt
+        st = self.stage
+        og = st.opt_state_global()
+        sd = {"step": ckpt._to_numpy(st.step_count).reshape(()).astype("int32"), "params": ckpt._plain(st.params_tree()),
+              "opt_state": {"0": {"count": ckpt._to_numpy(og["count"]).reshape(()), "mu": ckpt._plain(og["mu"]),
+                                  "nu": ckpt._plain(og["nu"])}, "1": {}, "2": {}},
+              "rng": ckpt._to_numpy(st.rng_base)}
+        return ckpt.merge_over_pipe(sd, self.mesh, self.pipe_axis)
+
+    def load_state_dict(self, loaded: Dict[str, object]) -> None:
+        """Inverse of ``state_dict`` (also accepts a checkpoint written by any other strategy): each stage
+        keeps the leaves it owns."""
+        import numpy as np
+        st = self.stage
+        st.load_params(loaded["params"])
+        adam = loaded["opt_state"]["0"]
+        st.load_opt_state_global(adam["mu"], adam["nu"], int(np.asarray(adam["count"]).reshape(-1)[0]))
+
     def report(self) -> Dict[str, object]:
         """Layer split, ideal GPipe bubble, and how long this stage's kernels are busy per step (its
         graphs replayed back to back without any communication), max / min over the stages: step time

@@ -188,3 +188,34 @@ def fsdp2d_worker(rank, world, steps, lr):
         names = {k: {kk: (vv.names if is_partitioned(vv) else None) for kk, vv in v.items()}
                  for k, v in state.params.items()}
     return {"params": full, "metrics": metrics, "names": names, "coords": mesh.coords}
+
+
+def pp_ckpt_worker(rank, world, path):
+    """2-stage GPipe, one step, global checkpoint merged over the pipe axis, restored into each stage."""
+    from jax_distributed_tuts_b200 import checkpoint as ckpt
+    from jax_distributed_tuts_b200.models.gpt2 import GPT2, gpt2_config
+    from jax_distributed_tuts_b200.parallel import pp
+    import torch.distributed as dist
+    cfg = gpt2_config("tiny", n_layer=4)
+    mesh = Mesh((1, world), ("data", "pipe"))
+    model = GPT2(cfg)
+    g = torch.Generator().manual_seed(0)
+    tok = torch.randint(0, cfg.vocab_size, (4, 129), generator=g)
+    batch = Batch(tok[:, :128].contiguous(), tok[:, 1:].contiguous())
+    with mesh:
+        stage = pp.GPT2Stage(model, mesh.axis_index("pipe"), world)
+        state = pp.init_pp(rng.PRNGKey(7), batch.inputs, stage, learning_rate=1e-3)
+        step = pp.make_train_step_pp(mesh, stage_model=stage, num_microbatches=2, pipe_axis="pipe")
+        state, _ = step(state, None, batch)
+        refused = False
+        try:
+            ckpt.save_checkpoint(path, state, mesh=mesh)
+        except ValueError:
+            refused = True
+        ckpt.save_checkpoint(path, state, mesh=mesh, pipe_axis="pipe")
+        dist.barrier()
+        loaded = ckpt.load_checkpoint(path)
+        restored = ckpt.restore_params(state.params, loaded["params"], mesh=mesh)
+        same = all(torch.equal(a, b) for a, b in zip(tree_leaves(state.params), tree_leaves(restored)))
+    return {"refused_without_axis": refused, "reload_equal": bool(same), "top_keys": sorted(loaded["params"].keys()),
+            "mu_keys": sorted(loaded["opt_state"]["0"]["mu"].keys())}

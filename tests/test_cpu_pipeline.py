@@ -64,3 +64,23 @@ def test_gpipe_with_data_axis():
         for k in a:
             assert torch.equal(a[k], b[k]), (stage, k)
     assert by[(0, 0)]["metrics"]["loss"][1] == 2 * 4 * 128
+
+
+def test_pipeline_checkpoint_holds_the_whole_model(tmp_path):
+    """A pipeline run saves ONE global checkpoint (stages merged over the pipe axis, tied wte once) and each
+    stage restores its own blocks from it; saving a single stage's state without naming the axis is refused."""
+    path = str(tmp_path / "pp.msgpack")
+    res = sim_multiCPU_dev(W.pp_ckpt_worker, 2, args=(path,))
+    want = ["h_0", "h_1", "h_2", "h_3", "ln_f", "wpe", "wte"]
+    for r in res:
+        assert r["refused_without_axis"] and r["reload_equal"]
+        assert r["top_keys"] == want and r["mu_keys"] == want
+
+
+def test_balanced_split_puts_fewer_blocks_next_to_the_head():
+    from jax_distributed_tuts_b200.engine.pp import balanced_split
+    assert [len(r) for r in balanced_split(12, 4, 5.46)] == [4, 4, 4, 0]
+    assert [len(r) for r in balanced_split(24, 4, 4.1)] == [7, 7, 7, 3]
+    assert [len(r) for r in balanced_split(12, 1, 5.46)] == [12]
+    s = balanced_split(4, 4, 0.3)
+    assert [list(r) for r in s] == [[0], [1], [2], [3]]

@@ -65,7 +65,16 @@ def run_case(rank, world, device, S, use_graph, schedule="1f1b") -> bool:
             losses.append(float(ls) / n)
         torch.cuda.synchronize()
         got = dict(tree_leaves_with_path(eng.params_tree()))
-    ok = all(abs(a - b) < 2e-3 for a, b in zip(ref_losses, losses))
+        # the merged checkpoint holds the whole model and reloads into the stages bit for bit
+        sd = eng.state_dict()
+        want_keys = sorted([f"h_{i}" for i in range(cfg.n_layer)] + ["wte", "wpe", "ln_f"])
+        ckpt_ok = sorted(sd["params"].keys()) == want_keys and sorted(sd["opt_state"]["0"]["mu"].keys()) == want_keys
+        before = {k: v.clone() for k, v in got.items()}
+        eng.load_state_dict(sd)
+        torch.cuda.synchronize()
+        again = dict(tree_leaves_with_path(eng.params_tree()))
+        ckpt_ok &= all(torch.equal(before[k], again[k]) for k in before)
+    ok = ckpt_ok and all(abs(a - b) < 2e-3 for a, b in zip(ref_losses, losses))
     worst = ("", 0.0)
     for k, v in got.items():
         r = ref_params[k]
