@@ -1,6 +1,12 @@
 """Pipeline parallelism: what the reference's pipeline_parallel.py stub was heading for, per
 BASELINE.json - a GPipe schedule over 4 stages with microbatched stage-to-stage transfers.
-A small GPT-2 (8 layers) is split over the "pipe" axis of a (data, pipe) mesh."""
+A small GPT-2 (8 layers) is split over the "pipe" axis of a (data, pipe) mesh.
+
+On CPU (the fake cluster) and with ``B200DIST_ENGINE=0`` this is the generic tier (autograd, eager
+launches, ``parallel/pp.py``); on GPUs under torchrun it is the fused pipeline engine (``engine/pp.py``:
+per-stage flat buffers, a CUDA graph per microbatch, NCCL p2p on its own streams)."""
+import os
+
 from _common import launch
 
 import torch
@@ -24,6 +30,20 @@ def worker(rank, world):
     g = torch.Generator().manual_seed(0)
     tok = torch.randint(0, cfg.vocab_size, (8 * n_data, 129), generator=g)
     batch = Batch(tok[:, :128].contiguous(), tok[:, 1:].contiguous())
+    if mesh.device.type == "cuda" and os.environ.get("B200DIST_ENGINE", "1") == "1":
+        from jax_distributed_tuts_b200.engine.pp import PipelineEngine
+        d = mesh.axis_index("data")
+        local = Batch(batch.inputs[d * 8:(d + 1) * 8].pin_memory(), batch.labels[d * 8:(d + 1) * 8].pin_memory())
+        with mesh:
+            params = model.init({"params": rng.PRNGKey(0)}, local.inputs[:1])["params"]
+            eng = PipelineEngine(cfg, mesh, batch_per_replica=8, seq_len=128, num_microbatches=MICROBATCHES, lr=1e-3,
+                                 init_params=params)
+            for _ in range(11):
+                loss_sum, count = eng.train_step(local)
+            if rank == 0:
+                print(f"mesh data={n_data} x pipe={n_stages}, layers per stage: {[len(r) for r in eng.split]} ({eng.schedule})")
+                print_metrics({"loss": (loss_sum, count)}, "pp - fused pipeline engine")
+        return
     with mesh:
         stage = pp.GPT2Stage(model, mesh.axis_index("pipe"), n_stages)
         local = dp.shard_batch(batch, "data")

@@ -19,7 +19,7 @@ def _ngpu():
 def _torchrun(script, n, port):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}", "--master-addr", "127.0.0.1",
            "--master-port", str(port), os.path.join(ROOT, "tools", script)]
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=ROOT)
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT)
     tail = "\n".join((r.stdout + r.stderr).splitlines()[-30:])
     assert r.returncode == 0, tail
     return r.stdout
@@ -35,3 +35,10 @@ def test_fused_mlp_engines_match_nccl():
 def test_fused_gpt2_engines_match_nccl():
     out = _torchrun("gpu_check_multi_gpt.py", min(_ngpu(), 8), 29532)
     assert "MULTI-GPU GPT CHECK PASS" in out
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs at least 2 GPUs")
+def test_pipeline_engine_matches_single_gpu_engine():
+    n = 4 if _ngpu() >= 4 else 2
+    out = _torchrun("gpu_check_pp.py", n, 29533)
+    assert "PIPELINE CHECK PASS" in out
