@@ -148,7 +148,7 @@ __device__ __forceinline__ void mc_st_b32x2(void* mc, uint32_t a, uint32_t b) {
 __device__ __forceinline__ void adamw1(float& p, float& m, float& v, float g, const b200_adamw_hparams& hp, float c1, float c2) {
   m = hp.beta1 * m + (1.0f - hp.beta1) * g;
   v = hp.beta2 * v + (1.0f - hp.beta2) * g * g;
-  p = p - hp.lr * ((m * c1) / (sqrtf(v * c2) + hp.eps) + hp.weight_decay * p);
+  p = p - hp.lr * (__fdividef(m * c1, sqrtf(v * c2) + hp.eps) + hp.weight_decay * p);   // (2 ulp division)
 }
 
 __device__ __forceinline__ void stamp(const RankArgs& a, int bid, int k) {
@@ -179,26 +179,29 @@ __device__ __forceinline__ void update_segment(const RankArgs& a, const b200_seg
     const int64_t nthreads = static_cast<int64_t>(vnblocks) * blockDim.x;
     constexpr int U = 4;   // independent 16-byte vectors per thread per iteration (memory-level parallelism)
     for (int64_t i0 = static_cast<int64_t>(vbid) * blockDim.x + threadIdx.x; i0 < total4; i0 += nthreads * U) {
-      // per vector only (row, col) are kept (32-bit); the three 64-bit offsets are rebuilt where used
-      uint32_t vrow[U], vcol[U];
+      // Per vector two 32-bit element offsets relative to the segment: `rel` into the contiguous local /
+      // destination rows (always 4 * index) and `srel` into the possibly strided source rows. The engines
+      // check that a segment spans fewer than 2^31 elements, pitch included.
+      uint32_t rel[U], srel[U];
       bool ok[U];
       float4 g[U], pp[U], mm[U], vv[U];
       float* p_base = broadcast ? c.param[c.rank] : a.p_local;
+      const bool contiguous = sg.rows == 1 || sg.src_pitch == sg.row_len;
 #pragma unroll
       for (int u = 0; u < U; ++u) {
         const int64_t i = i0 + u * nthreads;
         ok[u] = i < total4;
         const uint32_t ii = ok[u] ? static_cast<uint32_t>(i) : 0u;
-        // rows == 1 (every DP segment, contiguous FSDP shards) needs no division; otherwise the
-        // segment is far below 2^31 vectors and a 32-bit division is enough
-        vrow[u] = sg.rows == 1 ? 0u : ii / static_cast<uint32_t>(rl4);
-        vcol[u] = (ii - vrow[u] * static_cast<uint32_t>(rl4)) << 2;
+        rel[u] = ii << 2;
+        srel[u] = rel[u];
+        if (!contiguous) {       // column shards: rows of row_len elements, src_pitch apart
+          const uint32_t row = ii / static_cast<uint32_t>(rl4);
+          srel[u] = row * static_cast<uint32_t>(sg.src_pitch) + ((ii - row * static_cast<uint32_t>(rl4)) << 2);
+        }
       }
-      auto src_of = [&](int u) { return sg.src_off + static_cast<int64_t>(vrow[u]) * sg.src_pitch + vcol[u]; };
-      auto loc_of = [&](int u) { return sg.loc_off + static_cast<int64_t>(vrow[u]) * sg.row_len + vcol[u]; };
-      auto dst_of = [&](int u) {
-        return (broadcast ? sg.dst_off : sg.loc_off) + static_cast<int64_t>(vrow[u]) * sg.row_len + vcol[u];
-      };
+      auto src_of = [&](int u) { return sg.src_off + srel[u]; };
+      auto loc_of = [&](int u) { return sg.loc_off + rel[u]; };
+      auto dst_of = [&](int u) { return (broadcast ? sg.dst_off : sg.loc_off) + rel[u]; };
       // ---- loads (all issued before any use; the peer-load path fetches m / v / p after its sums to
       //      keep the registers for the peers' vectors) ----
       const bool p2p = c.world > 1 && !use_mc;

@@ -644,7 +644,7 @@ class FusedEngine:
         if self.mode == "dp":
             for (b0, b1) in self.layout.bucket_ranges:
                 sl = (b1 - b0) // W
-                assert sl // 4 < 2 ** 31, "bucket slice too large for one fused-update segment: use more buckets"
+                assert sl < 2 ** 31, "bucket slice too large for one fused-update segment: use more buckets"
                 seg = Seg(src_off=b0 + r * sl, src_pitch=sl, dst_off=b0 + r * sl, loc_off=b0 // W, rows=1, row_len=sl)
                 self.bucket_segs.append((self._segs_to_device([seg]), 1))
                 self._host_segs.append(seg)
@@ -664,7 +664,7 @@ class FusedEngine:
                 seg = Seg(src_off=sp.offset + self.sidx * rws * sp.ld, src_pitch=sp.ld, dst_off=0,
                           loc_off=self.loc_off[path], rows=rws, row_len=sp.ld)
             # the kernel indexes a segment's 16-byte vectors and its rows / columns with 32 bits
-            assert seg.rows * seg.row_len // 4 < 2 ** 31 and seg.row_len < 2 ** 31 and seg.rows < 2 ** 31, \
+            assert seg.rows * max(seg.row_len, seg.src_pitch) < 2 ** 31, \
                 f"{path}: segment of {seg.rows} x {seg.row_len} elements is too large for one fused-update segment"
             per_bucket.setdefault(sp.bucket, []).append(seg)
         order = sorted(per_bucket)

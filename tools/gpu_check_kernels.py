@@ -21,7 +21,7 @@ GROUPS = ["gemm_kmajor", "gemm_mnmajor", "gemm_epilogue", "gemm_xent", "gemm_sha
 
 def _rel_err(got, ref):
     """Largest error relative to the largest reference magnitude, AND an element-wise test: every element
-    must satisfy |got - ref| <= 0.08 |ref| + 0.03 rms(ref). The max-norm alone lets a wrong value hide in a
+    must satisfy |got - ref| <= 0.10 |ref| + 0.05 rms(ref). The max-norm alone lets a wrong value hide in a
     small-magnitude region (a flipped sign there is far below the global scale); the element-wise bound is
     loose enough for bf16 outputs and approximate activations, tight enough for that. A violation is
     reported as an error of at least 1."""
@@ -32,10 +32,10 @@ def _rel_err(got, ref):
     d = (got - ref).abs()
     err = (d.max() / denom).item()
     rms = ref.pow(2).mean().sqrt().clamp_min(1e-12)
-    bad = d > 0.08 * ref.abs() + 0.03 * rms
+    bad = d > 0.10 * ref.abs() + 0.05 * rms
     nbad = int(bad.sum().item()) if bad.numel() else 0
     if nbad or err != err:
-        worst = (d / (0.08 * ref.abs() + 0.03 * rms)).max().item()
+        worst = (d / (0.10 * ref.abs() + 0.05 * rms)).max().item()
         print(f"    element-wise bound violated by {nbad} of {bad.numel()} elements (worst {worst:.1f}x the bound)", flush=True)
         return max(err, 1.0)
     return err
