@@ -19,31 +19,35 @@ GROUPS = ["gemm_kmajor", "gemm_mnmajor", "gemm_epilogue", "gemm_xent", "gemm_sha
           "attention", "gemm_perf", "gemm_epi_perf"]
 
 
+class _Err(float):
+    """Max-norm error that also carries the element-wise excess (see ``_rel_err``)."""
+    elem = 0.0
+    nbad_at = None
+
+
 def _rel_err(got, ref):
-    """Largest error relative to the largest reference magnitude, AND an element-wise test: every element
-    must satisfy |got - ref| <= 0.10 |ref| + 0.05 rms(ref). The max-norm alone lets a wrong value hide in a
-    small-magnitude region (a flipped sign there is far below the global scale); the element-wise bound is
-    loose enough for bf16 outputs and approximate activations, tight enough for that. A violation is
-    reported as an error of at least 1."""
+    """Largest error relative to the largest reference magnitude. The returned float also carries
+    ``elem`` = max over elements of (|got - ref| - 0.1 |ref|) / rms(ref), which ``_report`` holds against
+    25 x the check's tolerance: the max-norm alone lets a wrong value hide in a small-magnitude region (a
+    flipped sign there is far below the global scale), the element-wise bound scaled by the same tolerance
+    does not."""
     import torch
     got = got.float()
     ref = ref.float()
     denom = ref.abs().max().clamp_min(1e-6)
     d = (got - ref).abs()
-    err = (d.max() / denom).item()
+    err = _Err((d.max() / denom).item())
     rms = ref.pow(2).mean().sqrt().clamp_min(1e-12)
-    bad = d > 0.10 * ref.abs() + 0.05 * rms
-    nbad = int(bad.sum().item()) if bad.numel() else 0
-    if nbad or err != err:
-        worst = (d / (0.10 * ref.abs() + 0.05 * rms)).max().item()
-        print(f"    element-wise bound violated by {nbad} of {bad.numel()} elements (worst {worst:.1f}x the bound)", flush=True)
-        return max(err, 1.0)
+    err.elem = ((d - 0.10 * ref.abs()).clamp_min(0) / rms).max().item() if d.numel() else 0.0
     return err
 
 
 def _report(name, err, tol):
-    ok = err == err and err <= tol
-    print(f"  [{'ok' if ok else 'FAIL'}] {name}: rel_err={err:.3e} (tol {tol:.1e})", flush=True)
+    elem = getattr(err, "elem", 0.0)
+    elem_ok = elem == elem and elem <= 25.0 * tol
+    ok = err == err and err <= tol and elem_ok
+    extra = "" if elem_ok else f" element-wise excess {elem:.3e} rms (bound {25.0 * tol:.1e})"
+    print(f"  [{'ok' if ok else 'FAIL'}] {name}: rel_err={float(err):.3e} (tol {tol:.1e}){extra}", flush=True)
     return ok
 
 
