@@ -74,6 +74,21 @@ def balanced_split(n_layer: int, n_stages: int, head_cost: float, embed_cost: fl
     return out
 
 
+def stage_sequence(schedule: str, n_stages: int, stage: int, n_micro: int) -> List[Tuple[str, int]]:
+    """Order of forwards ("F", k) and backwards ("B", k) on one stage. "gpipe": every forward, then the
+    backwards from the last microbatch down. "1f1b": S-1-s warm-up forwards, then one forward and one
+    backward in turn (backwards in arrival order 0, 1, ...), then the remaining backwards. Every stage
+    sends its forwards up and its backwards down in exactly this order, which is also the order in
+    which its neighbours post the matching receives (checked by simulation in tests/test_cpu_pipeline.py)."""
+    if schedule == "gpipe":
+        return [("F", k) for k in range(n_micro)] + [("B", k) for k in range(n_micro - 1, -1, -1)]
+    warm = min(n_stages - 1 - stage, n_micro)
+    seq = [("F", k) for k in range(warm)]
+    for i in range(n_micro - warm):
+        seq += [("F", warm + i), ("B", i)]
+    return seq + [("B", k) for k in range(n_micro - warm, n_micro)]
+
+
 class PipelineEngine:
     """``train_step(batch) -> (loss_sum, token_count)`` for one (data, pipe) mesh coordinate."""
 
@@ -288,15 +303,7 @@ class PipelineEngine:
             return dist.irecv(buf, src, group=group)
 
     def _sequence(self) -> List[Tuple[str, int]]:
-        """This stage's order of forwards and backwards."""
-        Mb = self.Mb
-        if self.schedule == "gpipe":
-            return [("F", k) for k in range(Mb)] + [("B", k) for k in self._bwd_order]
-        warm = min(self.S - 1 - self.s, Mb)
-        seq = [("F", k) for k in range(warm)]
-        for i in range(Mb - warm):
-            seq += [("F", warm + i), ("B", i)]
-        return seq + [("B", k) for k in range(Mb - warm, Mb)]
+        return stage_sequence(self.schedule, self.S, self.s, self.Mb)
 
     def run_step(self) -> None:
         st = self.stage

@@ -219,3 +219,18 @@ def pp_ckpt_worker(rank, world, path):
         same = all(torch.equal(a, b) for a, b in zip(tree_leaves(state.params), tree_leaves(restored)))
     return {"refused_without_axis": refused, "reload_equal": bool(same), "top_keys": sorted(loaded["params"].keys()),
             "mu_keys": sorted(loaded["opt_state"]["0"]["mu"].keys())}
+
+
+def fused_backend_fallback_worker(rank, world):
+    """set_backend("fused") on CPU ranks: the fused kernels need GPUs, the calls fall back to the axis' gloo group."""
+    mesh = Mesh((world,), ("data",))
+    C.set_backend("fused")
+    try:
+        with mesh:
+            t = torch.full((5,), float(rank + 1))
+            s = C.psum(t, "data")
+            g = C.all_gather(torch.tensor([rank], dtype=torch.int64), "data", axis=0)
+            rs = C.psum_scatter(torch.arange(world * 2, dtype=torch.float32) + rank, "data", scatter_dimension=0)
+    finally:
+        C.set_backend("auto")
+    return {"psum": s.tolist(), "gather": g.tolist(), "scatter": rs.tolist(), "fused_calls": C.fused_calls}

@@ -107,3 +107,10 @@ def test_fsdp_on_2d_mesh_matches_dp():
         for a, b in zip(tree_leaves(r0["params"]), tree_leaves(r["params"])):
             assert torch.equal(a, b)
     assert r0["metrics"]["loss"][1] == 128 * steps
+
+
+def test_fused_collective_backend_falls_back_on_cpu():
+    res = sim_multiCPU_dev(W.fused_backend_fallback_worker, 2)
+    for r, out in enumerate(res):
+        assert out["psum"] == [3.0] * 5 and out["gather"] == [0, 1] and out["fused_calls"] == 0
+        assert out["scatter"] == [float(2 * (2 * r) + 1), float(2 * (2 * r + 1) + 1)]

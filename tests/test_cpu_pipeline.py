@@ -84,3 +84,57 @@ def test_balanced_split_puts_fewer_blocks_next_to_the_head():
     assert [len(r) for r in balanced_split(12, 1, 5.46)] == [12]
     s = balanced_split(4, 4, 0.3)
     assert [list(r) for r in s] == [[0], [1], [2], [3]]
+
+
+def _simulate(schedule, S, M):
+    """Runs the stages' sequences against each other the way the engine does: a stage's next operation
+    needs its input message (forward: activations from below, backward: gradients from above), messages
+    between a pair and direction are FIFO (one communicator each, receives posted in the receiver's own
+    order), sends never block. Returns True when every stage finishes, i.e. no deadlock and every
+    receive meets the send its peer issues at that position."""
+    from jax_distributed_tuts_b200.engine.pp import stage_sequence
+    seqs = [stage_sequence(schedule, S, s, M) for s in range(S)]
+    pos = [0] * S
+    up = [[] for _ in range(S)]      # up[s]: activations sent by stage s-1 to s, in send order
+    down = [[] for _ in range(S)]    # down[s]: gradients sent by stage s+1 to s
+    took_up, took_down = [0] * S, [0] * S
+    progress = True
+    while progress:
+        progress = False
+        for s in range(S):
+            if pos[s] == len(seqs[s]):
+                continue
+            kind, k = seqs[s][pos[s]]
+            if kind == "F":
+                if s > 0:
+                    if took_up[s] >= len(up[s]):
+                        continue
+                    assert up[s][took_up[s]] == k, (schedule, S, M, s, "forward receive order")
+                    took_up[s] += 1
+                if s + 1 < S:
+                    up[s + 1].append(k)
+            else:
+                if s + 1 < S:
+                    if took_down[s] >= len(down[s]):
+                        continue
+                    assert down[s][took_down[s]] == k, (schedule, S, M, s, "backward receive order")
+                    took_down[s] += 1
+                if s > 0:
+                    down[s - 1].append(k)
+            pos[s] += 1
+            progress = True
+    return all(p == len(q) for p, q in zip(pos, seqs))
+
+
+def test_pipeline_schedules_are_deadlock_free_and_cover_every_microbatch():
+    from jax_distributed_tuts_b200.engine.pp import stage_sequence
+    for schedule in ("gpipe", "1f1b"):
+        for S in range(1, 9):
+            for M in (1, 2, 3, 4, 7, 16):
+                for s in range(S):
+                    seq = stage_sequence(schedule, S, s, M)
+                    assert sorted(k for kind, k in seq if kind == "F") == list(range(M))
+                    assert sorted(k for kind, k in seq if kind == "B") == list(range(M))
+                    for k in range(M):      # a microbatch's backward never precedes its forward
+                        assert seq.index(("F", k)) < seq.index(("B", k))
+                assert _simulate(schedule, S, M), (schedule, S, M)
