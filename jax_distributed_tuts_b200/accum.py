@@ -129,6 +129,7 @@ class ScanBody:
 
 
 _SCAN_CACHE: dict = {}
+_SCAN_CACHE_MAX = 8
 
 
 def accum_grads_scan(batch: Batch, state: TrainState, key: _rng.Key, n_minbatch: int,
@@ -142,7 +143,10 @@ def accum_grads_scan(batch: Batch, state: TrainState, key: _rng.Key, n_minbatch:
                batch.labels.dtype, tuple((tuple(t.shape), t.dtype) for t in leaves), str(batch.inputs.device))
         body = _SCAN_CACHE.get(sig)
         if body is None:
+            # the entry keeps loss_fn / apply_fn alive, so their ids in `sig` cannot be recycled while it exists
             body = ScanBody(state, batch.slice(0, min_batch_size), loss_fn)
+            if len(_SCAN_CACHE) >= _SCAN_CACHE_MAX:
+                _SCAN_CACHE.pop(next(iter(_SCAN_CACHE)))       # oldest captured body (and its static buffers)
             _SCAN_CACHE[sig] = body
         return body.run(batch, state, keys, n_minbatch)
     grad_fn = value_and_grad(loss_fn, has_aux=True)

@@ -154,10 +154,13 @@ class SymmetricArena:
             import torch.distributed._symmetric_memory as symm_mem
             gname = group.group_name
             if hasattr(symm_mem, "enable_symm_mem_for_group"):
-                try:
-                    symm_mem.enable_symm_mem_for_group(gname)
-                except Exception:  # noqa: BLE001  (newer torch: every group is enabled)
-                    pass
+                import warnings
+                with warnings.catch_warnings():      # (deprecated no-op in newer torch, required by older ones)
+                    warnings.simplefilter("ignore")
+                    try:
+                        symm_mem.enable_symm_mem_for_group(gname)
+                    except Exception:  # noqa: BLE001
+                        pass
             self.buf = symm_mem.empty(self.nbytes, dtype=torch.uint8, device=device)
             self.buf.zero_()
             hdl = symm_mem.rendezvous(self.buf, gname)
