@@ -148,7 +148,7 @@ class BaselineTrainer:
             return self._step_pp(x, y)
         if not self._g:
             return self._step_impl(x, y)
-        # CUDA-graphed step: three eager steps on a side stream, then capture, then replays
+        # CUDA-graphed step: three eager steps (lazy initialisation), then one capture, then replays
         if self.graph is None:
             self._calls += 1
             if self._calls <= 3:
