@@ -157,7 +157,6 @@ def main():
         # ---- generic tier on the fused collective backend (no NCCL kernels for psum/pmean/gather/scatter) ----
         try:
             from jax_distributed_tuts_b200.comm import collectives as Cc
-            from jax_distributed_tuts_b200.parallel import fsdp
             Cc.set_backend("fused")
             before = Cc.fused_calls
             gen2 = init.replace(params=tree_map(to_dev, init.params), rng=init.rng.to(device))
