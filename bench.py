@@ -342,7 +342,6 @@ def measure(R, args, steps: int, warmup: int, rank: int, world: int, device, flu
     _sync(world)
     sampler = ClockSampler(torch.cuda.current_device()) if (clocks and rank == 0) else None
     per_step, dev_ms = time_steps(R, steps, world, flush, device)
-    clk = sampler.stop() if sampler else None
     ms_per_step = dev_ms / steps
     gb = R["global_batch"]
     # ---- end-to-end region: public API, pinned H2D every step, loss read back every step ----
@@ -377,6 +376,9 @@ def measure(R, args, steps: int, warmup: int, rank: int, world: int, device, flu
                    "readback": "loss copied to pinned host memory every step, consumed by the host one step later"}
         if loss_val is not None:
             loss_val = loss_val / R["rows_den"]
+    # (the clock sampler covers both timed regions: the device-timed one alone lasts tens of milliseconds on
+    #  the MLP, less than nvidia-smi's sampling period)
+    clk = sampler.stop() if sampler else None
     # ---- exposed communication: the same step with every cross-GPU access stubbed out ----
     if exposed and fused and world > 1:
         try:

@@ -11,8 +11,9 @@ then gradient sync + optimizer per stage.
 Here every rank of the ``pipe`` mesh axis owns a contiguous range of layers. Activations and
 activation gradients travel as NCCL point-to-point messages (``batch_isend_irecv``) posted ahead
 of the compute that needs them, so the transfer of microbatch m+1 overlaps the compute of
-microbatch m; compute is our kernels behind autograd (generic tier). A ``data`` axis, if the
-mesh has one, averages gradients with ``sync_gradients`` semantics.
+microbatch m; compute is our kernels behind autograd (generic tier; the product path with per-stage fused engines and CUDA
+graphs is ``engine/pp.py``). A ``data`` axis, if the mesh has one, averages gradients with ``sync_gradients``
+semantics.
 """
 from __future__ import annotations
 
@@ -152,9 +153,8 @@ def train_step_pp(state: TrainState, metrics: Optional[Metrics], batch: Batch, *
                 send = out.detach().to(torch.bfloat16).contiguous()
                 pending_sends.append((send, C.send_recv(send, s + 1, None, None, pipe_axis, m)))
                 saved.append((x_in, out))
-    for _, reqs in pending_sends:
-        wait(reqs)
-    pending_sends.clear()
+    # (the forward sends stay in flight: they are only waited for at the end of the step, together with the
+    #  backward ones, so a slow receiver never stalls this stage between its two phases)
 
     # ---------------- backward: microbatches in reverse ----------------
     nxt = post_recv(s + 1) if not last else None
