@@ -61,13 +61,18 @@ def init_from_env(backend: Optional[str] = None) -> tuple[int, int, torch.device
     return rank, world, device
 
 
-def _worker(rank: int, world: int, port: int, fn: Callable, args: tuple, result_dir: str) -> None:
+def _worker(rank: int, world: int, port: int, fn: Callable, args: tuple, result_dir: str,
+            timeout_s: Optional[float] = None) -> None:
     os.environ.update(RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank),
                       MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), B200DIST_FORCE_CPU="1")
     torch.set_num_threads(1)
     try:
+        kw = {}
+        if timeout_s is not None:      # a peer that dies must fail the others' collectives after this long
+            import datetime
+            kw["timeout"] = datetime.timedelta(seconds=timeout_s)
         dist.init_process_group("gloo", rank=rank, world_size=world,
-                                init_method=f"tcp://127.0.0.1:{port}")
+                                init_method=f"tcp://127.0.0.1:{port}", **kw)
         out = fn(rank, world, *args)
         torch.save(out, os.path.join(result_dir, f"rank{rank}.pt"))
         dist.barrier()
@@ -80,13 +85,17 @@ def _worker(rank: int, world: int, port: int, fn: Callable, args: tuple, result_
             dist.destroy_process_group()
 
 
-def sim_multiCPU_dev(fn: Callable[..., Any], device_count: int = 8, args: tuple = ()) -> list:
+def sim_multiCPU_dev(fn: Callable[..., Any], device_count: int = 8, args: tuple = (),
+                     timeout_s: Optional[float] = None) -> list:
     """Runs ``fn(rank, world, *args)`` on ``device_count`` CPU processes (gloo) and returns the
-    per-rank results. The fake-cluster mode of the reference (util.py:31-38)."""
+    per-rank results. The fake-cluster mode of the reference (util.py:31-38). ``timeout_s`` bounds
+    every collective: when a rank dies, the survivors' next collective raises after that long and
+    the call fails with the workers' tracebacks instead of hanging (failure detection)."""
     port = _free_port()
     with tempfile.TemporaryDirectory() as d:
         ctx = mp.get_context("spawn")
-        procs = [ctx.Process(target=_worker, args=(r, device_count, port, fn, args, d)) for r in range(device_count)]
+        procs = [ctx.Process(target=_worker, args=(r, device_count, port, fn, args, d, timeout_s))
+                 for r in range(device_count)]
         for p in procs:
             p.start()
         for p in procs:

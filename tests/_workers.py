@@ -234,3 +234,13 @@ def fused_backend_fallback_worker(rank, world):
     finally:
         C.set_backend("auto")
     return {"psum": s.tolist(), "gather": g.tolist(), "scatter": rs.tolist(), "fused_calls": C.fused_calls}
+
+
+def dying_peer_worker(rank, world):
+    """Rank 1 dies before the collective; the others must get an error out of it, not wait forever."""
+    import torch.distributed as dist
+    if rank == 1:
+        os._exit(17)
+    t = torch.ones(4)
+    dist.all_reduce(t)          # raises once the time-out set by the launcher expires (or the connection drops)
+    return {"sum": t.tolist()}

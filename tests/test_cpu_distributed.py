@@ -114,3 +114,11 @@ def test_fused_collective_backend_falls_back_on_cpu():
     for r, out in enumerate(res):
         assert out["psum"] == [3.0] * 5 and out["gather"] == [0, 1] and out["fused_calls"] == 0
         assert out["scatter"] == [float(2 * (2 * r) + 1), float(2 * (2 * r + 1) + 1)]
+
+
+def test_a_dead_rank_fails_the_job_instead_of_hanging_it():
+    import time
+    t0 = time.time()
+    with pytest.raises(RuntimeError):
+        sim_multiCPU_dev(W.dying_peer_worker, 3, timeout_s=8.0)
+    assert time.time() - t0 < 90.0
