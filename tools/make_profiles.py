@@ -13,7 +13,7 @@ OBJ = os.path.join(ROOT, "build", "obj")
 PROF = os.path.join(ROOT, "profiles")
 SASS = os.path.join(ROOT, "sass")
 KEYS = ["UTCHMMA", "UTCQMMA", "UTCBAR", "LDTM", "STTM", "UTMALDG", "UTMASTG", "UTMAPF", "UTMACCTL", "UBLKCP",
-        "SYNCS", "LDGMC", "MULTIMEM", "RED", "ATOMG", "HMMA", "UTCATOMSWS", "UCGABAR"]
+        "SYNCS", "LDGMC", "STG.SYS", "RED", "ATOMG", "HMMA", "UTCATOMSWS", "UCGABAR"]
 
 
 def sass_evidence():
@@ -22,7 +22,9 @@ def sass_evidence():
              "Counts of the instructions that identify a Blackwell-native kernel (B200_PROFILING.md): `UTC*MMA` = "
              "`tcgen05.mma`, `LDTM`/`STTM` = `tcgen05.ld/st`, `UTMALDG`/`UTMASTG` = TMA tensor copies, `SYNCS` = mbarrier, "
              "`LDGMC` = `multimem.ld_reduce`, `RED`/`ATOMG` = global reductions/atomics, `UCGABAR` = cluster barrier. "
-             "`HMMA` (legacy `mma.sync`) must be absent. Full listings: `sass/<file>.sass.gz`.", ""]
+             "`HMMA` (legacy `mma.sync`) must be absent. `multimem.st` has no mnemonic of its own: it is an ordinary "
+             "`STG.E.{64,128}.STRONG.SYS` whose address lies in the multicast mapping (column `STG.SYS`), next to the "
+             "system-scope flag stores. Full listings: `sass/<file>.sass.gz`.", ""]
     for obj in sorted(glob.glob(os.path.join(OBJ, "*.o"))):
         name = os.path.basename(obj)[:-2]
         txt = subprocess.run(["cuobjdump", "-sass", obj], capture_output=True, text=True).stdout
@@ -47,6 +49,8 @@ def sass_evidence():
                 for k in KEYS:
                     if op.startswith(k):
                         counts[k] += 1
+                if op.startswith("STG") and op.endswith("STRONG.SYS"):
+                    counts["STG.SYS"] += 1
         flush()
         lines.append("")
     open(os.path.join(PROF, "sass_summary.md"), "w").write("\n".join(lines))
