@@ -66,3 +66,24 @@ def test_errors_are_reported_not_swallowed():
     assert b"multiple of 128" in handle.b200_last_error()
     with pytest.raises(lib.B200Error):
         lib.check(rc)
+
+
+def test_comm_entry_points_validate_before_touching_a_device():
+    """Argument errors of the fused-collective entry points are reported by the host code (no GPU needed)."""
+    lib = _lib()
+    h = lib.lib()
+    assert h.b200_comm_wait_published(None, 3, 2, None) != 0 and b"bad rank" in h.b200_last_error()
+    assert h.b200_comm_wait_published(None, 0, 1, None) == 0            # one rank: nothing to wait for, no launch
+    assert h.b200_cast_zero_wait(None, None, -1, None, 0, None, 0, None, None, 0, 1, None) != 0
+    assert b"negative size" in h.b200_last_error()
+    a = lib.CollectiveArgs()
+    a.rank, a.world, a.mode, a.n = 0, 9, 0, 16
+    assert h.b200_fused_collective(ctypes.byref(a), None) != 0 and b"world" in h.b200_last_error()
+    a.world, a.mode = 2, 7
+    assert h.b200_fused_collective(ctypes.byref(a), None) != 0 and b"unknown mode" in h.b200_last_error()
+    a.mode, a.n = 0, 10                                                   # not a multiple of 4 x world
+    assert h.b200_fused_collective(ctypes.byref(a), None) != 0 and b"multiple of 4" in h.b200_last_error()
+    assert h.b200_fused_update_emulated(None, 0, None, None) != 0 and b"emulated ranks" in h.b200_last_error()
+    assert int(h.b200_fused_update_emulated_scratch_bytes()) > 0
+    assert ctypes.sizeof(lib.Seg) == 48 and lib.SIG_PUB == 128 * 8 + 128
+    assert h.b200_source_hash().decode() not in ("", "unstamped")
