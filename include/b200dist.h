@@ -276,6 +276,8 @@ typedef struct b200_seg {
   int32_t flags;     /* B200_SEG_*                                                           */
   int32_t reserved;
 } b200_seg;
+/* A segment must span fewer than 2^31 elements, pitch included (rows * max(row_len, src_pitch)): the
+ * kernel keeps 32-bit offsets relative to the segment. The engines assert it when they build the lists. */
 /* The segment is reduced by several ranks redundantly (a replicated leaf of a sharded run): sum it
  * with peer loads in rank order instead of the in-switch reduction, so all replicas get the same bits. */
 #define B200_SEG_ORDERED 1
