@@ -178,3 +178,45 @@ def test_print_exception_names_the_class(capsys):
         print_exception(e)
     out = capsys.readouterr().out
     assert "ValueError" in out and "bad shape" in out
+
+
+def test_sgd_matches_the_optax_formula_and_trains():
+    """optax.sgd: trace_t = g + momentum * trace_{t-1}; update = -lr * trace_t (nesterov: -lr * (g + momentum * trace_t))."""
+    import torch
+    from jax_distributed_tuts_b200.optim import sgd
+    p = {"w": torch.tensor([1.0, -2.0]), "b": torch.tensor([0.5])}
+    g1 = {"w": torch.tensor([0.1, 0.2]), "b": torch.tensor([-1.0])}
+    g2 = {"w": torch.tensor([-0.3, 0.0]), "b": torch.tensor([0.5])}
+    for nesterov in (False, True):
+        tx = sgd(0.1, momentum=0.9, nesterov=nesterov)
+        st = tx.init(p)
+        u1, st = tx.update(g1, st, p)
+        p1 = tx.apply_updates(p, u1)
+        u2, st = tx.update(g2, st, p1)
+        t1 = g1["w"]
+        t2 = g2["w"] + 0.9 * t1
+        want2 = -0.1 * (g2["w"] + 0.9 * t2) if nesterov else -0.1 * t2
+        assert torch.allclose(u2["w"], want2) and torch.allclose(st[0].trace["w"], t2)
+    plain = sgd(0.5)
+    u, st = plain.update(g1, plain.init(p), p)
+    assert torch.allclose(u["b"], torch.tensor([0.5])) and len(st) == 2
+    # plugs into the reference's train step
+    from jax_distributed_tuts_b200 import rng
+    from jax_distributed_tuts_b200.config import dp_config
+    from jax_distributed_tuts_b200.mesh import Mesh
+    from jax_distributed_tuts_b200.models.mlp import Classifier
+    from jax_distributed_tuts_b200.parallel import dp
+    from jax_distributed_tuts_b200.state import Batch
+    cfg = dp_config()
+    cfg.model.dropout_rate = 0.0
+    mesh = Mesh((1,), ("data",), device=torch.device("cpu"))
+    x = torch.randn(32, 784, generator=torch.Generator().manual_seed(0))
+    y = torch.randint(0, 10, (32,), generator=torch.Generator().manual_seed(1))
+    with mesh:
+        state = dp.init_dp(rng.PRNGKey(0), x, Classifier(cfg.model), optimizer=sgd(0.05, momentum=0.9))
+        step = dp.make_train_step_dp(mesh, num_minibatches=2)
+        losses = []
+        for _ in range(8):
+            state, m = step(state, None, Batch(x, y))
+            losses.append(float(m["loss"][0]) / m["loss"][1])
+    assert losses[-1] < 0.7 * losses[0], losses
