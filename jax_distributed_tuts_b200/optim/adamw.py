@@ -46,7 +46,7 @@ def _like(box, v):
 
 @dataclasses.dataclass(frozen=True)
 class AdamW:
-    learning_rate: float
+    learning_rate: float      # or a schedule: count -> rate (optim/schedules.py)
     b1: float = 0.9
     b2: float = 0.999
     eps: float = 1e-8
@@ -67,10 +67,12 @@ class AdamW:
         nu = tree_map(lambda v, g: _like(v, b2 * _val(v) + (1 - b2) * _val(g).float() ** 2), adam.nu, grads,
                       is_leaf=is_partitioned)
         c1, c2 = 1.0 - b1 ** t, 1.0 - b2 ** t
+        from .schedules import resolve
+        lr = resolve(self.learning_rate, adam.count)      # a float, or an optax-style schedule count -> rate
 
         def upd(m, v, p):
             mh, vh = _val(m) / c1, _val(v) / c2
-            return _like(p, -self.learning_rate * (mh / (vh.sqrt() + self.eps) + self.weight_decay * _val(p).float()))
+            return _like(p, -lr * (mh / (vh.sqrt() + self.eps) + self.weight_decay * _val(p).float()))
 
         updates = tree_map(upd, mu, nu, params, is_leaf=is_partitioned)
         return updates, (ScaleByAdamState(count=t, mu=mu, nu=nu), e1, e2)

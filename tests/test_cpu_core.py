@@ -220,3 +220,28 @@ def test_sgd_matches_the_optax_formula_and_trains():
             state, m = step(state, None, Batch(x, y))
             losses.append(float(m["loss"][0]) / m["loss"][1])
     assert losses[-1] < 0.7 * losses[0], losses
+
+
+def test_learning_rate_schedules():
+    import torch
+    from jax_distributed_tuts_b200.optim import adamw, sgd, warmup_cosine_decay_schedule, linear_schedule
+    s = warmup_cosine_decay_schedule(0.0, 1e-3, warmup_steps=10, decay_steps=100, end_value=1e-4)
+    assert s(0) == 0.0 and abs(s(5) - 5e-4) < 1e-12 and abs(s(10) - 1e-3) < 1e-12
+    assert abs(s(100) - 1e-4) < 1e-9 and abs(s(1000) - 1e-4) < 1e-9 and s(30) > s(60) > s(90)
+    lin = linear_schedule(1.0, 0.0, 4, transition_begin=2)
+    assert [lin(c) for c in (0, 2, 4, 6, 9)] == [1.0, 1.0, 0.5, 0.0, 0.0]
+    # the optimizers evaluate the schedule at the number of updates done so far
+    p = {"w": torch.ones(2)}
+    g = {"w": torch.ones(2)}
+    tx = sgd(lin)
+    st = tx.init(p)
+    seen = []
+    for _ in range(5):
+        u, st = tx.update(g, st, p)
+        seen.append(-u["w"][0].item())
+    assert seen == [1.0, 1.0, 1.0, 0.75, 0.5] and st[1].count == 5
+    ta = adamw(lambda count: 0.1 if count == 0 else 0.0, weight_decay=0.0)
+    sa = ta.init(p)
+    u0, sa = ta.update(g, sa, p)
+    u1, sa = ta.update(g, sa, p)
+    assert abs(u0["w"][0].item() + 0.1) < 1e-6 and u1["w"][0].item() == 0.0
