@@ -49,6 +49,7 @@ def balanced_split(n_layer: int, n_stages: int, head_cost: float, embed_cost: fl
     """Contiguous layer ranges that minimise the most loaded stage, where the last stage also carries
     the head (``head_cost`` in units of one block) and the first the embeddings. The last stage may
     end up with no block at all."""
+    assert n_layer >= n_stages - 1, f"{n_stages} stages need at least {n_stages - 1} blocks, the model has {n_layer}"
     best, best_cut = None, None      # best = (largest load, sum of squared loads): even stages among equal maxima
 
     def rec(start: int, stage: int, cuts: List[int], worst: float, sq: float):
@@ -61,8 +62,8 @@ def balanced_split(n_layer: int, n_stages: int, head_cost: float, embed_cost: fl
             if best is None or cand < best:
                 best, best_cut = cand, cuts + [n_layer]
             return
-        lo = 1 if stage == 0 else 0       # the first stage keeps at least one block (it has the cheap embeddings)
-        for n in range(lo, n_layer - start + 1):
+        # every stage but the last keeps at least one block (only the last owns something else: the head)
+        for n in range(1, n_layer - start + 1):
             load = n + (embed_cost if stage == 0 else 0.0)
             rec(start + n, stage + 1, cuts + [start + n], max(worst, load), sq + load * load)
 
@@ -90,7 +91,8 @@ def stage_sequence(schedule: str, n_stages: int, stage: int, n_micro: int) -> Li
 
 
 class PipelineEngine:
-    """``train_step(batch) -> (loss_sum, token_count)`` for one (data, pipe) mesh coordinate."""
+    """``train_step(batch) -> (loss_sum, token_count)`` for one (data, pipe) mesh coordinate. The mesh must
+    cover the whole job; the engine's kernels run on the stream that is current when it is constructed."""
 
     def __init__(self, config, mesh: Mesh, *, batch_per_replica: int, seq_len: Optional[int] = None,
                  num_microbatches: int = 4, lr: float = 3e-4, init_params: Optional[Dict] = None,
@@ -147,9 +149,9 @@ class PipelineEngine:
 
     # ------------------------------------------------------------------ communicators -------------
     def _setup_groups(self) -> None:
-        """One 2-rank communicator per adjacent stage pair of every pipeline (every rank creates all of
-        them, in the same order), one for the (first, last) pair, and the group over the whole mesh for
-        the metrics."""
+        """Two 2-rank communicators (one per direction) per adjacent stage pair of every pipeline and one for
+        the (first, last) pair; every rank creates all of them, in the same order. The metrics use the
+        communicator of the whole job."""
         m = self.mesh
         ai_p = m.axis_names.index(self.pipe_axis)
         others = [i for i in range(len(m.axis_names)) if i != ai_p]
