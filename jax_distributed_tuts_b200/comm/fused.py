@@ -121,6 +121,11 @@ class AxisWorkspace:
         return out.view(x.dtype).reshape((self.world,) + tuple(x.shape))
 
 
+def reset() -> None:
+    """Drops every axis workspace (their symmetric allocations are freed with them)."""
+    _GROUPS.clear()
+
+
 def workspace(mesh: Mesh, axes: AxisNames) -> AxisWorkspace:
     """The (lazily created) workspace of an axis. Collective on first use: every rank of the axis
     must make its first fused call on that axis at the same point of the program."""
@@ -133,7 +138,7 @@ def workspace(mesh: Mesh, axes: AxisNames) -> AxisWorkspace:
 
 
 def _reducible(t: torch.Tensor) -> bool:
-    return t.is_cuda and (t.dtype in (torch.float32, torch.bfloat16, torch.float16) or
+    return t.is_cuda and t.numel() > 0 and (t.dtype in (torch.float32, torch.bfloat16, torch.float16) or
                           (not t.dtype.is_floating_point and not t.dtype.is_complex and t.numel() <= 64))
 
 
